@@ -1,0 +1,140 @@
+/* cnfb200.h — C ABI of libcnfb200.so, the B200-native batched augmented-dynamics solve
+ * of ContinuousNormalizingFlows.jl ("MatrixMode" hot path).
+ *
+ * Each entry point cites the reference interface it replaces (paths relative to the
+ * reference checkout).  Plain C: pointers + sizes only; the Julia side binds these with
+ * `ccall`, the in-repo Python host mirror binds them with ctypes.
+ *
+ * Layouts: every matrix is Julia column-major `rows x B`, i.e. sample-major contiguous
+ * (`xs[b*nvars + i]`).  Pointers may be host or device pointers (detected with
+ * cudaPointerGetAttributes); host buffers are copied in/out inside the call.
+ * No pointer is retained after a call returns.
+ *
+ * Return codes: 0 ok; >0 solver retcodes (outputs are still written, like the reference,
+ * which reads the last state without checking: src/base_icnf.jl:141-142);
+ * <0 hard failure, text via cnfb200_last_error().
+ */
+#ifndef CNFB200_H
+#define CNFB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CNF_MAX_LAYERS 8
+
+/* flags: the type-level booleans of `ICNF{...}` (src/base_icnf.jl:42-60, src/icnf.jl:69-104) */
+#define CNF_FLAG_COND        (1u << 0) /* COND: CondLayer wraps nn (src/layers/cond_layer.jl:1-9) */
+#define CNF_FLAG_AUGMENTED   (1u << 1) /* naugmented != 0 */
+#define CNF_FLAG_NORM_Z      (1u << 2) /* lambda1 != 0: integrate ||zdot||_2 (src/icnf.jl:335-341) */
+#define CNF_FLAG_NORM_J      (1u << 3) /* lambda2 != 0: integrate ||eps^T J||_2 (src/icnf.jl:342-348) */
+#define CNF_FLAG_NORM_Z_AUG  (1u << 4) /* lambda3 != 0: ||z_aug(t1)||_2 (src/base_icnf.jl:179-187) */
+
+/* mode: src/types.jl Mode {TestMode, TrainMode} */
+#define CNF_MODE_TEST  0 /* exact trace, R = D+1 rows (src/icnf.jl:148-184) */
+#define CNF_MODE_TRAIN 1 /* Hutchinson,  R = D+3 rows (src/icnf.jl:318-456) */
+
+/* trace_mode: src/types.jl DIVecJacMatrixMode / DIJacVecMatrixMode */
+#define CNF_TRACE_VJP 0
+#define CNF_TRACE_JVP 1
+
+/* status / retcodes */
+#define CNF_OK               0
+#define CNF_RET_MAXITERS     1
+#define CNF_RET_DTLESSTHANMIN 2
+#define CNF_RET_UNSTABLE     3
+#define CNF_ERR_BADCONFIG   (-1)
+#define CNF_ERR_CUDA        (-2)
+#define CNF_ERR_NCCL        (-3)
+#define CNF_ERR_OOM         (-4)
+#define CNF_ERR_BADARG      (-5)
+#define CNF_ERR_UNSUPPORTED (-6)
+
+/* mirrors the fields of the `ICNF` struct the path reads (src/icnf.jl:69-104) plus the
+ * `sol_kwargs` the solver consumes (src/base_icnf.jl:26,141). */
+typedef struct cnf_config {
+    int32_t D;          /* nvars + naugmented */
+    int32_t C;          /* condition rows (0 if unconditional) */
+    int32_t nvars;
+    int32_t n_layers;   /* L Dense(tanh) layers */
+    int32_t dims[CNF_MAX_LAYERS + 1]; /* d0 = D+C, ..., dL = D */
+    int32_t trace_mode; /* CNF_TRACE_* */
+    uint32_t flags;     /* CNF_FLAG_* */
+    float lambda1, lambda2, lambda3;
+    float reltol, abstol;     /* 0 => solver default (1e-3, 1e-6) */
+    int64_t maxiters;         /* 0 => 1e5 */
+    float dt0, dtmax, dtmin;  /* 0 => solver default */
+    int32_t device;           /* CUDA device ordinal of this process */
+    int32_t kernel_path;      /* 0 auto; 1 force generic SIMT; 2 force register-resident narrow; 3 force tcgen05 */
+} cnf_config;
+
+typedef struct cnf_stats {
+    int64_t naccept, nreject, nf; /* nf = augmented_f evaluations */
+    int32_t retcode;
+    int32_t kernel_path;          /* path actually used (1,2,3) */
+    float t_final, dt_last;
+    double ms_total;              /* device time of the whole call (CUDA events) */
+    double ms_solve;              /* device time of the RK loop only */
+    int64_t gpu_launches;         /* kernels launched by this call */
+} cnf_stats;
+
+typedef struct cnf_handle cnf_handle;
+
+const char* cnfb200_version(void);
+
+/* replaces construct(...) bookkeeping on the device side (src/base_icnf.jl:1-77) */
+int32_t cnfb200_create(const cnf_config* cfg, cnf_handle** out);
+int32_t cnfb200_destroy(cnf_handle* h);
+const char* cnfb200_last_error(const cnf_handle* h);
+
+/* flat ComponentArray parameter vector `ps` + per-layer weight/bias offsets (in floats);
+ * weight l is d_{l+1} x d_l column-major (Lux Dense; src/exts/mlj_ext/core_icnf.jl:37-38) */
+int32_t cnfb200_set_params(cnf_handle* h, const float* theta, int64_t n,
+                           const int64_t* w_off, const int64_t* b_off);
+
+/* batch sharding over one-process-per-GPU ranks: rank 0 makes an id, every rank inits.
+ * Afterwards every solve allreduces the scalar error-norm partials each attempted step
+ * (whole-batch RMS semantics of the matrix-valued ODE state, src/base_icnf.jl:280-285)
+ * and cnfb200_loss_grad allreduces loss and gradient.  B_global = sum of local B. */
+int32_t cnfb200_comm_unique_id(char id_out[128]);
+int32_t cnfb200_comm_init(cnf_handle* h, int32_t nranks, int32_t rank, const char id[128]);
+
+/* one evaluation du = augmented_f(u, p, t, icnf, mode, nn, st, eps)
+ * (src/icnf.jl:148-164 Test; :318-350 Train/VecJac; :384-420 Train/JacVec).  u, du: R x B. */
+int32_t cnfb200_augmented_f(cnf_handle* h, int32_t mode, const float* u, const float* ys,
+                            const float* eps, int64_t B, float* du);
+
+/* replaces inference(icnf, mode, xs[, ys], ps, st) = inference_prob + inference_sol
+ * (src/base_icnf.jl:266-309, 167-189, 407-426).  xs: nvars x B; ys: C x B or NULL;
+ * eps: D x B (may be NULL in TestMode, where it is unused);
+ * logp: B; regs: 3 x B rows (E, n, A) in TrainMode, 1 x B (A) in TestMode, or NULL;
+ * z_out: D x B final latent state or NULL. */
+int32_t cnfb200_logdensity(cnf_handle* h, int32_t mode, const float* xs, const float* ys,
+                           const float* eps, int64_t B, float t0, float t1,
+                           float* logp, float* regs, float* z_out, cnf_stats* stats);
+
+/* replaces loss(icnf, TrainMode(), xs[, ys], ps, st) (src/icnf.jl:481-502) and its gradient
+ * w.r.t. ps / xs (call sites src/exts/mlj_ext/core_icnf.jl:59-63, test/call_tests.jl:239-251)
+ * by a discretise-then-optimise reverse sweep.  grad_theta: n floats (layout of theta) or NULL;
+ * grad_x: nvars x B or NULL.  With a communicator, loss and grad_theta are global means/sums. */
+int32_t cnfb200_loss_grad(cnf_handle* h, const float* xs, const float* ys, const float* eps,
+                          int64_t B, float t0, float t1, float* loss, float* grad_theta,
+                          float* grad_x, cnf_stats* stats);
+
+/* replaces generate(...) = generate_prob + generate_sol (src/base_icnf.jl:358-405, 202-211,
+ * 447-466): integrates z0 (D x n, drawn by the caller from basedist) from t_from to t_to
+ * and returns rows 1:nvars.  xs_out: nvars x n. */
+int32_t cnfb200_generate(cnf_handle* h, int32_t mode, const float* z0, const float* ys,
+                         const float* eps, int64_t n, float t_from, float t_to,
+                         float* xs_out, cnf_stats* stats);
+
+/* measurement helper (bench only): sustained FP32 FFMA rate of this GPU in TFLOP/s,
+ * the roofline denominator MEASURED_PEAKS.json does not provide. */
+int32_t cnfb200_measure_fp32_peak(int32_t device, double* tflops_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CNFB200_H */
