@@ -1,0 +1,595 @@
+// cnf_api.cu — C-ABI entry points of libcnfb200.so (include/cnfb200.h) and the host-side
+// orchestration: the host only enqueues kernels and polls the device controller block.
+#include "cnf_internal.h"
+#include <cstring>
+#include <new>
+
+int launch_eval_generic_sel(cnf_handle* h, const CnfBufs& bf, int mode, int src_sel,
+                            const float* src_ptr, int kidx, float* kout_ptr, int check_done);
+
+static bool is_device_ptr(const void* p) {
+    if (!p) return false;
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+static inline long long round_up(long long x, long long m) { return (x + m - 1) / m * m; }
+
+extern "C" const char* cnfb200_version(void) { return "cnfb200 0.1.0 (sm_100a)"; }
+
+extern "C" const char* cnfb200_last_error(const cnf_handle* h) { return h ? h->err.c_str() : "null handle"; }
+
+static int validate_config(const cnf_config& c, std::string& err) {
+    if (c.n_layers < 1 || c.n_layers > CNF_MAX_LAYERS) { err = "n_layers out of range"; return CNF_ERR_BADCONFIG; }
+    if (c.D < 1 || c.nvars < 1 || c.nvars > c.D || c.C < 0) { err = "bad D/nvars/C"; return CNF_ERR_BADCONFIG; }
+    if (c.dims[0] != c.D + c.C) { err = "dims[0] must equal D + C"; return CNF_ERR_BADCONFIG; }
+    if (c.dims[c.n_layers] != c.D) { err = "dims[L] must equal D"; return CNF_ERR_BADCONFIG; }
+    for (int l = 0; l <= c.n_layers; ++l)
+        if (c.dims[l] < 1) { err = "layer width < 1"; return CNF_ERR_BADCONFIG; }
+    if (c.trace_mode != CNF_TRACE_VJP && c.trace_mode != CNF_TRACE_JVP) { err = "bad trace_mode"; return CNF_ERR_BADCONFIG; }
+    if (((c.flags & CNF_FLAG_COND) != 0) != (c.C > 0)) { err = "COND flag and C disagree"; return CNF_ERR_BADCONFIG; }
+    return CNF_OK;
+}
+
+extern "C" int32_t cnfb200_create(const cnf_config* cfg, cnf_handle** out) {
+    if (!cfg || !out) return CNF_ERR_BADARG;
+    *out = nullptr;
+    cnf_handle* h = new (std::nothrow) cnf_handle();
+    if (!h) return CNF_ERR_OOM;
+    *out = h;  // returned even on failure so the caller can read last_error, then destroy
+    h->cfg = *cfg;
+    int rc = validate_config(h->cfg, h->err);
+    if (rc) return rc;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        h->err = "no CUDA device: libcnfb200 has no CPU fallback";
+        return CNF_ERR_CUDA;
+    }
+    h->device = cfg->device;
+    CNF_CUDA(cudaSetDevice(h->device));
+    cudaDeviceProp prop;
+    CNF_CUDA(cudaGetDeviceProperties(&prop, h->device));
+    if (prop.major != 10) {
+        h->err = "libcnfb200 is built for sm_100a only";
+        return CNF_ERR_UNSUPPORTED;
+    }
+    CNF_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    CNF_CUDA(cudaEventCreate(&h->ev0));
+    CNF_CUDA(cudaEventCreate(&h->ev1));
+    CNF_CUDA(cudaEventCreate(&h->ev2));
+    CNF_CUDA(cudaEventCreate(&h->ev3));
+    CNF_CUDA(cudaEventCreateWithFlags(&h->evchk[0], cudaEventDisableTiming));
+    CNF_CUDA(cudaEventCreateWithFlags(&h->evchk[1], cudaEventDisableTiming));
+    CNF_CUDA(cudaMalloc(&h->d_ctrl, sizeof(CnfCtrl)));
+    CNF_CUDA(cudaMallocHost(&h->h_ctrl, 2 * sizeof(CnfCtrl)));
+    CNF_CUDA(cudaMalloc(&h->d_dts, CNF_MAX_SLOTS * sizeof(float)));
+    CNF_CUDA(cudaMalloc(&h->d_lossacc, sizeof(double)));
+    CNF_CUDA(cudaMalloc(&h->d_slots, CNF_MAX_SLOTS * sizeof(float*)));
+    CNF_CUDA(cudaMemset(h->d_slots, 0, CNF_MAX_SLOTS * sizeof(float*)));
+    cnf_upload_constants();
+    CNF_CUDA(cudaGetLastError());
+    return CNF_OK;
+}
+
+static void free_workspaces(cnf_handle* h) {
+    for (int j = 0; j < 7; ++j) { cudaFree(h->d_K[j]); h->d_K[j] = nullptr; }
+    cudaFree(h->d_S); h->d_S = nullptr;
+    cudaFree(h->d_eps); h->d_eps = nullptr;
+    cudaFree(h->d_ys); h->d_ys = nullptr;
+    for (float* p : h->slots) cudaFree(p);
+    h->slots.clear();
+    for (int j = 0; j < 16; ++j) { cudaFree(h->d_bw[j]); h->d_bw[j] = nullptr; }
+    h->cap_bw = 0;
+    h->cap_B = 0;
+    h->cap_R = 0;
+}
+
+extern "C" int32_t cnfb200_destroy(cnf_handle* h) {
+    if (!h) return CNF_OK;
+    if (h->stream) {
+        cudaSetDevice(h->device);
+        cudaStreamSynchronize(h->stream);
+    }
+    free_workspaces(h);
+    cudaFree(h->d_io);
+    cudaFree(h->d_theta); cudaFree(h->d_wt); cudaFree(h->d_grad);
+    cudaFree(h->d_ctrl); cudaFree(h->d_dts); cudaFree(h->d_lossacc); cudaFree(h->d_slots);
+    if (h->h_ctrl) cudaFreeHost(h->h_ctrl);
+    if (h->ev0) cudaEventDestroy(h->ev0);
+    if (h->ev1) cudaEventDestroy(h->ev1);
+    if (h->ev2) cudaEventDestroy(h->ev2);
+    if (h->ev3) cudaEventDestroy(h->ev3);
+    if (h->evchk[0]) cudaEventDestroy(h->evchk[0]);
+    if (h->evchk[1]) cudaEventDestroy(h->evchk[1]);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    cudaGetLastError();
+    delete h;
+    return CNF_OK;
+}
+
+// W (col-major dout x din) -> Wt (row-major dout x din): Wt[o*din + i] = W[i*dout + o]
+__global__ void k_transpose_w(const float* __restrict__ W, int dout, int din, float* __restrict__ Wt) {
+    long long n = (long long)dout * din;
+    for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < n;
+         p += (long long)gridDim.x * blockDim.x) {
+        int o = (int)(p / din), i = (int)(p % din);
+        Wt[p] = W[(long long)i * dout + o];
+    }
+}
+
+extern "C" int32_t cnfb200_set_params(cnf_handle* h, const float* theta, int64_t n,
+                                      const int64_t* w_off, const int64_t* b_off) {
+    if (!h || !theta || !w_off || !b_off || n <= 0) return CNF_ERR_BADARG;
+    CNF_CUDA(cudaSetDevice(h->device));
+    const cnf_config& c = h->cfg;
+    long long wt_total = 0;
+    for (int l = 0; l < c.n_layers; ++l) {
+        long long wsz = (long long)c.dims[l] * c.dims[l + 1];
+        if (w_off[l] < 0 || w_off[l] + wsz > n || b_off[l] < 0 || b_off[l] + c.dims[l + 1] > n) {
+            h->err = "set_params: offsets outside theta";
+            return CNF_ERR_BADARG;
+        }
+        h->w_off[l] = w_off[l];
+        h->b_off[l] = b_off[l];
+        h->wt_off[l] = wt_total;
+        wt_total += wsz;
+    }
+    if (n != h->nparams) {
+        cudaFree(h->d_theta); cudaFree(h->d_wt); cudaFree(h->d_grad);
+        h->d_theta = h->d_wt = h->d_grad = nullptr;
+        CNF_CUDA(cudaMalloc(&h->d_theta, n * sizeof(float)));
+        CNF_CUDA(cudaMalloc(&h->d_wt, wt_total * sizeof(float)));
+        CNF_CUDA(cudaMalloc(&h->d_grad, n * sizeof(float)));
+        h->nparams = n;
+    }
+    CNF_CUDA(cudaMemcpyAsync(h->d_theta, theta, n * sizeof(float), cudaMemcpyDefault, h->stream));
+    CnfNet& net = h->net;
+    net.L = c.n_layers; net.D = c.D; net.C = c.C;
+    net.flags = c.flags; net.trace_mode = c.trace_mode;
+    for (int l = 0; l <= c.n_layers; ++l) net.dims[l] = c.dims[l];
+    for (int l = 0; l < c.n_layers; ++l) {
+        net.W[l] = h->d_theta + h->w_off[l];
+        net.b[l] = h->d_theta + h->b_off[l];
+        net.Wt[l] = h->d_wt + h->wt_off[l];
+        net.w_off[l] = h->w_off[l];
+        net.b_off[l] = h->b_off[l];
+        long long wsz = (long long)c.dims[l] * c.dims[l + 1];
+        unsigned g = (unsigned)((wsz + 255) / 256);
+        if (g > 1184) g = 1184;
+        k_transpose_w<<<g, 256, 0, h->stream>>>(net.W[l], c.dims[l + 1], c.dims[l], h->d_wt + h->wt_off[l]);
+    }
+    CNF_CUDA(cudaGetLastError());
+    CNF_CUDA(cudaStreamSynchronize(h->stream));  // theta may be a pageable host buffer
+    h->have_params = true;
+    return CNF_OK;
+}
+
+// ------------------------------------------------------------------ workspaces
+static int ensure_slots(cnf_handle* h, size_t want) {
+    if (want > CNF_MAX_SLOTS) want = CNF_MAX_SLOTS;
+    if (h->slots.size() >= want) return CNF_OK;
+    size_t old = h->slots.size();
+    while (h->slots.size() < want) {
+        float* p = nullptr;
+        CNF_CUDA(cudaMalloc(&p, h->slot_elems * sizeof(float)));
+        h->slots.push_back(p);
+    }
+    CNF_CUDA(cudaMemcpyAsync(h->d_slots + old, h->slots.data() + old,
+                             (h->slots.size() - old) * sizeof(float*), cudaMemcpyHostToDevice, h->stream));
+    return CNF_OK;
+}
+
+static int ensure_workspace(cnf_handle* h, long long B, int R) {
+    long long Bs = round_up(B, 128);
+    if (Bs <= h->cap_B && R <= h->cap_R) return CNF_OK;
+    CNF_CUDA(cudaStreamSynchronize(h->stream));
+    long long capB = Bs > h->cap_B ? Bs : h->cap_B;
+    int capR = R > h->cap_R ? R : h->cap_R;
+    free_workspaces(h);
+    const cnf_config& c = h->cfg;
+    for (int j = 0; j < 7; ++j) CNF_CUDA(cudaMalloc(&h->d_K[j], (size_t)capR * capB * sizeof(float)));
+    CNF_CUDA(cudaMalloc(&h->d_S, (size_t)c.D * capB * sizeof(float)));
+    CNF_CUDA(cudaMalloc(&h->d_eps, (size_t)c.D * capB * sizeof(float)));
+    CNF_CUDA(cudaMalloc(&h->d_ys, (size_t)(c.C > 0 ? c.C : 1) * capB * sizeof(float)));
+    h->cap_B = capB;
+    h->cap_R = capR;
+    h->slot_elems = (long long)capR * capB;
+    return ensure_slots(h, 2);
+}
+
+static int ensure_io(cnf_handle* h, long long nfloats) {
+    if (nfloats <= h->cap_io) return CNF_OK;
+    CNF_CUDA(cudaStreamSynchronize(h->stream));
+    cudaFree(h->d_io);
+    h->d_io = nullptr;
+    CNF_CUDA(cudaMalloc(&h->d_io, (size_t)nfloats * sizeof(float)));
+    h->cap_io = nfloats;
+    return CNF_OK;
+}
+
+// bring a caller matrix (rows x B, sample-major; host or device) into an SoA buffer
+static int stage_in(cnf_handle* h, const float* src, int rows, long long B, float* dst, long long Bs,
+                    long long io_off) {
+    const float* dsrc = src;
+    if (!is_device_ptr(src)) {
+        CNF_CUDA(cudaMemcpyAsync(h->d_io + io_off, src, (size_t)rows * B * sizeof(float),
+                                 cudaMemcpyHostToDevice, h->stream));
+        dsrc = h->d_io + io_off;
+    }
+    launch_pack_rows(h, dsrc, rows, B, dst, Bs);
+    return CNF_OK;
+}
+
+static CnfBufs make_bufs(cnf_handle* h, long long B) {
+    CnfBufs bf;
+    bf.slots = h->d_slots;
+    for (int j = 0; j < 7; ++j) bf.K[j] = h->d_K[j];
+    bf.S = h->d_S;
+    bf.eps = h->d_eps;
+    bf.ys = h->d_ys;
+    bf.Bs = round_up(B, 128);
+    bf.B = (int)B;
+    return bf;
+}
+
+// ------------------------------------------------------------------ the solve (device-driven)
+static int eval_stage(cnf_handle* h, const CnfBufs& bf, int mode, int src_sel, int kidx, int check_done) {
+    return launch_eval_generic_sel(h, bf, mode, src_sel, nullptr, kidx, nullptr, check_done);
+}
+
+static int enqueue_attempt(cnf_handle* h, const CnfBufs& bf, int mode) {
+    int rc;
+    for (int i = 1; i <= 5; ++i) {
+        launch_combine(h, bf, i);
+        if ((rc = eval_stage(h, bf, mode, 0 /*SRC_S*/, i, 1))) return rc;
+    }
+    launch_combine(h, bf, 6);
+    if ((rc = eval_stage(h, bf, mode, 1 /*SRC_UNEW*/, 6, 1))) return rc;
+    launch_errnorm(h, bf);
+    if (h->nranks > 1 && (rc = cnf_nccl_allreduce_f64(h, &h->d_ctrl->errsum, 1))) return rc;
+    launch_controller(h);
+    return CNF_OK;
+}
+
+// state already packed into slot 0; runs the adaptive solve; fills stats (host copy of ctrl)
+static int solve_device(cnf_handle* h, const CnfBufs& bf, int mode, int R, long long Bglobal,
+                        float t0, float t1, bool use_tape, CnfCtrl* out) {
+    const cnf_config& c = h->cfg;
+    CnfCtrl ic;
+    memset(&ic, 0, sizeof(ic));
+    ic.qold = CNF_QOLDINIT;
+    ic.nglobal = (double)R * (double)Bglobal;
+    ic.maxiters = c.maxiters > 0 ? c.maxiters : CNF_DEFAULT_MAXITERS;
+    ic.t = ic.t0 = t0;
+    ic.t1 = t1;
+    ic.tdir = (t1 >= t0) ? 1.0f : -1.0f;
+    ic.dtmax = c.dtmax > 0 ? c.dtmax : fabsf(t1 - t0);
+    ic.dtmin = c.dtmin;
+    ic.reltol = c.reltol > 0 ? c.reltol : CNF_DEFAULT_RELTOL;
+    ic.abstol = c.abstol > 0 ? c.abstol : CNF_DEFAULT_ABSTOL;
+    ic.use_tape = use_tape ? 1 : 0;
+    ic.R = R;
+    ic.D = c.D;
+    ic.nf = 1;
+    if (c.dt0 > 0) ic.dt = ic.tdir * c.dt0;
+    h->h_ctrl[0] = ic;
+    CNF_CUDA(cudaMemcpyAsync(h->d_ctrl, &h->h_ctrl[0], sizeof(CnfCtrl), cudaMemcpyHostToDevice, h->stream));
+    CNF_CUDA(cudaEventRecord(h->ev1, h->stream));
+    int rc;
+    if ((rc = eval_stage(h, bf, mode, 2 /*SRC_SLOT0*/, 0, 0))) return rc;   // k1 = f(u0)
+    if (c.dt0 > 0) {
+        launch_initdt(h, 2);
+    } else {
+        launch_initnorm(h, bf, 0);
+        if (h->nranks > 1 && (rc = cnf_nccl_allreduce_f64(h, h->d_ctrl->initsum, 2))) return rc;
+        launch_initdt(h, 0);
+        launch_combine(h, bf, -1);
+        if ((rc = launch_eval_generic_sel(h, bf, mode, 0 /*SRC_S*/, nullptr, -1, bf.K[1], 0))) return rc;
+        launch_initnorm(h, bf, 1);
+        if (h->nranks > 1 && (rc = cnf_nccl_allreduce_f64(h, h->d_ctrl->initsum + 2, 1))) return rc;
+        launch_initdt(h, 1);
+    }
+    // attempts are enqueued speculatively; kernels of attempts after `done` return immediately
+    long long launched = 0;
+    int pend = -1;  // index of the pinned snapshot in flight
+    for (;;) {
+        if (use_tape && (long long)h->slots.size() < launched + 2 && (rc = ensure_slots(h, (size_t)(launched + 10)))) return rc;
+        if ((rc = enqueue_attempt(h, bf, mode))) return rc;
+        launched++;
+        int cur = (int)(launched & 1);
+        CNF_CUDA(cudaMemcpyAsync(&h->h_ctrl[cur], h->d_ctrl, sizeof(CnfCtrl), cudaMemcpyDeviceToHost, h->stream));
+        CNF_CUDA(cudaEventRecord(h->evchk[cur], h->stream));
+        if (pend >= 0) {
+            CNF_CUDA(cudaEventSynchronize(h->evchk[pend]));
+            if (h->h_ctrl[pend].done) break;
+        }
+        pend = cur;
+        if (launched > ic.maxiters + 2) break;
+    }
+    CNF_CUDA(cudaEventRecord(h->ev2, h->stream));
+    CNF_CUDA(cudaMemcpyAsync(&h->h_ctrl[0], h->d_ctrl, sizeof(CnfCtrl), cudaMemcpyDeviceToHost, h->stream));
+    CNF_CUDA(cudaStreamSynchronize(h->stream));
+    *out = h->h_ctrl[0];
+    CNF_CUDA(cudaGetLastError());
+    return CNF_OK;
+}
+
+static void fill_stats(cnf_handle* h, const CnfCtrl& c, cnf_stats* st) {
+    if (!st) return;
+    memset(st, 0, sizeof(*st));
+    st->naccept = c.naccept;
+    st->nreject = c.nreject;
+    st->nf = c.nf;
+    st->retcode = c.retcode;
+    st->kernel_path = h->path_used;
+    st->t_final = c.t;
+    st->dt_last = c.dt_last;
+    float ms = 0.0f;
+    if (cudaEventElapsedTime(&ms, h->ev0, h->ev3) == cudaSuccess) st->ms_total = ms;
+    if (cudaEventElapsedTime(&ms, h->ev1, h->ev2) == cudaSuccess) st->ms_solve = ms;
+    cudaGetLastError();
+    st->gpu_launches = h->launches;
+}
+
+// ------------------------------------------------------------------ shared front/back ends
+struct IoPlan {
+    long long off_xs, off_ys, off_eps, off_logp, off_regs, off_z, total;
+};
+static IoPlan plan_io(const cnf_config& c, long long B, int rows_x) {
+    IoPlan p;
+    long long o = 0;
+    p.off_xs = o; o += (long long)rows_x * B;
+    p.off_ys = o; o += (long long)c.C * B;
+    p.off_eps = o; o += (long long)c.D * B;
+    p.off_logp = o; o += B;
+    p.off_regs = o; o += 3 * B;
+    p.off_z = o; o += (long long)c.D * B;
+    p.total = o;
+    return p;
+}
+
+// pack [x; 0] into slot 0, eps and ys into SoA buffers
+static int load_problem(cnf_handle* h, const CnfBufs& bf, const IoPlan& io, int mode, int R,
+                        const float* x, int rows_x, const float* ys, const float* eps, long long B) {
+    const cnf_config& c = h->cfg;
+    int rc;
+    float* slot0 = h->slots[0];
+    CNF_CUDA(cudaMemsetAsync(slot0, 0, (size_t)R * bf.Bs * sizeof(float), h->stream));
+    if ((rc = stage_in(h, x, rows_x, B, slot0, bf.Bs, io.off_xs))) return rc;
+    if (c.C > 0) {
+        if (!ys) { h->err = "conditional flow: ys is required"; return CNF_ERR_BADARG; }
+        if ((rc = stage_in(h, ys, c.C, B, h->d_ys, bf.Bs, io.off_ys))) return rc;
+    }
+    if (mode == CNF_MODE_TRAIN) {
+        if (!eps) { h->err = "TrainMode: eps is required"; return CNF_ERR_BADARG; }
+        if ((rc = stage_in(h, eps, c.D, B, h->d_eps, bf.Bs, io.off_eps))) return rc;
+    }
+    return CNF_OK;
+}
+
+static int check_call(cnf_handle* h, int mode, long long B) {
+    if (!h) return CNF_ERR_BADARG;
+    if (!h->have_params) { h->err = "set_params has not been called"; return CNF_ERR_BADARG; }
+    if (mode != CNF_MODE_TEST && mode != CNF_MODE_TRAIN) { h->err = "bad mode"; return CNF_ERR_BADARG; }
+    if (B < 1 || B > 0x7fffff00LL) { h->err = "bad batch size"; return CNF_ERR_BADARG; }
+    return CNF_OK;
+}
+
+static long long global_batch(cnf_handle* h, long long B, int* rc) {
+    *rc = CNF_OK;
+    if (h->nranks <= 1) return B;
+    double* d = &h->d_ctrl->initsum[3];
+    double v = (double)B;
+    cudaMemcpyAsync(d, &v, sizeof(double), cudaMemcpyHostToDevice, h->stream);
+    cudaStreamSynchronize(h->stream);
+    *rc = cnf_nccl_allreduce_f64(h, d, 1);
+    cudaMemcpyAsync(&v, d, sizeof(double), cudaMemcpyDeviceToHost, h->stream);
+    cudaStreamSynchronize(h->stream);
+    return (long long)(v + 0.5);
+}
+
+extern "C" int32_t cnfb200_augmented_f(cnf_handle* h, int32_t mode, const float* u, const float* ys,
+                                       const float* eps, int64_t B, float* du) {
+    int rc = check_call(h, mode, B);
+    if (rc) return rc;
+    if (!u || !du) { h->err = "null u/du"; return CNF_ERR_BADARG; }
+    CNF_CUDA(cudaSetDevice(h->device));
+    const cnf_config& c = h->cfg;
+    const int R = c.D + (mode == CNF_MODE_TRAIN ? 3 : 1);
+    h->cur_R = R;
+    if ((rc = ensure_workspace(h, B, R))) return rc;
+    IoPlan io = plan_io(c, B, R);
+    if ((rc = ensure_io(h, io.total + (long long)R * B))) return rc;
+    CnfBufs bf = make_bufs(h, B);
+    if ((rc = load_problem(h, bf, io, mode, R, u, R, ys, eps, B))) return rc;
+    h->path_used = 1;
+    if ((rc = launch_eval_generic(h, bf, mode, h->slots[0], h->d_K[0]))) return rc;
+    float* dout = is_device_ptr(du) ? du : h->d_io + io.total;
+    launch_unpack_rows(h, h->d_K[0], R, B, bf.Bs, dout);
+    if (dout != du)
+        CNF_CUDA(cudaMemcpyAsync(du, dout, (size_t)R * B * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    CNF_CUDA(cudaStreamSynchronize(h->stream));
+    CNF_CUDA(cudaGetLastError());
+    return CNF_OK;
+}
+
+// common body of logdensity / generate: x has rows_x rows (nvars for inference, D for generate)
+static int run_flow(cnf_handle* h, int mode, const float* x, int rows_x, const float* ys,
+                    const float* eps, long long B, float t0, float t1, float* logp, float* regs,
+                    float* z_out, int z_rows, cnf_stats* stats) {
+    int rc = check_call(h, mode, B);
+    if (rc) return rc;
+    CNF_CUDA(cudaSetDevice(h->device));
+    const cnf_config& c = h->cfg;
+    const int R = c.D + (mode == CNF_MODE_TRAIN ? 3 : 1);
+    h->cur_R = R;
+    h->launches = 0;
+    if ((rc = ensure_workspace(h, B, R))) return rc;
+    IoPlan io = plan_io(c, B, rows_x);
+    if ((rc = ensure_io(h, io.total))) return rc;
+    long long Bglobal = global_batch(h, B, &rc);
+    if (rc) return rc;
+    CnfBufs bf = make_bufs(h, B);
+    CNF_CUDA(cudaEventRecord(h->ev0, h->stream));
+    if ((rc = load_problem(h, bf, io, mode, R, x, rows_x, ys, eps, B))) return rc;
+    h->path_used = 1;
+    CnfCtrl fin;
+    if ((rc = solve_device(h, bf, mode, R, Bglobal, t0, t1, false, &fin))) return rc;
+    // epilogue writes in the caller's layout; host destinations go through the staging area
+    const int nreg = mode == CNF_MODE_TRAIN ? 3 : 1;
+    float* d_logp = logp ? (is_device_ptr(logp) ? logp : h->d_io + io.off_logp) : nullptr;
+    float* d_regs = regs ? (is_device_ptr(regs) ? regs : h->d_io + io.off_regs) : nullptr;
+    float* d_z = nullptr;
+    const bool gen = z_rows < 0;   // generate: return rows 1:(-z_rows) of the final state
+    if (gen) z_rows = -z_rows;
+    if (z_out && !gen) d_z = is_device_ptr(z_out) ? z_out : h->d_io + io.off_z;
+    CNF_CUDA(cudaMemsetAsync(h->d_lossacc, 0, sizeof(double), h->stream));
+    if (logp || regs || d_z) launch_epilogue(h, bf, mode, d_logp, d_regs, d_z, Bglobal);
+    if (z_out && gen) {
+        float* dz = is_device_ptr(z_out) ? z_out : h->d_io + io.off_z;
+        const float* fs = h->slots[fin.naccept & 1];
+        launch_unpack_rows(h, fs, z_rows, B, bf.Bs, dz);
+        if (dz != z_out)
+            CNF_CUDA(cudaMemcpyAsync(z_out, dz, (size_t)z_rows * B * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    }
+    if (logp && d_logp != logp)
+        CNF_CUDA(cudaMemcpyAsync(logp, d_logp, (size_t)B * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    if (regs && d_regs != regs)
+        CNF_CUDA(cudaMemcpyAsync(regs, d_regs, (size_t)nreg * B * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    if (d_z && d_z != z_out)
+        CNF_CUDA(cudaMemcpyAsync(z_out, d_z, (size_t)c.D * B * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    CNF_CUDA(cudaEventRecord(h->ev3, h->stream));
+    CNF_CUDA(cudaStreamSynchronize(h->stream));
+    CNF_CUDA(cudaGetLastError());
+    fill_stats(h, fin, stats);
+    return fin.retcode;
+}
+
+extern "C" int32_t cnfb200_logdensity(cnf_handle* h, int32_t mode, const float* xs, const float* ys,
+                                      const float* eps, int64_t B, float t0, float t1, float* logp,
+                                      float* regs, float* z_out, cnf_stats* stats) {
+    if (!h) return CNF_ERR_BADARG;
+    if (!xs) { h->err = "null xs"; return CNF_ERR_BADARG; }
+    return run_flow(h, mode, xs, h->cfg.nvars, ys, eps, B, t0, t1, logp, regs, z_out, h->cfg.D, stats);
+}
+
+extern "C" int32_t cnfb200_generate(cnf_handle* h, int32_t mode, const float* z0, const float* ys,
+                                    const float* eps, int64_t n, float t_from, float t_to,
+                                    float* xs_out, cnf_stats* stats) {
+    if (!h) return CNF_ERR_BADARG;
+    if (!z0 || !xs_out) { h->err = "null z0/xs_out"; return CNF_ERR_BADARG; }
+    return run_flow(h, mode, z0, h->cfg.D, ys, eps, n, t_from, t_to, nullptr, nullptr, xs_out,
+                    -h->cfg.nvars, stats);
+}
+
+// ------------------------------------------------------------------ loss + discrete adjoint
+static int ensure_bw(cnf_handle* h, long long Bs) {
+    const long long need = (long long)h->cfg.D * Bs;
+    if (need <= h->cap_bw) return CNF_OK;
+    CNF_CUDA(cudaStreamSynchronize(h->stream));
+    for (int j = 0; j < 12; ++j) {
+        cudaFree(h->d_bw[j]);
+        h->d_bw[j] = nullptr;
+        CNF_CUDA(cudaMalloc(&h->d_bw[j], (size_t)need * sizeof(float)));
+    }
+    h->cap_bw = need;
+    return CNF_OK;
+}
+
+extern "C" int32_t cnfb200_loss_grad(cnf_handle* h, const float* xs, const float* ys, const float* eps,
+                                     int64_t B, float t0, float t1, float* loss, float* grad_theta,
+                                     float* grad_x, cnf_stats* stats) {
+    const int mode = CNF_MODE_TRAIN;
+    int rc = check_call(h, mode, B);
+    if (rc) return rc;
+    if (!xs || !loss) { h->err = "null xs/loss"; return CNF_ERR_BADARG; }
+    CNF_CUDA(cudaSetDevice(h->device));
+    const cnf_config& c = h->cfg;
+    const int R = c.D + 3;
+    const bool want_grad = grad_theta || grad_x;
+    h->cur_R = R;
+    h->launches = 0;
+    if ((rc = ensure_workspace(h, B, R))) return rc;
+    IoPlan io = plan_io(c, B, c.nvars);
+    if ((rc = ensure_io(h, io.total))) return rc;
+    CnfBufs bf = make_bufs(h, B);
+    if (want_grad && (rc = ensure_bw(h, bf.Bs))) return rc;
+    long long Bglobal = global_batch(h, B, &rc);
+    if (rc) return rc;
+    CNF_CUDA(cudaEventRecord(h->ev0, h->stream));
+    if ((rc = load_problem(h, bf, io, mode, R, xs, c.nvars, ys, eps, B))) return rc;
+    h->path_used = 1;
+    CnfCtrl fin;
+    if ((rc = solve_device(h, bf, mode, R, Bglobal, t0, t1, want_grad, &fin))) return rc;
+    CNF_CUDA(cudaMemsetAsync(h->d_lossacc, 0, sizeof(double), h->stream));
+    launch_epilogue(h, bf, mode, nullptr, nullptr, nullptr, Bglobal);
+    if (h->nranks > 1 && (rc = cnf_nccl_allreduce_f64(h, h->d_lossacc, 1))) return rc;
+    double lsum = 0.0;
+    CNF_CUDA(cudaMemcpyAsync(&lsum, h->d_lossacc, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    if (want_grad) {
+        CNF_CUDA(cudaMemsetAsync(h->d_grad, 0, (size_t)h->nparams * sizeof(float), h->stream));
+        launch_init_ubar(h, bf, h->d_bw[11], Bglobal);
+        if ((rc = backward_sweep(h, bf, fin.naccept, Bglobal))) return rc;
+        if (grad_theta) {
+            if (h->nranks > 1 && (rc = cnf_nccl_allreduce_f32(h, h->d_grad, h->nparams))) return rc;
+            CNF_CUDA(cudaMemcpyAsync(grad_theta, h->d_grad, (size_t)h->nparams * sizeof(float),
+                                     cudaMemcpyDefault, h->stream));
+        }
+        if (grad_x) {
+            float* dg = is_device_ptr(grad_x) ? grad_x : h->d_io + io.off_z;
+            launch_unpack_rows(h, h->d_bw[11], c.nvars, B, bf.Bs, dg);
+            if (dg != grad_x)
+                CNF_CUDA(cudaMemcpyAsync(grad_x, dg, (size_t)c.nvars * B * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+        }
+    }
+    CNF_CUDA(cudaEventRecord(h->ev3, h->stream));
+    CNF_CUDA(cudaStreamSynchronize(h->stream));
+    CNF_CUDA(cudaGetLastError());
+    *loss = (float)(lsum / (double)Bglobal);
+    fill_stats(h, fin, stats);
+    return fin.retcode;
+}
+
+// ------------------------------------------------------------------ FP32 FFMA peak probe
+__global__ void k_ffma_peak(float* out, int iters) {
+    float a0 = threadIdx.x * 1e-3f, a1 = a0 + 1.f, a2 = a0 + 2.f, a3 = a0 + 3.f;
+    float a4 = a0 + 4.f, a5 = a0 + 5.f, a6 = a0 + 6.f, a7 = a0 + 7.f;
+    const float m = 0.999f, c = 1e-3f;
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int u = 0; u < 16; ++u) {
+            a0 = fmaf(a0, m, c); a1 = fmaf(a1, m, c); a2 = fmaf(a2, m, c); a3 = fmaf(a3, m, c);
+            a4 = fmaf(a4, m, c); a5 = fmaf(a5, m, c); a6 = fmaf(a6, m, c); a7 = fmaf(a7, m, c);
+        }
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+}
+
+extern "C" int32_t cnfb200_measure_fp32_peak(int32_t device, double* tflops_out) {
+    if (!tflops_out) return CNF_ERR_BADARG;
+    if (cudaSetDevice(device) != cudaSuccess) return CNF_ERR_CUDA;
+    const int blocks = 148 * 8, threads = 256, iters = 4096;
+    float* d = nullptr;
+    if (cudaMalloc(&d, (size_t)blocks * threads * sizeof(float)) != cudaSuccess) return CNF_ERR_OOM;
+    cudaEvent_t a, b;
+    cudaEventCreate(&a);
+    cudaEventCreate(&b);
+    double best = 0.0;
+    for (int rep = 0; rep < 5; ++rep) {
+        cudaEventRecord(a);
+        k_ffma_peak<<<blocks, threads>>>(d, iters);
+        cudaEventRecord(b);
+        cudaEventSynchronize(b);
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, a, b);
+        double fl = 2.0 * 128.0 * iters * (double)blocks * threads;
+        double tf = fl / (ms * 1e-3) / 1e12;
+        if (rep > 0 && tf > best) best = tf;
+    }
+    cudaEventDestroy(a);
+    cudaEventDestroy(b);
+    cudaFree(d);
+    *tflops_out = best;
+    return cudaGetLastError() == cudaSuccess ? CNF_OK : CNF_ERR_CUDA;
+}

@@ -1,0 +1,86 @@
+// cnf_internal.h — host-side declarations shared by the .cu files of libcnfb200.
+#pragma once
+#include "cnf_common.cuh"
+#include <string>
+#include <vector>
+
+struct cnf_handle {
+    cnf_config cfg;
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr, ev3 = nullptr, evchk[2] = {nullptr, nullptr};
+    std::string err;
+    // parameters
+    long long nparams = 0;
+    float* d_theta = nullptr;   // flat theta (layout of the caller)
+    float* d_wt = nullptr;      // transposed weight copies, layer after layer
+    float* d_grad = nullptr;    // gradient accumulator (layout of theta)
+    long long w_off[CNF_MAX_LAYERS], b_off[CNF_MAX_LAYERS], wt_off[CNF_MAX_LAYERS];
+    bool have_params = false;
+    CnfNet net;
+    // controller
+    CnfCtrl* d_ctrl = nullptr;
+    CnfCtrl* h_ctrl = nullptr;  // pinned, 2 entries
+    float* d_dts = nullptr;     // accepted dt tape (CNF_MAX_SLOTS)
+    double* d_lossacc = nullptr;
+    // workspaces (grown lazily, never shrunk)
+    long long cap_B = 0;        // samples the K/S/eps/ys buffers are sized for
+    int cap_R = 0;
+    int cur_R = 0;              // rows of the state in the current call
+    float* d_K[7] = {};
+    float* d_S = nullptr;
+    float* d_eps = nullptr;
+    float* d_ys = nullptr;
+    float* d_io = nullptr;      // staging for host<->device copies of sample-major I/O
+    long long cap_io = 0;
+    std::vector<float*> slots;  // state slots allocated so far
+    long long slot_elems = 0;
+    float** d_slots = nullptr;  // device table [CNF_MAX_SLOTS]
+    // backward workspaces
+    float* d_bw[16] = {};
+    long long cap_bw = 0;
+    // communicator (NCCL via dlopen)
+    void* nccl_comm = nullptr;
+    int nranks = 1, rank = 0;
+    long long launches = 0;
+    int path_used = 0;
+};
+
+#define CNF_CUDA(call)                                                                   \
+    do {                                                                                 \
+        cudaError_t e__ = (call);                                                        \
+        if (e__ != cudaSuccess) {                                                        \
+            h->err = std::string(#call) + ": " + cudaGetErrorString(e__);                \
+            return (e__ == cudaErrorMemoryAllocation) ? CNF_ERR_OOM : CNF_ERR_CUDA;      \
+        }                                                                                \
+    } while (0)
+
+// ---- cnf_solver.cu
+void cnf_upload_constants();
+void launch_pack_rows(cnf_handle* h, const float* src, int rows, long long B, float* dst, long long Bs);
+void launch_unpack_rows(cnf_handle* h, const float* src, int rows, long long B, long long Bs, float* dst);
+void launch_combine(cnf_handle* h, const CnfBufs& bf, int stage);   // stage 1..5 -> S, 6 -> unew, -1 -> init probe
+void launch_errnorm(cnf_handle* h, const CnfBufs& bf);
+void launch_controller(cnf_handle* h);
+void launch_initnorm(cnf_handle* h, const CnfBufs& bf, int which);
+void launch_initdt(cnf_handle* h, int phase);  // 0: dt0 from d0,d1; 1: final dt; 2: fixed dt0 begin
+void launch_epilogue(cnf_handle* h, const CnfBufs& bf, int mode, float* logp, float* regs,
+                     float* z_out, long long Bglobal);
+void launch_init_ubar(cnf_handle* h, const CnfBufs& bf, float* ubar, long long Bglobal);
+
+// ---- cnf_stage_generic.cu
+// du = augmented_f(stage input) ; src: D x Bs z rows ; kout: R x Bs
+int launch_eval_generic(cnf_handle* h, const CnfBufs& bf, int mode, const float* src, float* kout);
+// VJP of TrainMode augmented_f: cotangent (abar D x Bs, scal[3] * w) -> zbar, grads
+int launch_vjp_generic(cnf_handle* h, const CnfBufs& bf, const float* src, const float* abar,
+                       int stage, float c_l, float c_E, float c_n, const float* dtp,
+                       float* zbar, float* grad);
+
+// ---- cnf_stage_narrow.cu : register-resident one-sample-per-thread kernels
+bool narrow_supported(const cnf_config& cfg);
+// fused: stage input from (u, k1..k_{i}) -> k_{i+1}; stage 6 also writes unew + error partials
+int launch_stage_narrow(cnf_handle* h, const CnfBufs& bf, int mode, int stage);
+
+// ---- cnf_nccl.cu
+int cnf_nccl_allreduce_f64(cnf_handle* h, double* dptr, int n);
+int cnf_nccl_allreduce_f32(cnf_handle* h, float* dptr, long long n);

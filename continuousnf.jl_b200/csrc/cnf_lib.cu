@@ -1,0 +1,7 @@
+// cnf_lib.cu — single translation unit of libcnfb200.so (keeps __constant__ tables and
+// templates in one module; no relocatable device code needed).
+#include "cnf_solver.cu"
+#include "cnf_stage_generic.cu"
+#include "cnf_backward.cu"
+#include "cnf_nccl.cu"
+#include "cnf_api.cu"

@@ -23,6 +23,12 @@
 extern "C" {
 #endif
 
+#if defined(__GNUC__)
+#define CNF_API __attribute__((visibility("default")))
+#else
+#define CNF_API
+#endif
+
 #define CNF_MAX_LAYERS 8
 
 /* flags: the type-level booleans of `ICNF{...}` (src/base_icnf.jl:42-60, src/icnf.jl:69-104) */
@@ -82,28 +88,28 @@ typedef struct cnf_stats {
 
 typedef struct cnf_handle cnf_handle;
 
-const char* cnfb200_version(void);
+CNF_API const char* cnfb200_version(void);
 
 /* replaces construct(...) bookkeeping on the device side (src/base_icnf.jl:1-77) */
-int32_t cnfb200_create(const cnf_config* cfg, cnf_handle** out);
-int32_t cnfb200_destroy(cnf_handle* h);
-const char* cnfb200_last_error(const cnf_handle* h);
+CNF_API int32_t cnfb200_create(const cnf_config* cfg, cnf_handle** out);
+CNF_API int32_t cnfb200_destroy(cnf_handle* h);
+CNF_API const char* cnfb200_last_error(const cnf_handle* h);
 
 /* flat ComponentArray parameter vector `ps` + per-layer weight/bias offsets (in floats);
  * weight l is d_{l+1} x d_l column-major (Lux Dense; src/exts/mlj_ext/core_icnf.jl:37-38) */
-int32_t cnfb200_set_params(cnf_handle* h, const float* theta, int64_t n,
+CNF_API int32_t cnfb200_set_params(cnf_handle* h, const float* theta, int64_t n,
                            const int64_t* w_off, const int64_t* b_off);
 
 /* batch sharding over one-process-per-GPU ranks: rank 0 makes an id, every rank inits.
  * Afterwards every solve allreduces the scalar error-norm partials each attempted step
  * (whole-batch RMS semantics of the matrix-valued ODE state, src/base_icnf.jl:280-285)
  * and cnfb200_loss_grad allreduces loss and gradient.  B_global = sum of local B. */
-int32_t cnfb200_comm_unique_id(char id_out[128]);
-int32_t cnfb200_comm_init(cnf_handle* h, int32_t nranks, int32_t rank, const char id[128]);
+CNF_API int32_t cnfb200_comm_unique_id(char id_out[128]);
+CNF_API int32_t cnfb200_comm_init(cnf_handle* h, int32_t nranks, int32_t rank, const char id[128]);
 
 /* one evaluation du = augmented_f(u, p, t, icnf, mode, nn, st, eps)
  * (src/icnf.jl:148-164 Test; :318-350 Train/VecJac; :384-420 Train/JacVec).  u, du: R x B. */
-int32_t cnfb200_augmented_f(cnf_handle* h, int32_t mode, const float* u, const float* ys,
+CNF_API int32_t cnfb200_augmented_f(cnf_handle* h, int32_t mode, const float* u, const float* ys,
                             const float* eps, int64_t B, float* du);
 
 /* replaces inference(icnf, mode, xs[, ys], ps, st) = inference_prob + inference_sol
@@ -111,7 +117,7 @@ int32_t cnfb200_augmented_f(cnf_handle* h, int32_t mode, const float* u, const f
  * eps: D x B (may be NULL in TestMode, where it is unused);
  * logp: B; regs: 3 x B rows (E, n, A) in TrainMode, 1 x B (A) in TestMode, or NULL;
  * z_out: D x B final latent state or NULL. */
-int32_t cnfb200_logdensity(cnf_handle* h, int32_t mode, const float* xs, const float* ys,
+CNF_API int32_t cnfb200_logdensity(cnf_handle* h, int32_t mode, const float* xs, const float* ys,
                            const float* eps, int64_t B, float t0, float t1,
                            float* logp, float* regs, float* z_out, cnf_stats* stats);
 
@@ -119,20 +125,20 @@ int32_t cnfb200_logdensity(cnf_handle* h, int32_t mode, const float* xs, const f
  * w.r.t. ps / xs (call sites src/exts/mlj_ext/core_icnf.jl:59-63, test/call_tests.jl:239-251)
  * by a discretise-then-optimise reverse sweep.  grad_theta: n floats (layout of theta) or NULL;
  * grad_x: nvars x B or NULL.  With a communicator, loss and grad_theta are global means/sums. */
-int32_t cnfb200_loss_grad(cnf_handle* h, const float* xs, const float* ys, const float* eps,
+CNF_API int32_t cnfb200_loss_grad(cnf_handle* h, const float* xs, const float* ys, const float* eps,
                           int64_t B, float t0, float t1, float* loss, float* grad_theta,
                           float* grad_x, cnf_stats* stats);
 
 /* replaces generate(...) = generate_prob + generate_sol (src/base_icnf.jl:358-405, 202-211,
  * 447-466): integrates z0 (D x n, drawn by the caller from basedist) from t_from to t_to
  * and returns rows 1:nvars.  xs_out: nvars x n. */
-int32_t cnfb200_generate(cnf_handle* h, int32_t mode, const float* z0, const float* ys,
+CNF_API int32_t cnfb200_generate(cnf_handle* h, int32_t mode, const float* z0, const float* ys,
                          const float* eps, int64_t n, float t_from, float t_to,
                          float* xs_out, cnf_stats* stats);
 
 /* measurement helper (bench only): sustained FP32 FFMA rate of this GPU in TFLOP/s,
  * the roofline denominator MEASURED_PEAKS.json does not provide. */
-int32_t cnfb200_measure_fp32_peak(int32_t device, double* tflops_out);
+CNF_API int32_t cnfb200_measure_fp32_peak(int32_t device, double* tflops_out);
 
 #ifdef __cplusplus
 }

@@ -26,7 +26,11 @@
 #define TS 16 /* samples per tile: inner loops vectorise over it */
 
 /* NNlib.tanh_fast for Float32; Lux uses it for Dense(tanh) on the CPU */
+static int g_perturb = 0;
+void cnf_oracle_set_perturb(int on) { g_perturb = on; }
+
 static inline float tanh_fast(float x) {
+    if (g_perturb) return tanhf(x);
     float x2 = x * x;
     float n = fmaf(x2, fmaf(x2, fmaf(x2, fmaf(x2, CNF_TANH_N4, CNF_TANH_N3), CNF_TANH_N2), CNF_TANH_N1), 1.0f);
     float d = fmaf(x2, fmaf(x2, fmaf(x2, fmaf(x2, CNF_TANH_D4, CNF_TANH_D3), CNF_TANH_D2), CNF_TANH_D1), 1.0f);
@@ -134,7 +138,7 @@ static void vjp_chain(const omodel* m, oscratch* sc, const float* seed) {
         int d = m->cfg.dims[L];
         const float* h = sc->h[L];
         float* g = sc->g[L];
-        for (int k = 0; k < d * TS; ++k) g[k] = seed[k] * (1.0f - h[k] * h[k]);
+        for (int k = 0; k < d * TS; ++k) g[k] = seed[k] * fmaf(-h[k], h[k], 1.0f);
     }
     for (int l = L; l >= 1; --l) {
         int din = m->cfg.dims[l - 1], dout = m->cfg.dims[l];
@@ -144,7 +148,7 @@ static void vjp_chain(const omodel* m, oscratch* sc, const float* seed) {
             const float* h = sc->h[l - 1];
             const float* q = sc->q[l];
             float* g = sc->g[l - 1];
-            for (int k = 0; k < din * TS; ++k) g[k] = q[k] * (1.0f - h[k] * h[k]);
+            for (int k = 0; k < din * TS; ++k) g[k] = q[k] * fmaf(-h[k], h[k], 1.0f);
         }
     }
 }
@@ -160,7 +164,7 @@ static void jvp_chain(const omodel* m, oscratch* sc, const float* seed) {
         const float* h = sc->h[l];
         const float* r = sc->q[l];
         float* t = sc->g[l];
-        for (int k = 0; k < dout * TS; ++k) t[k] = r[k] * (1.0f - h[k] * h[k]);
+        for (int k = 0; k < dout * TS; ++k) t[k] = r[k] * fmaf(-h[k], h[k], 1.0f);
         in = sc->g[l];
     }
 }
@@ -637,7 +641,7 @@ static void rhs_vjp_tile(const omodel* m, oscratch* sc, obscratch* bs, const flo
             if (l < L) {
                 for (int k = 0; k < dout * TS; ++k) {
                     bs->db[l][k] = bs->gb[l][k] * sc->q[l + 1][k];
-                    bs->qb[k] = bs->gb[l][k] * (1.0f - hl[k] * hl[k]);
+                    bs->qb[k] = bs->gb[l][k] * fmaf(-hl[k], hl[k], 1.0f);
                 }
                 /* next qb must not alias this layer's output: ping-pong through hb2 */
                 memcpy(bs->hb2, bs->qb, sizeof(float) * (size_t)dout * TS);
@@ -657,7 +661,7 @@ static void rhs_vjp_tile(const omodel* m, oscratch* sc, obscratch* bs, const flo
             const float* hl = sc->h[l];
             float* rb = bs->gb[l];
             for (int k = 0; k < dout * TS; ++k) {
-                rb[k] = taub[k] * (1.0f - hl[k] * hl[k]);
+                rb[k] = taub[k] * fmaf(-hl[k], hl[k], 1.0f);
                 bs->db[l][k] = taub[k] * sc->q[l][k];
             }
             outer_acc(gth + m->w_off[l - 1], dout, used, rb, (l == 1) ? e : sc->g[l - 1]);
@@ -672,7 +676,7 @@ static void rhs_vjp_tile(const omodel* m, oscratch* sc, obscratch* bs, const flo
         const float* hl = sc->h[l];
         for (int k = 0; k < dout * TS; ++k) {
             float hbk = fmaf(-2.0f * hl[k], bs->db[l][k], hb[k]);
-            bs->pb[k] = hbk * (1.0f - hl[k] * hl[k]);
+            bs->pb[k] = hbk * fmaf(-hl[k], hl[k], 1.0f);
         }
         outer_acc(gth + m->w_off[l - 1], dout, din, bs->pb, sc->h[l - 1]);
         for (int o = 0; o < dout; ++o) {

