@@ -1,0 +1,313 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the B200-native augmented-dynamics solve.
+
+  python bench.py --gpus N --steps K --warmup W [--config C2] [--impl reference]
+
+A "step" is one pass of the hot path over one batch of synthetic input: one
+`inference(icnf, TestMode(), xs, ps, st)` call (log-density configs) or one loss+gradient call
+(training configs) on the config's batch.  N=1 workload: C2 = BASELINE.json configs[1]
+(ICNF exact trace, DIJacVecMatrixMode, MLP 2->64->64->2, B = 2^20).  N>1: weak scaling, every
+rank solves its own shard of B columns; the step-size controller sees the whole batch through a
+per-step NCCL allreduce of the error-norm partials.
+
+Prints ONE JSON line (rank 0).  `value` = device-resident inputs, CUDA-event time of the calls
+(max over ranks); `e2e` = the same call with HOST buffers (pinned), host<->device copies inside the
+timed region; `roofline` = the RK stage kernel against the measured FP32-FMA peak; `cpu_baseline`
+= the CPU oracle (port of the reference's CPU path) on a bounded sample on this box's cores.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = {"test": ("logdensity_samples_per_s", "samples/s"),
+          "train": ("rnode_train_samples_per_s", "samples/s")}
+
+
+def parse():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=10)
+    p.add_argument("--warmup", type=int, default=3)
+    p.add_argument("--config", default="C2")
+    p.add_argument("--batch", type=int, default=0, help="override the per-GPU batch (debug)")
+    p.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    p.add_argument("--kernel-path", type=int, default=0)
+    p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--cpu-sample", type=int, default=0)
+    return p.parse_args()
+
+
+class ClockSampler:
+    """samples nvidia-smi clocks / throttle reasons during the timed region"""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+                for n, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except (ValueError, IndexError):
+                pass
+        busy = [x for x in sm if x > 0.5 * max(mx)] if mx else sm
+        return {"sm_mhz": float(np.median(busy or sm)) if sm else None,
+                "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def make_model(cnf, cid, device, kernel_path):
+    c = cnf.workloads.CONFIGS[cid]
+    dims = c["dims"]
+    nn = cnf.Chain(*[cnf.Dense(dims[i], dims[i + 1], "tanh") for i in range(len(dims) - 1)])
+    cm = cnf.DIJacVecMatrixMode() if c["trace_mode"] == 1 else cnf.DIVecJacMatrixMode()
+    tag = {"RNODE": cnf.RNODE, "ICNF": cnf.FFJORD, "CondRNODE": cnf.CondRNODE}[c["tag"]]
+    sk = {k: c[k] for k in ("reltol", "abstol") if c[k]}
+    return cnf.construct(tag, nn, c["nvars"], c["naug"], compute_mode=cm, tspan=c["tspan"],
+                         sol_kwargs=sk, lambda1=c["lambda1"], lambda2=c["lambda2"],
+                         lambda3=c["lambda3"], resource=cnf.B200Libs(device, kernel_path),
+                         rng=np.random.default_rng(0))
+
+
+def oracle_step(O, cfg, c, inp, train):
+    if train:
+        _, _, _, st = O.loss_grad(cfg, inp["theta"], inp["xs"], inp["ys"], inp["eps"], *c["tspan"])
+    else:
+        _, _, _, st = O.logdensity(cfg, inp["theta"], 0, inp["xs"], inp["ys"], None, *c["tspan"])
+    return st
+
+
+def oracle_config(O, c):
+    return O.make_config(c["nvars"], c["naug"], c["dims"], C_=c["C"], trace_mode=c["trace_mode"],
+                         lambda1=c["lambda1"], lambda2=c["lambda2"], lambda3=c["lambda3"],
+                         reltol=c["reltol"], abstol=c["abstol"])
+
+
+def cpu_sample_size(cid, override):
+    if override:
+        return override
+    return {"C0": 64, "C1": 1024, "C2": 1 << 16, "C3": 1 << 11, "C4": 1 << 14, "C5": 1 << 7}[cid]
+
+
+def run_reference(args, cnf):
+    """--impl reference: the reference's CPU implementation of the path.  Julia is absent, so this
+    is the CPU oracle (a port), all host threads, each step a bounded sample of the workload."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import oracle as O
+    wl = cnf.workloads
+    cid = args.config
+    c = wl.CONFIGS[cid]
+    train = c["mode"] == "train"
+    Bs = cpu_sample_size(cid, args.cpu_sample)
+    inp = wl.make_inputs(cid, B=Bs)
+    cfg = oracle_config(O, c)
+    for _ in range(args.warmup):
+        oracle_step(O, cfg, c, inp, train)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        st = oracle_step(O, cfg, c, inp, train)
+    dt = time.perf_counter() - t0
+    val = Bs * args.steps / dt
+    metric, unit = METRIC[c["mode"]]
+    line = {
+        "impl": "reference", "metric": metric, "value": val, "unit": unit, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": f"{cid}: {c['tag']} dims={c['dims']} B={c['B']} mode={c['mode']}",
+                   "sample_per_step": Bs, "naccept": st["naccept"], "nreject": st["nreject"]},
+        "cpu_baseline": {"value": val, "unit": unit, "cores": O.num_threads(), "kind": "port",
+                         "sample": f"{Bs} samples per step of the {c['B']}-sample workload "
+                                   "(CPU throughput is linear in the batch)"},
+        "e2e": {"value": val, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse()
+    import cnfb200_loader
+    cnf = cnfb200_loader.load_package()
+    if args.impl == "reference":
+        return run_reference(args, cnf)
+    import torch
+    import torch.distributed as dist
+    wl = cnf.workloads
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    cid = args.config
+    c = wl.CONFIGS[cid]
+    train = c["mode"] == "train"
+    B = args.batch or c["B"]
+    D = c["nvars"] + c["naug"]
+    inp = wl.make_inputs(cid, B=B, offset=rank)
+    icnf = make_model(cnf, cid, local, args.kernel_path)
+    if world > 1:
+        cnf.parallel.init_comm(icnf, rank, world)
+    cnf.set_option(icnf, "time_stages", 1)
+    mode = cnf.TrainMode() if train else cnf.TestMode()
+    dev = torch.device("cuda", local)
+    # device-resident inputs (value) and pinned host inputs (e2e); `rows x B` views, Julia-style
+    xs_d = torch.from_numpy(inp["xs"]).to(dev).t()
+    ys_d = torch.from_numpy(inp["ys"]).to(dev).t() if inp["ys"] is not None else None
+    eps_d = torch.from_numpy(inp["eps"]).to(dev).t()
+    pin = lambda a: torch.from_numpy(a).pin_memory().numpy().T
+    xs_h = pin(inp["xs"])
+    ys_h = pin(inp["ys"]) if inp["ys"] is not None else None
+    eps_h = pin(inp["eps"])
+    theta = inp["theta"]
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    def step(xs, ys, eps):
+        tail = ((ys,) if ys is not None else ()) + (theta, {})
+        if train:
+            out = cnf.loss_and_grad(icnf, mode, xs, *tail, eps=eps)
+        else:
+            out = cnf.inference(icnf, mode, xs, *tail)
+        return out, cnf.last_stats(icnf)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step(xs_d, ys_d, eps_d)
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    ms_dev = ms_stage = 0.0
+    n_stage = launches = 0
+    t_wall = time.perf_counter()
+    for _ in range(args.steps):
+        flush.zero_()
+        torch.cuda.synchronize()
+        _, st = step(xs_d, ys_d, eps_d)
+        ms_dev += st["ms_total"]
+        ms_stage += st["ms_stage"]
+        n_stage += st["n_stage"]
+        launches += st["gpu_launches"]
+    barrier()
+    wall = time.perf_counter() - t_wall
+    # end-to-end: same call, HOST buffers; H2D of the inputs and D2H of the result inside the call
+    for _ in range(min(args.warmup, 2)):
+        step(xs_h, ys_h, eps_h)
+    barrier()
+    t_e2e = time.perf_counter()
+    for _ in range(args.steps):
+        out_h, st_h = step(xs_h, ys_h, eps_h)
+    barrier()
+    e2e_s = time.perf_counter() - t_e2e
+    clocks = sampler.stop()
+    if world > 1:
+        t = torch.tensor([ms_dev, e2e_s], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_dev, e2e_s = float(t[0]), float(t[1])
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    metric, unit = METRIC[c["mode"]]
+    total = B * world * args.steps
+    value = total / (ms_dev * 1e-3)
+    h2d = inp["xs"].nbytes + (inp["ys"].nbytes if inp["ys"] is not None else 0) + \
+        (inp["eps"].nbytes if train else 0) + theta.nbytes
+    d2h = (theta.nbytes + 4) if train else (B * 4 + B * 4)
+    # roofline of the dominant kernel: one RK stage kernel = one augmented_f evaluation of B samples
+    flops_eval = wl.flops_per_eval(cid) * B
+    lib = cnf._cabi.load()
+    import ctypes
+    pk = ctypes.c_double(0.0)
+    lib.cnfb200_measure_fp32_peak(local, ctypes.byref(pk))
+    stage_ms = ms_stage / max(n_stage, 1)
+    achieved = flops_eval / (stage_ms * 1e-3) / 1e12 if stage_ms > 0 else 0.0
+    roofline = {"bound": "fp32_fma", "achieved": achieved, "peak": pk.value, "unit": "TFLOP/s",
+                "frac": achieved / pk.value if pk.value else None, "traffic": None,
+                "kernel": "RK stage kernel (augmented_f over the whole batch)",
+                "peak_source": "measured in this run by cnfb200_measure_fp32_peak (dependent-FFMA "
+                               "microbenchmark); MEASURED_PEAKS.json has no FP32 figure",
+                "stage_ms": stage_ms, "stage_launches": n_stage, "kernel_path": st["kernel_path"],
+                "stage_share_of_step": ms_stage / ms_dev if ms_dev else None}
+    line = {
+        "metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{cid}: {c['tag']} dims={c['dims']} B={B}/GPU mode={c['mode']} "
+                               f"trace={'JVP' if c['trace_mode'] else 'VJP'} tspan={c['tspan']}",
+                   "global_batch": B * world, "parallelism": f"dp{world} (columns sharded)",
+                   "l2": "256 MB flush between timed steps", "naccept": st["naccept"],
+                   "nreject": st["nreject"], "nf": st["nf"], "timing": "sum of per-call CUDA-event "
+                   "times on the library stream, max over ranks", "wall_ms_per_step_incl_flush":
+                   1e3 * wall / args.steps},
+        "clocks": clocks,
+        "e2e": {"value": total / e2e_s, "unit": unit, "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": d2h, "ms_per_step": 1e3 * e2e_s / args.steps},
+        "gpu_launches": launches,
+        "roofline": roofline,
+    }
+    if not args.no_cpu_baseline and world == 1:
+        from oracle import oracle as O
+        Bs = cpu_sample_size(cid, args.cpu_sample)
+        sinp = wl.make_inputs(cid, B=Bs)
+        cfg = oracle_config(O, c)
+        oracle_step(O, cfg, c, sinp, train)
+        t0 = time.perf_counter()
+        reps = 0
+        while reps < 3 and time.perf_counter() - t0 < 20:
+            oracle_step(O, cfg, c, sinp, train)
+            reps += 1
+        dt = (time.perf_counter() - t0) / reps
+        line["cpu_baseline"] = {"value": Bs / dt, "unit": unit, "cores": O.num_threads(), "kind": "port",
+                                "sample": f"{Bs} of {B} samples, {reps} repetitions, same synthetic stream"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -4,10 +4,10 @@ ContinuousNormalizingFlows.jl behind the reference's own operator interface.
 The directory name contains a dot, so import it through `cnfb200_loader.load_package()` (repo
 root) or importlib; the module registers itself as `cnfb200`.
 """
-from . import _cabi, workloads  # noqa: F401
+from . import _cabi, parallel, workloads  # noqa: F401
 from .api import (  # noqa: F401
     B200Libs, Chain, CondFFJORD, CondRNODE, Dense, DIJacVecMatrixMode, DIJacVecVectorMode,
     DIVecJacMatrixMode, DIVecJacVectorMode, FFJORD, ICNF, RNODE, TestMode, TrainMode, augmented_f,
-    construct, generate, inference, last_stats, loss, loss_and_grad, param_offsets, setup,
+    construct, generate, inference, last_stats, loss, loss_and_grad, param_offsets, set_option, setup,
     steer_tspan,
 )

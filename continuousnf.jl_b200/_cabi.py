@@ -14,7 +14,7 @@ FLAG_COND, FLAG_AUGMENTED, FLAG_NORM_Z, FLAG_NORM_J, FLAG_NORM_Z_AUG = 1, 2, 4, 
 RETCODES = {0: "Success", 1: "MaxIters", 2: "DtLessThanMin", 3: "Unstable"}
 
 EXPORTS = [
-    "cnfb200_version", "cnfb200_create", "cnfb200_destroy", "cnfb200_last_error",
+    "cnfb200_version", "cnfb200_create", "cnfb200_destroy", "cnfb200_set_option", "cnfb200_last_error",
     "cnfb200_set_params", "cnfb200_comm_unique_id", "cnfb200_comm_init", "cnfb200_augmented_f",
     "cnfb200_logdensity", "cnfb200_loss_grad", "cnfb200_generate", "cnfb200_measure_fp32_peak",
 ]
@@ -37,6 +37,7 @@ class CnfStats(C.Structure):
         ("retcode", C.c_int32), ("kernel_path", C.c_int32),
         ("t_final", C.c_float), ("dt_last", C.c_float),
         ("ms_total", C.c_double), ("ms_solve", C.c_double), ("gpu_launches", C.c_int64),
+        ("ms_stage", C.c_double), ("n_stage", C.c_int64),
     ]
 
     def as_dict(self):
@@ -66,6 +67,7 @@ def load():
     lib.cnfb200_last_error.argtypes = [C.c_void_p]
     lib.cnfb200_create.argtypes = [C.POINTER(CnfConfig), C.POINTER(C.c_void_p)]
     lib.cnfb200_destroy.argtypes = [C.c_void_p]
+    lib.cnfb200_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_int64]
     lib.cnfb200_set_params.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, _I64P, _I64P]
     lib.cnfb200_comm_unique_id.argtypes = [C.c_char_p]
     lib.cnfb200_comm_init.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_char_p]

@@ -435,5 +435,10 @@ def augmented_f(icnf, mode, u, *args, eps=None):
     return _rows_view(du)
 
 
+def set_option(icnf, key, value):
+    """runtime options of the handle: 'time_stages', 'kernel_path'"""
+    icnf._check(_cabi.load().cnfb200_set_option(icnf.handle(), key.encode(), int(value)), "cnfb200_set_option")
+
+
 def last_stats(icnf):
     return icnf._last_stats

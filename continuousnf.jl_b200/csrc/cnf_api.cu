@@ -96,6 +96,7 @@ extern "C" int32_t cnfb200_destroy(cnf_handle* h) {
     cudaFree(h->d_theta); cudaFree(h->d_wt); cudaFree(h->d_grad);
     cudaFree(h->d_ctrl); cudaFree(h->d_dts); cudaFree(h->d_lossacc); cudaFree(h->d_slots);
     if (h->h_ctrl) cudaFreeHost(h->h_ctrl);
+    for (cudaEvent_t e : h->stage_ev) cudaEventDestroy(e);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
     if (h->ev2) cudaEventDestroy(h->ev2);
@@ -163,6 +164,39 @@ extern "C" int32_t cnfb200_set_params(cnf_handle* h, const float* theta, int64_t
     CNF_CUDA(cudaStreamSynchronize(h->stream));  // theta may be a pageable host buffer
     h->have_params = true;
     return CNF_OK;
+}
+
+void stage_timer_begin(cnf_handle* h) {
+    if (!h->time_stages) return;
+    if (h->stage_ev_used + 2 > h->stage_ev.size()) {
+        for (int i = 0; i < 64; ++i) { cudaEvent_t e; cudaEventCreate(&e); h->stage_ev.push_back(e); }
+    }
+    cudaEventRecord(h->stage_ev[h->stage_ev_used++], h->stream);
+}
+void stage_timer_end(cnf_handle* h) {
+    if (!h->time_stages) return;
+    cudaEventRecord(h->stage_ev[h->stage_ev_used++], h->stream);
+}
+static void stage_timer_collect(cnf_handle* h) {
+    h->ms_stage = 0.0;
+    h->n_stage = 0;
+    for (size_t i = 0; i + 1 < h->stage_ev_used; i += 2) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, h->stage_ev[i], h->stage_ev[i + 1]) == cudaSuccess) {
+            h->ms_stage += ms;
+            h->n_stage++;
+        }
+    }
+    h->stage_ev_used = 0;
+    cudaGetLastError();
+}
+
+extern "C" int32_t cnfb200_set_option(cnf_handle* h, const char* key, int64_t value) {
+    if (!h || !key) return CNF_ERR_BADARG;
+    if (!strcmp(key, "time_stages")) { h->time_stages = value != 0; return CNF_OK; }
+    if (!strcmp(key, "kernel_path")) { h->cfg.kernel_path = (int32_t)value; return CNF_OK; }
+    h->err = std::string("unknown option ") + key;
+    return CNF_ERR_BADARG;
 }
 
 // ------------------------------------------------------------------ workspaces
@@ -235,7 +269,10 @@ static CnfBufs make_bufs(cnf_handle* h, long long B) {
 
 // ------------------------------------------------------------------ the solve (device-driven)
 static int eval_stage(cnf_handle* h, const CnfBufs& bf, int mode, int src_sel, int kidx, int check_done) {
-    return launch_eval_generic_sel(h, bf, mode, src_sel, nullptr, kidx, nullptr, check_done);
+    stage_timer_begin(h);
+    int rc = launch_eval_generic_sel(h, bf, mode, src_sel, nullptr, kidx, nullptr, check_done);
+    stage_timer_end(h);
+    return rc;
 }
 
 static int enqueue_attempt(cnf_handle* h, const CnfBufs& bf, int mode) {
@@ -330,6 +367,9 @@ static void fill_stats(cnf_handle* h, const CnfCtrl& c, cnf_stats* st) {
     if (cudaEventElapsedTime(&ms, h->ev1, h->ev2) == cudaSuccess) st->ms_solve = ms;
     cudaGetLastError();
     st->gpu_launches = h->launches;
+    stage_timer_collect(h);
+    st->ms_stage = h->ms_stage;
+    st->n_stage = h->n_stage;
 }
 
 // ------------------------------------------------------------------ shared front/back ends

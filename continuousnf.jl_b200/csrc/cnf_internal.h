@@ -43,6 +43,12 @@ struct cnf_handle {
     void* nccl_comm = nullptr;
     int nranks = 1, rank = 0;
     long long launches = 0;
+    // optional per-stage-kernel timing (cnfb200_set_option "time_stages")
+    bool time_stages = false;
+    std::vector<cudaEvent_t> stage_ev;
+    size_t stage_ev_used = 0;
+    double ms_stage = 0.0;
+    long long n_stage = 0;
     int path_used = 0;
 };
 
@@ -54,6 +60,10 @@ struct cnf_handle {
             return (e__ == cudaErrorMemoryAllocation) ? CNF_ERR_OOM : CNF_ERR_CUDA;      \
         }                                                                                \
     } while (0)
+
+// ---- stage timing helpers (cnf_api.cu)
+void stage_timer_begin(cnf_handle* h);
+void stage_timer_end(cnf_handle* h);
 
 // ---- cnf_solver.cu
 void cnf_upload_constants();

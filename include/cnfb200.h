@@ -84,6 +84,8 @@ typedef struct cnf_stats {
     double ms_total;              /* device time of the whole call (CUDA events) */
     double ms_solve;              /* device time of the RK loop only */
     int64_t gpu_launches;         /* kernels launched by this call */
+    double ms_stage;              /* summed device time of the RK stage kernels (option time_stages) */
+    int64_t n_stage;              /* number of stage-kernel launches timed */
 } cnf_stats;
 
 typedef struct cnf_handle cnf_handle;
@@ -93,6 +95,9 @@ CNF_API const char* cnfb200_version(void);
 /* replaces construct(...) bookkeeping on the device side (src/base_icnf.jl:1-77) */
 CNF_API int32_t cnfb200_create(const cnf_config* cfg, cnf_handle** out);
 CNF_API int32_t cnfb200_destroy(cnf_handle* h);
+/* runtime options: "time_stages" (0/1: CUDA-event timing of every stage kernel -> cnf_stats.ms_stage),
+ * "kernel_path" (0 auto, 1 generic, 2 narrow, 3 tcgen05) */
+CNF_API int32_t cnfb200_set_option(cnf_handle* h, const char* key, int64_t value);
 CNF_API const char* cnfb200_last_error(const cnf_handle* h);
 
 /* flat ComponentArray parameter vector `ps` + per-layer weight/bias offsets (in floats);

@@ -89,6 +89,21 @@ static void oscratch_free(oscratch* s) { free(s->store); }
 /* out[o][:] = (bias ? b[o] : 0) + sum_{i<din_used} W[o,i] * in[i][:]   (W: dout x din col-major) */
 static void dense_mul(const float* W, const float* b, int dout, int din_used,
                       const float* in, float* out) {
+    /* accumulation order per output: bias, then ascending i (same in both branches) */
+    if ((long)dout * din_used <= 65536) { /* small layer: accumulators stay in registers */
+        for (int o = 0; o < dout; ++o) {
+            float acc[TS];
+            float bv = b ? b[o] : 0.0f;
+            for (int s = 0; s < TS; ++s) acc[s] = bv;
+            for (int i = 0; i < din_used; ++i) {
+                float w = W[(size_t)i * dout + o];
+                const float* x = in + i * TS;
+                for (int s = 0; s < TS; ++s) acc[s] = fmaf(w, x[s], acc[s]);
+            }
+            for (int s = 0; s < TS; ++s) out[o * TS + s] = acc[s];
+        }
+        return;
+    }
     for (int o = 0; o < dout; ++o) {
         float bv = b ? b[o] : 0.0f;
         for (int s = 0; s < TS; ++s) out[o * TS + s] = bv;

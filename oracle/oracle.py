@@ -39,6 +39,7 @@ class Stats(C.Structure):
         ("retcode", C.c_int32), ("kernel_path", C.c_int32),
         ("t_final", C.c_float), ("dt_last", C.c_float),
         ("ms_total", C.c_double), ("ms_solve", C.c_double), ("gpu_launches", C.c_int64),
+        ("ms_stage", C.c_double), ("n_stage", C.c_int64),
     ]
 
     def as_dict(self):

@@ -89,7 +89,7 @@ def solve(rhs, u, t0, t1, reltol=1e-3, abstol=1e-6, maxiters=100000, frozen_dts=
             u = u + dt * sum(a * kk for a, kk in zip(A[6], k))
         return u, dict(naccept=len(frozen_dts), nreject=0)
     N = u.numel()
-    rms = lambda x: float(torch.sqrt((x * x).sum() / N))
+    rms = lambda x: float(torch.sqrt((x.detach() * x.detach()).sum() / N))
     dtmax = abs(t1 - t0)
     k1 = rhs(u)
     sk = abstol + u.abs() * reltol
@@ -171,7 +171,7 @@ def run(cfg, theta, mode, xs, ys=None, eps=None, t0=0.0, t1=1.0, frozen_dts=None
         regs = Aa[:, None]
         loss = (-logp).mean()
     out["regs"] = regs.detach().numpy()
-    out["loss"] = float(loss)
+    out["loss"] = float(loss.detach())
     if requires_grad:
         gth, gx = torch.autograd.grad(loss, [th, x])
         out["grad_theta"], out["grad_x"] = gth.numpy(), gx.numpy()
