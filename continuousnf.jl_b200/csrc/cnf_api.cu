@@ -92,6 +92,7 @@ extern "C" int32_t cnfb200_destroy(cnf_handle* h) {
         cudaStreamSynchronize(h->stream);
     }
     free_workspaces(h);
+    narrow_free(h);
     cudaFree(h->d_io);
     cudaFree(h->d_theta); cudaFree(h->d_wt); cudaFree(h->d_grad);
     cudaFree(h->d_ctrl); cudaFree(h->d_dts); cudaFree(h->d_lossacc); cudaFree(h->d_slots);
@@ -162,6 +163,11 @@ extern "C" int32_t cnfb200_set_params(cnf_handle* h, const float* theta, int64_t
     }
     CNF_CUDA(cudaGetLastError());
     CNF_CUDA(cudaStreamSynchronize(h->stream));  // theta may be a pageable host buffer
+    if (narrow_supported(c, CNF_MODE_TEST)) {
+        std::vector<float> th((size_t)n);
+        CNF_CUDA(cudaMemcpy(th.data(), h->d_theta, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost));
+        narrow_set_params(h, th.data());
+    }
     h->have_params = true;
     return CNF_OK;
 }
@@ -215,7 +221,7 @@ static int ensure_slots(cnf_handle* h, size_t want) {
 }
 
 static int ensure_workspace(cnf_handle* h, long long B, int R) {
-    long long Bs = round_up(B, 128);
+    long long Bs = round_up(B, 256);
     if (Bs <= h->cap_B && R <= h->cap_R) return CNF_OK;
     CNF_CUDA(cudaStreamSynchronize(h->stream));
     long long capB = Bs > h->cap_B ? Bs : h->cap_B;
@@ -262,12 +268,24 @@ static CnfBufs make_bufs(cnf_handle* h, long long B) {
     bf.S = h->d_S;
     bf.eps = h->d_eps;
     bf.ys = h->d_ys;
-    bf.Bs = round_up(B, 128);
+    bf.Bs = round_up(B, 256);
     bf.B = (int)B;
     return bf;
 }
 
 // ------------------------------------------------------------------ the solve (device-driven)
+static bool use_narrow(cnf_handle* h, int mode) {
+    if (h->cfg.kernel_path == 1) return false;
+    return narrow_supported(h->cfg, mode) && h->narrow_w != nullptr;
+}
+
+static int narrow_stage(cnf_handle* h, const CnfBufs& bf, int stage, int check_done) {
+    stage_timer_begin(h);
+    int rc = launch_stage_narrow(h, bf, stage, check_done);
+    stage_timer_end(h);
+    return rc;
+}
+
 static int eval_stage(cnf_handle* h, const CnfBufs& bf, int mode, int src_sel, int kidx, int check_done) {
     stage_timer_begin(h);
     int rc = launch_eval_generic_sel(h, bf, mode, src_sel, nullptr, kidx, nullptr, check_done);
@@ -277,6 +295,13 @@ static int eval_stage(cnf_handle* h, const CnfBufs& bf, int mode, int src_sel, i
 
 static int enqueue_attempt(cnf_handle* h, const CnfBufs& bf, int mode) {
     int rc;
+    if (use_narrow(h, mode)) {   // fused path: 6 stage launches (the 7th stage carries the error norm)
+        for (int i = 1; i <= 6; ++i)
+            if ((rc = narrow_stage(h, bf, i, 1))) return rc;
+        if (h->nranks > 1 && (rc = cnf_nccl_allreduce_f64(h, &h->d_ctrl->errsum, 1))) return rc;
+        launch_controller(h);
+        return CNF_OK;
+    }
     for (int i = 1; i <= 5; ++i) {
         launch_combine(h, bf, i);
         if ((rc = eval_stage(h, bf, mode, 0 /*SRC_S*/, i, 1))) return rc;
@@ -314,15 +339,23 @@ static int solve_device(cnf_handle* h, const CnfBufs& bf, int mode, int R, long 
     CNF_CUDA(cudaMemcpyAsync(h->d_ctrl, &h->h_ctrl[0], sizeof(CnfCtrl), cudaMemcpyHostToDevice, h->stream));
     CNF_CUDA(cudaEventRecord(h->ev1, h->stream));
     int rc;
-    if ((rc = eval_stage(h, bf, mode, 2 /*SRC_SLOT0*/, 0, 0))) return rc;   // k1 = f(u0)
+    const bool nar = use_narrow(h, mode);
+    h->path_used = nar ? 2 : 1;
+    if (nar) rc = narrow_stage(h, bf, 0, 0);
+    else rc = eval_stage(h, bf, mode, 2 /*SRC_SLOT0*/, 0, 0);   // k1 = f(u0)
+    if (rc) return rc;
     if (c.dt0 > 0) {
         launch_initdt(h, 2);
     } else {
         launch_initnorm(h, bf, 0);
         if (h->nranks > 1 && (rc = cnf_nccl_allreduce_f64(h, h->d_ctrl->initsum, 2))) return rc;
         launch_initdt(h, 0);
-        launch_combine(h, bf, -1);
-        if ((rc = launch_eval_generic_sel(h, bf, mode, 0 /*SRC_S*/, nullptr, -1, bf.K[1], 0))) return rc;
+        if (nar) {
+            if ((rc = narrow_stage(h, bf, -1, 0))) return rc;
+        } else {
+            launch_combine(h, bf, -1);
+            if ((rc = launch_eval_generic_sel(h, bf, mode, 0 /*SRC_S*/, nullptr, -1, bf.K[1], 0))) return rc;
+        }
         launch_initnorm(h, bf, 1);
         if (h->nranks > 1 && (rc = cnf_nccl_allreduce_f64(h, h->d_ctrl->initsum + 2, 1))) return rc;
         launch_initdt(h, 1);

@@ -50,6 +50,7 @@ struct cnf_handle {
     double ms_stage = 0.0;
     long long n_stage = 0;
     int path_used = 0;
+    void* narrow_w = nullptr;   // host copy of the packed kernel-parameter weights (narrow path)
 };
 
 #define CNF_CUDA(call)                                                                   \
@@ -87,9 +88,11 @@ int launch_vjp_generic(cnf_handle* h, const CnfBufs& bf, const float* src, const
                        float* zbar, float* grad);
 
 // ---- cnf_stage_narrow.cu : register-resident one-sample-per-thread kernels
-bool narrow_supported(const cnf_config& cfg);
-// fused: stage input from (u, k1..k_{i}) -> k_{i+1}; stage 6 also writes unew + error partials
-int launch_stage_narrow(cnf_handle* h, const CnfBufs& bf, int mode, int stage);
+bool narrow_supported(const cnf_config& cfg, int mode);
+void narrow_set_params(cnf_handle* h, const float* theta_host);
+void narrow_free(cnf_handle* h);
+// fused: stage input from (u, k1..k_i) -> k_{i+1}; stage 6 also writes unew + error partials
+int launch_stage_narrow(cnf_handle* h, const CnfBufs& bf, int stage, int check_done);
 
 // ---- cnf_nccl.cu
 int cnf_nccl_allreduce_f64(cnf_handle* h, double* dptr, int n);

@@ -2,6 +2,7 @@
 // templates in one module; no relocatable device code needed).
 #include "cnf_solver.cu"
 #include "cnf_stage_generic.cu"
+#include "cnf_stage_narrow.cu"
 #include "cnf_backward.cu"
 #include "cnf_nccl.cu"
 #include "cnf_api.cu"

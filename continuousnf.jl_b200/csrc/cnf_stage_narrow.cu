@@ -1,0 +1,237 @@
+// cnf_stage_narrow.cu — register-resident stage kernels for narrow nets (hidden <= 64):
+// one sample per thread, activations and tangents in registers, weights passed as a
+// __grid_constant__ kernel parameter so they reach the FMA pipe as uniform-register operands
+// (LDCU.128 + FFMA R,R,UR,R: no shared-memory or LSU traffic in the inner loop).  One launch per
+// RK stage fuses: stage-input combination u + dt*sum a_ij k_j, Dense/tanh chain forward, the D
+// tangent sweeps of the exact trace (reference src/utils.jl:19-36 via src/icnf.jl:148-164), the
+// output rows, and for the 7th stage the new state and the embedded-error partial sums.
+// Coalesced SoA row loads/stores; block reduction by __shfl.
+#include "cnf_internal.h"
+
+#define NARROW_MAXW 7936   // floats; kernel parameters are limited to 32764 bytes
+struct alignas(16) NarrowW { float w[NARROW_MAXW]; };
+
+// rational tanh_fast without the saturation branch and with rcp.approx (fast path; the generic
+// path keeps the IEEE division).  Input clamped to +-sqrt(66), where the rational is +-1 to 3e-7.
+__device__ __forceinline__ float cnf_tanh_fastpath(float x) {
+    x = fminf(fmaxf(x, -8.1240384f), 8.1240384f);
+    float x2 = x * x;
+    float n = fmaf(x2, fmaf(x2, fmaf(x2, fmaf(x2, CNF_TANH_N4, CNF_TANH_N3), CNF_TANH_N2), CNF_TANH_N1), 1.0f);
+    float d = fmaf(x2, fmaf(x2, fmaf(x2, fmaf(x2, CNF_TANH_D4, CNF_TANH_D3), CNF_TANH_D2), CNF_TANH_D1), 1.0f);
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(d));
+    r = fmaf(fmaf(-d, r, 1.0f), r, r);   // one Newton step: <= 1 ulp
+    return x * (n * r);
+}
+
+// packed parameter layout (all sections padded to 4 floats)
+template <int D, int H1, int H2>
+struct NarrowLayout {
+    static constexpr int pad4(int x) { return (x + 3) / 4 * 4; }
+    static constexpr int OB = 4;                        // outputs per inner block of layer 2
+    static constexpr int W1 = 0;                        // [H1][D] row-major
+    static constexpr int B1 = W1 + pad4(H1 * D);
+    static constexpr int W2 = B1 + pad4(H1);            // [H2/OB][H1][OB] o-blocked
+    static constexpr int B2 = W2 + H2 * H1;
+    static constexpr int W3 = B2 + pad4(H2);            // [H2][D] o-major
+    static constexpr int B3 = W3 + pad4(H2 * D);
+    static constexpr int TOTAL = B3 + pad4(D);
+    static_assert(H2 % OB == 0, "H2 must be a multiple of 4");
+    static_assert(TOTAL <= NARROW_MAXW, "network too large for the kernel-parameter path");
+};
+
+// stage: 0 k1 = f(u0) [init]; -1 init probe f(u0 + tdir*dt0init*k1) -> K[1]; 1..5 -> K[stage];
+// 6 -> new state, k7 and the error partial sum.
+template <int D, int H1, int H2>
+__global__ void __launch_bounds__(256, 1)
+k_stage_narrow_test_jvp(const __grid_constant__ NarrowW p, CnfCtrl* __restrict__ c, CnfBufs bf,
+                        int stage, int check_done) {
+    using LY = NarrowLayout<D, H1, H2>;
+    if (check_done && c->done) return;
+    constexpr int R = D + 1;
+    const long long Bs = bf.Bs;
+    const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool live = b < bf.B;
+    const float* u = bf.slots[cnf_slot(c, stage <= 0 ? (stage == 0 ? 0 : 0) : c->naccept)];
+    const float* k1 = bf.K[c->k1idx];
+    float* kout = (stage == 0) ? bf.K[c->k1idx] : (stage == -1 ? bf.K[1] : (stage == 6 ? bf.K[6 - c->k1idx] : bf.K[stage]));
+    const float dt = c->dt;
+    // ---- stage input
+    float z[D];
+    if (stage == 0) {
+#pragma unroll
+        for (int i = 0; i < D; ++i) z[i] = u[(long long)i * Bs + b];
+    } else if (stage == -1) {
+        const float hh = c->tdir * c->dt0init;
+#pragma unroll
+        for (int i = 0; i < D; ++i) z[i] = fmaf(hh, k1[(long long)i * Bs + b], u[(long long)i * Bs + b]);
+    } else {
+        float* unew = bf.slots[cnf_slot(c, c->naccept + 1)];
+        const int nrow = (stage == 6) ? R : D;
+        for (int r = 0; r < nrow; ++r) {   // rows D.. only at the 7th stage (pure quadrature rows)
+            const long long at = (long long)r * Bs + b;
+            float acc = c_A[stage][0] * k1[at];
+            for (int j = 1; j < stage; ++j) acc = fmaf(c_A[stage][j], bf.K[j][at], acc);
+            float v = fmaf(dt, acc, u[at]);
+            if (stage == 6) unew[at] = v;
+            if (r < D) z[r] = v;
+        }
+    }
+    // ---- layer 1 and the D one-hot tangents tau1_v = W1[:,v] .* (1 - h1^2)
+    float h1[H1], t1[D][H1];
+#pragma unroll
+    for (int o = 0; o < H1; ++o) {
+        float a = p.w[LY::B1 + o];
+#pragma unroll
+        for (int i = 0; i < D; ++i) a = fmaf(p.w[LY::W1 + o * D + i], z[i], a);
+        float h = cnf_tanh_fastpath(a);
+        h1[o] = h;
+        float d = fmaf(-h, h, 1.0f);
+#pragma unroll
+        for (int v = 0; v < D; ++v) t1[v][o] = p.w[LY::W1 + o * D + v] * d;
+    }
+    // ---- layers 2 and 3 streamed: 4 outputs of layer 2 at a time, consumed at once by layer 3
+    float p3[D], r3[D][D];
+#pragma unroll
+    for (int j = 0; j < D; ++j) {
+        p3[j] = p.w[LY::B3 + j];
+#pragma unroll
+        for (int v = 0; v < D; ++v) r3[v][j] = 0.0f;
+    }
+#pragma unroll 1
+    for (int ob = 0; ob < H2 / LY::OB; ++ob) {
+        float a[LY::OB], t[LY::OB][D];
+        const float4 bb = *reinterpret_cast<const float4*>(&p.w[LY::B2 + ob * 4]);
+        a[0] = bb.x; a[1] = bb.y; a[2] = bb.z; a[3] = bb.w;
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+#pragma unroll
+            for (int v = 0; v < D; ++v) t[k][v] = 0.0f;
+        const float4* wblk = reinterpret_cast<const float4*>(&p.w[LY::W2 + ob * (H1 * 4)]);
+#pragma unroll
+        for (int i = 0; i < H1; ++i) {
+            const float4 w4 = wblk[i];
+            const float w[4] = {w4.x, w4.y, w4.z, w4.w};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                a[k] = fmaf(w[k], h1[i], a[k]);
+#pragma unroll
+                for (int v = 0; v < D; ++v) t[k][v] = fmaf(w[k], t1[v][i], t[k][v]);
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int o = ob * 4 + k;
+            float h = cnf_tanh_fastpath(a[k]);
+            float d = fmaf(-h, h, 1.0f);
+#pragma unroll
+            for (int j = 0; j < D; ++j) {
+                const float w3 = p.w[LY::W3 + o * D + j];
+                p3[j] = fmaf(w3, h, p3[j]);
+#pragma unroll
+                for (int v = 0; v < D; ++v) r3[v][j] = fmaf(w3, t[k][v] * d, r3[v][j]);
+            }
+        }
+    }
+    // ---- outputs: zdot rows and -tr(J)
+    float y[D], tr = 0.0f;
+#pragma unroll
+    for (int j = 0; j < D; ++j) {
+        y[j] = cnf_tanh_fastpath(p3[j]);
+        tr -= fmaf(-y[j], y[j], 1.0f) * r3[j][j];
+        kout[(long long)j * Bs + b] = y[j];
+    }
+    kout[(long long)D * Bs + b] = tr;
+    if (stage != 6) return;
+    // ---- 7th stage: embedded error partial sum over this thread's R elements
+    double acc = 0.0;
+    if (live) {
+        const float* un = bf.slots[cnf_slot(c, c->naccept + 1)];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const long long at = (long long)r * Bs + b;
+            float a = c_BT[0] * k1[at];
+            for (int j = 1; j < 6; ++j) a = fmaf(c_BT[j], bf.K[j][at], a);
+            a = fmaf(c_BT[6], r < D ? y[r] : tr, a);
+            float ut = dt * a;
+            float unv = un[at];
+            float sc = fmaf(fmaxf(fabsf(u[at]), fabsf(unv)), c->reltol, c->abstol);
+            float q = ut / sc;
+            if (unv != unv) q = unv;
+            acc += (double)q * (double)q;
+        }
+    }
+    __shared__ double sh[32];
+    acc = cnf_block_sum(acc, sh);
+    if (threadIdx.x == 0) atomicAdd(&c->errsum, acc);
+}
+
+// ------------------------------------------------------------------ host side
+template <int D, int H1, int H2>
+static void narrow_pack(const cnf_handle* h, const float* theta, NarrowW* out) {
+    using LY = NarrowLayout<D, H1, H2>;
+    memset(out, 0, sizeof(*out));
+    const float* W1 = theta + h->w_off[0];   // col-major H1 x D
+    const float* W2 = theta + h->w_off[1];   // col-major H2 x H1
+    const float* W3 = theta + h->w_off[2];   // col-major D x H2
+    for (int o = 0; o < H1; ++o) {
+        for (int i = 0; i < D; ++i) out->w[LY::W1 + o * D + i] = W1[i * H1 + o];
+        out->w[LY::B1 + o] = theta[h->b_off[0] + o];
+    }
+    for (int o = 0; o < H2; ++o) {
+        for (int i = 0; i < H1; ++i) out->w[LY::W2 + (o / 4) * (H1 * 4) + i * 4 + (o % 4)] = W2[i * H2 + o];
+        out->w[LY::B2 + o] = theta[h->b_off[1] + o];
+    }
+    for (int o = 0; o < H2; ++o)
+        for (int j = 0; j < D; ++j) out->w[LY::W3 + o * D + j] = W3[o * D + j];
+    for (int j = 0; j < D; ++j) out->w[LY::B3 + j] = theta[h->b_off[2] + j];
+}
+
+template <int D, int H1, int H2>
+static void narrow_launch(cnf_handle* h, const CnfBufs& bf, int stage, int check_done) {
+    unsigned grid = (unsigned)(bf.Bs / 256);
+    k_stage_narrow_test_jvp<D, H1, H2><<<grid, 256, 0, h->stream>>>(*(const NarrowW*)h->narrow_w, h->d_ctrl, bf,
+                                                                  stage, check_done);
+    h->launches++;
+}
+
+struct NarrowEntry {
+    int D, H1, H2;
+    void (*pack)(const cnf_handle*, const float*, NarrowW*);
+    void (*launch)(cnf_handle*, const CnfBufs&, int, int);
+};
+#define NARROW_ENTRY(D, H1, H2) {D, H1, H2, narrow_pack<D, H1, H2>, narrow_launch<D, H1, H2>}
+static const NarrowEntry g_narrow[] = {
+    NARROW_ENTRY(2, 64, 64), NARROW_ENTRY(2, 32, 32), NARROW_ENTRY(1, 64, 64),
+    NARROW_ENTRY(3, 64, 64), NARROW_ENTRY(4, 32, 32),
+};
+
+static const NarrowEntry* narrow_find(const cnf_config& c) {
+    if (c.n_layers != 3 || c.C != 0) return nullptr;
+    for (const NarrowEntry& e : g_narrow)
+        if (e.D == c.D && e.H1 == c.dims[1] && e.H2 == c.dims[2]) return &e;
+    return nullptr;
+}
+
+// TestMode + JacVec exact trace on a supported shape
+bool narrow_supported(const cnf_config& c, int mode) {
+    return mode == CNF_MODE_TEST && c.trace_mode == CNF_TRACE_JVP && narrow_find(c) != nullptr;
+}
+
+// called from set_params with a host copy of theta
+void narrow_set_params(cnf_handle* h, const float* theta_host) {
+    const NarrowEntry* e = narrow_find(h->cfg);
+    if (!e) return;
+    if (!h->narrow_w) h->narrow_w = new NarrowW();
+    e->pack(h, theta_host, (NarrowW*)h->narrow_w);
+}
+void narrow_free(cnf_handle* h) {
+    delete (NarrowW*)h->narrow_w;
+    h->narrow_w = nullptr;
+}
+int launch_stage_narrow(cnf_handle* h, const CnfBufs& bf, int stage, int check_done) {
+    const NarrowEntry* e = narrow_find(h->cfg);
+    if (!e || !h->narrow_w) { h->err = "narrow path: unsupported shape"; return CNF_ERR_UNSUPPORTED; }
+    e->launch(h, bf, stage, check_done);
+    return CNF_OK;
+}
