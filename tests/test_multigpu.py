@@ -1,0 +1,28 @@
+"""K9 on real GPUs (needs >= 2 B200s; skipped otherwise): sharded solve with the NCCL per-step
+error-norm allreduce == single-GPU solve of the whole batch."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.gpu
+def test_shard_invariance_two_ranks():
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+           "--master-addr", "127.0.0.1", "--master-port", "29631", os.path.join(ROOT, "tests", "multigpu_worker.py")]
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
+    line = [l for l in p.stdout.splitlines() if l.startswith("RESULT ")][-1]
+    res = json.loads(line[7:])
+    assert res["C2"]["dsteps"] <= 1 and res["C4"]["dsteps"] <= 1
+    if res["C2"]["dsteps"] == 0:
+        assert res["C2"]["lp_rel"] < 1e-4
+    if res["C4"]["dsteps"] == 0:
+        assert res["C4"]["loss_rel"] < 1e-4 and res["C4"]["grad_rel"] < 1e-3
