@@ -93,6 +93,7 @@ extern "C" int32_t cnfb200_destroy(cnf_handle* h) {
     }
     free_workspaces(h);
     narrow_free(h);
+    tc_free(h);
     cudaFree(h->d_io);
     cudaFree(h->d_theta); cudaFree(h->d_wt); cudaFree(h->d_grad);
     cudaFree(h->d_ctrl); cudaFree(h->d_dts); cudaFree(h->d_lossacc); cudaFree(h->d_slots);
@@ -167,6 +168,11 @@ extern "C" int32_t cnfb200_set_params(cnf_handle* h, const float* theta, int64_t
         std::vector<float> th((size_t)n);
         CNF_CUDA(cudaMemcpy(th.data(), h->d_theta, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost));
         narrow_set_params(h, th.data());
+    }
+    {
+        int rc = tc_set_params(h);
+        if (rc) return rc;
+        CNF_CUDA(cudaStreamSynchronize(h->stream));
     }
     h->have_params = true;
     return CNF_OK;
@@ -279,6 +285,16 @@ static bool use_narrow(cnf_handle* h, int mode) {
     return narrow_supported(h->cfg, mode) && h->narrow_w != nullptr;
 }
 
+static bool use_tc(cnf_handle* h, int mode) {
+    return tc_supported(h->cfg, mode) && h->tc_state != nullptr;
+}
+static int tc_stage(cnf_handle* h, const CnfBufs& bf, const float* src, int kidx, float* kout_fixed, int check_done) {
+    stage_timer_begin(h);
+    int rc = tc_eval(h, bf, src, kidx, kout_fixed, check_done);
+    stage_timer_end(h);
+    return rc;
+}
+
 static int narrow_stage(cnf_handle* h, const CnfBufs& bf, int stage, int check_done) {
     stage_timer_begin(h);
     int rc = launch_stage_narrow(h, bf, stage, check_done);
@@ -298,6 +314,18 @@ static int enqueue_attempt(cnf_handle* h, const CnfBufs& bf, int mode) {
     if (use_narrow(h, mode)) {   // fused path: 6 stage launches (the 7th stage carries the error norm)
         for (int i = 1; i <= 6; ++i)
             if ((rc = narrow_stage(h, bf, i, 1))) return rc;
+        if (h->nranks > 1 && (rc = cnf_nccl_allreduce_f64(h, &h->d_ctrl->errsum, 1))) return rc;
+        launch_controller(h);
+        return CNF_OK;
+    }
+    if (use_tc(h, mode)) {       // tensor path: layer GEMMs on tcgen05, RK combination streaming
+        for (int i = 1; i <= 5; ++i) {
+            launch_combine(h, bf, i);
+            if ((rc = tc_stage(h, bf, bf.S, i, nullptr, 1))) return rc;
+        }
+        launch_combine(h, bf, 6, 1);
+        if ((rc = tc_stage(h, bf, bf.S, 6, nullptr, 1))) return rc;
+        launch_errnorm(h, bf);
         if (h->nranks > 1 && (rc = cnf_nccl_allreduce_f64(h, &h->d_ctrl->errsum, 1))) return rc;
         launch_controller(h);
         return CNF_OK;
@@ -340,8 +368,10 @@ static int solve_device(cnf_handle* h, const CnfBufs& bf, int mode, int R, long 
     CNF_CUDA(cudaEventRecord(h->ev1, h->stream));
     int rc;
     const bool nar = use_narrow(h, mode);
-    h->path_used = nar ? 2 : 1;
+    const bool tcp = !nar && use_tc(h, mode);
+    h->path_used = nar ? 2 : (tcp ? 3 : 1);
     if (nar) rc = narrow_stage(h, bf, 0, 0);
+    else if (tcp) rc = tc_stage(h, bf, h->slots[0], 0, nullptr, 0);
     else rc = eval_stage(h, bf, mode, 2 /*SRC_SLOT0*/, 0, 0);   // k1 = f(u0)
     if (rc) return rc;
     if (c.dt0 > 0) {
@@ -352,6 +382,9 @@ static int solve_device(cnf_handle* h, const CnfBufs& bf, int mode, int R, long 
         launch_initdt(h, 0);
         if (nar) {
             if ((rc = narrow_stage(h, bf, -1, 0))) return rc;
+        } else if (tcp) {
+            launch_combine(h, bf, -1);
+            if ((rc = tc_stage(h, bf, bf.S, -1, bf.K[1], 0))) return rc;
         } else {
             launch_combine(h, bf, -1);
             if ((rc = launch_eval_generic_sel(h, bf, mode, 0 /*SRC_S*/, nullptr, -1, bf.K[1], 0))) return rc;
@@ -477,7 +510,10 @@ extern "C" int32_t cnfb200_augmented_f(cnf_handle* h, int32_t mode, const float*
     CnfBufs bf = make_bufs(h, B);
     if ((rc = load_problem(h, bf, io, mode, R, u, R, ys, eps, B))) return rc;
     h->path_used = 1;
-    if ((rc = launch_eval_generic(h, bf, mode, h->slots[0], h->d_K[0]))) return rc;
+    if (use_tc(h, mode)) {
+        h->path_used = 3;
+        if ((rc = tc_eval(h, bf, h->slots[0], -1, h->d_K[0], 0))) return rc;
+    } else if ((rc = launch_eval_generic(h, bf, mode, h->slots[0], h->d_K[0]))) return rc;
     float* dout = is_device_ptr(du) ? du : h->d_io + io.total;
     launch_unpack_rows(h, h->d_K[0], R, B, bf.Bs, dout);
     if (dout != du)

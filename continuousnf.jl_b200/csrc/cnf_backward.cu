@@ -292,6 +292,12 @@ static int launch_vjp_generic_stage(cnf_handle* h, const CnfBufs& bf, const floa
     return CNF_OK;
 }
 
+// forward re-evaluation used by the stage checkpointing: tensor path when available
+static int bw_eval(cnf_handle* h, const CnfBufs& bf, const float* src, float* kout) {
+    if (tc_supported(h->cfg, CNF_MODE_TRAIN) && h->tc_state) return tc_eval(h, bf, src, -1, kout, 0);
+    return launch_eval_generic(h, bf, CNF_MODE_TRAIN, src, kout);
+}
+
 static unsigned bw_grid(long long n) {
     long long g = (n + CNF_NT - 1) / CNF_NT;
     if (g > 148LL * 16) g = 148LL * 16;
@@ -313,11 +319,11 @@ static int backward_sweep(cnf_handle* h, const CnfBufs& bf, long long naccept, l
         const float* un = h->slots[n];
         const float* dtp = h->d_dts + n;
         // stage checkpointing: recompute k_1..k_5 and the stage inputs s_2..s_6 of step n
-        if ((rc = launch_eval_generic(h, bf, CNF_MODE_TRAIN, un, h->d_K[0]))) return rc;
+        if ((rc = bw_eval(h, bf, un, h->d_K[0]))) return rc;
         for (int i = 1; i <= 5; ++i) {
             k_combine_bw<<<bw_grid(nz), CNF_NT, 0, h->stream>>>(un, bf, i, dtp, w[i - 1], nz);
             h->launches++;
-            if (i < 5 && (rc = launch_eval_generic(h, bf, CNF_MODE_TRAIN, w[i - 1], h->d_K[i]))) return rc;
+            if (i < 5 && (rc = bw_eval(h, bf, w[i - 1], h->d_K[i]))) return rc;
         }
         k_kbar_init<<<bw_grid(nz), CNF_NT, 0, h->stream>>>(ubar, dtp, kb[0], kb[1], kb[2], kb[3], kb[4], kb[5], nz);
         h->launches++;

@@ -50,6 +50,7 @@ struct cnf_handle {
     double ms_stage = 0.0;
     long long n_stage = 0;
     int path_used = 0;
+    void* tc_state = nullptr;   // tensor-core path state (cnf_stage_tc.cu)
     void* narrow_w = nullptr;   // host copy of the packed kernel-parameter weights (narrow path)
 };
 
@@ -70,7 +71,7 @@ void stage_timer_end(cnf_handle* h);
 void cnf_upload_constants();
 void launch_pack_rows(cnf_handle* h, const float* src, int rows, long long B, float* dst, long long Bs);
 void launch_unpack_rows(cnf_handle* h, const float* src, int rows, long long B, long long Bs, float* dst);
-void launch_combine(cnf_handle* h, const CnfBufs& bf, int stage);   // stage 1..5 -> S, 6 -> unew, -1 -> init probe
+void launch_combine(cnf_handle* h, const CnfBufs& bf, int stage, int also_S = 0);   // stage 1..5 -> S, 6 -> unew, -1 -> init probe
 void launch_errnorm(cnf_handle* h, const CnfBufs& bf);
 void launch_controller(cnf_handle* h);
 void launch_initnorm(cnf_handle* h, const CnfBufs& bf, int which);
@@ -93,6 +94,12 @@ void narrow_set_params(cnf_handle* h, const float* theta_host);
 void narrow_free(cnf_handle* h);
 // fused: stage input from (u, k1..k_i) -> k_{i+1}; stage 6 also writes unew + error partials
 int launch_stage_narrow(cnf_handle* h, const CnfBufs& bf, int stage, int check_done);
+
+// ---- cnf_stage_tc.cu : tcgen05 tensor path (wide nets, TrainMode)
+bool tc_supported(const cnf_config& cfg, int mode);
+int tc_set_params(cnf_handle* h);
+void tc_free(cnf_handle* h);
+int tc_eval(cnf_handle* h, const CnfBufs& bf, const float* src, int kidx, float* kout_fixed, int check_done);
 
 // ---- cnf_nccl.cu
 int cnf_nccl_allreduce_f64(cnf_handle* h, double* dptr, int n);

@@ -45,7 +45,7 @@ void launch_unpack_rows(cnf_handle* h, const float* src, int rows, long long B, 
 // ---------------------------------------------------------------- RK combination (generic path)
 // stage s in 1..5: S = u + dt*sum_{j<s+... } a[s][j] k_j on the D z rows (f reads only those);
 // stage 6: unew = u + dt*sum a7j k_j on all R rows; stage -1: S = u + tdir*dt0init*k1 (init probe).
-__global__ void k_combine(const CnfCtrl* __restrict__ c, CnfBufs bf, int stage) {
+__global__ void k_combine(const CnfCtrl* __restrict__ c, CnfBufs bf, int stage, int also_S) {
     if (c->done) return;
     const int nrows = (stage == 6) ? c->R : c->D;
     const long long n = (long long)nrows * bf.Bs;
@@ -59,7 +59,9 @@ __global__ void k_combine(const CnfCtrl* __restrict__ c, CnfBufs bf, int stage) 
         } else {
             float acc = c_A[stage][0] * k1[e];
             for (int j = 1; j < stage; ++j) acc = fmaf(c_A[stage][j], bf.K[j][e], acc);
-            out[e] = fmaf(c->dt, acc, u[e]);
+            const float v = fmaf(c->dt, acc, u[e]);
+            out[e] = v;
+            if (also_S && e < (long long)c->D * bf.Bs) bf.S[e] = v;   // z rows of the new state
         }
     }
 }
@@ -68,9 +70,9 @@ static inline unsigned grid_for(long long n) {
     if (g > 148LL * 16) g = 148LL * 16;
     return (unsigned)(g < 1 ? 1 : g);
 }
-void launch_combine(cnf_handle* h, const CnfBufs& bf, int stage) {
+void launch_combine(cnf_handle* h, const CnfBufs& bf, int stage, int also_S) {
     int nrows = (stage == 6) ? h->cur_R : h->cfg.D;
-    k_combine<<<grid_for((long long)nrows * bf.Bs), CNF_NT, 0, h->stream>>>(h->d_ctrl, bf, stage);
+    k_combine<<<grid_for((long long)nrows * bf.Bs), CNF_NT, 0, h->stream>>>(h->d_ctrl, bf, stage, also_S);
     h->launches++;
 }
 

@@ -1,0 +1,572 @@
+// cnf_stage_tc.cu — tensor-core path for wide nets (hidden >= 128, TrainMode Hutchinson).
+// Every layer product of the Dense/tanh chain and of its VJP / JVP chain is a TMA-fed
+// tcgen05.mma GEMM with the batch as the M dimension (128 samples per tile, one TMEM lane per
+// sample), FP32 accumulators in TMEM, and the layer's elementwise work fused into the
+// TMEM->register epilogue (bias + tanh, the (1-h^2) Hadamard factor, the eps dot product and
+// the un-squared norms of reference src/icnf.jl:335-348).
+// Precision: BF16x6 operand splitting (x = p0 + p1 + p2 in bf16; products p0p0 + p1p0 + p0p1 +
+// p1p1 + p2p0 + p0p2, FP32 accumulate) = FP32-level accuracy (1e-8 relative on log-density in
+// scripts/precision_study.py).  BF16x3 (1e-6..4e-6) meets the 1e-4 value tolerance but its 1e-5
+// noise in f is amplified by the abstol = 1e-6 rows of the error norm and changes the accepted-step
+// count by 5-7 steps; plain TF32 (1e-4..2e-4) misses the value tolerance as well.
+// Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (one elected thread), warps 2..9 =
+// epilogue (two warps per TMEM lane quadrant, half of the columns each); two TMEM accumulator
+// buffers so the epilogue of tile i overlaps the MMAs of tile i+1.
+#include "cnf_internal.h"
+#include "cnf_tc_ptx.cuh"
+#include <cuda.h>
+
+#define TC_BM 128
+#define TC_BK 64            // bf16 elements per 128-byte swizzled row
+#define TC_THREADS 320      // 10 warps
+#define TC_EPI_WARP0 2
+
+enum { TC_FWD_HIDDEN = 0, TC_FWD_LAST = 1, TC_BWD_HIDDEN = 2, TC_BWD_LAST = 3, TC_JVP_LAST = 4 };
+
+struct TcEpi {
+    int kind;
+    int N;                         // valid output columns
+    const float* bias;             // [N]                       (FWD_*)
+    __nv_bfloat16* out[3];         // [rows x ld_out] planes    (hidden kinds; FWD_LAST: g_L planes)
+    int ld_out;
+    const __nv_bfloat16* hp[3];    // activations for d = 1-h^2 (BWD_HIDDEN)
+    int ld_h;
+    const float* eps;              // D x Bs (SoA)
+    float* kout;                   // R x Bs (SoA); if kout_ind != nullptr the pointer is read from there
+    float* const* kout_ind;        // device-resolved output buffer (k7 / FSAL index lives on the device)
+    const CnfCtrl* ctrl;           // early exit when the solve is done (nullptr: never)
+    long long Bs;
+    long long row0;                // first sample of this chunk
+    int D;
+    unsigned flags;
+    int vjp;                       // FWD_LAST: also emit g_L = eps .* (1-y^2) planes
+};
+
+#define TC_NP 3   // bf16 planes per operand
+__device__ __forceinline__ void tc_split(float x, __nv_bfloat16 (&p)[3]) {
+    p[0] = __float2bfloat16_rn(x);
+    float r = x - __bfloat162float(p[0]);
+    p[1] = __float2bfloat16_rn(r);
+    r -= __bfloat162float(p[1]);
+    p[2] = __float2bfloat16_rn(r);
+}
+__device__ __forceinline__ uint32_t tc_pack(__nv_bfloat16 a, __nv_bfloat16 b) {
+    return (uint32_t)__bfloat16_as_ushort(a) | ((uint32_t)__bfloat16_as_ushort(b) << 16);
+}
+
+struct TcMaps { CUtensorMap a[3], b[3]; };   // A planes, B planes
+
+struct TcSmemCtl {
+    uint64_t full[8], empty[8], tfull[2], tempty[2];
+    uint32_t tmem_base;
+};
+
+// ---- epilogue helpers: one thread = one sample row; v = 32 accumulator columns c0..c0+31
+__device__ __forceinline__ void tc_store_planes32(const float (&x)[32], __nv_bfloat16* const (&dst)[3], long long off) {
+    uint32_t pk[3][16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+        __nv_bfloat16 a[3], b[3];
+        tc_split(x[2 * j], a);
+        tc_split(x[2 * j + 1], b);
+#pragma unroll
+        for (int q = 0; q < 3; ++q) pk[q][j] = tc_pack(a[q], b[q]);
+    }
+#pragma unroll
+    for (int q = 0; q < 3; ++q) {
+        uint4* d = reinterpret_cast<uint4*>(dst[q] + off);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) d[j] = make_uint4(pk[q][4 * j], pk[q][4 * j + 1], pk[q][4 * j + 2], pk[q][4 * j + 3]);
+    }
+}
+
+__device__ __forceinline__ void tc_load_planes32(const __nv_bfloat16* const (&src)[3], long long off, float (&h)[32]) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) h[j] = 0.0f;
+#pragma unroll
+    for (int q = 2; q >= 0; --q) {   // smallest plane first
+        const uint4* sp = reinterpret_cast<const uint4*>(src[q] + off);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            uint4 a = __ldg(sp + j);
+            const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                h[8 * j + 2 * k] += __uint_as_float(aw[k] << 16);
+                h[8 * j + 2 * k + 1] += __uint_as_float(aw[k] & 0xffff0000u);
+            }
+        }
+    }
+}
+
+// BM x BN output tile per (m_blk, n_blk); K in blocks of 64 bf16; persistent over tiles.
+__global__ void __launch_bounds__(TC_THREADS, 1)
+k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, int nk, int nstage, TcEpi ep) {
+    if (ep.ctrl && ep.ctrl->done) return;
+    if (ep.kout_ind) ep.kout = *ep.kout_ind;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    const uint32_t a_bytes = TC_BM * 128;          // one plane of A per stage
+    const uint32_t b_bytes = (uint32_t)BN * 128;   // one plane of B per stage
+    const uint32_t stage_bytes = TC_NP * (a_bytes + b_bytes);
+    TcSmemCtl* ctl = reinterpret_cast<TcSmemCtl*>(smem + (size_t)nstage * stage_bytes);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int total = m_tiles * n_tiles;
+
+    if (warp == 0 && lane == 0) {
+        for (int q = 0; q < TC_NP; ++q) { tc::tma_prefetch_desc(&mp.a[q]); tc::tma_prefetch_desc(&mp.b[q]); }
+        for (int s = 0; s < nstage; ++s) { tc::mbar_init(&ctl->full[s], 1); tc::mbar_init(&ctl->empty[s], 1); }
+        for (int a = 0; a < 2; ++a) { tc::mbar_init(&ctl->tfull[a], 1); tc::mbar_init(&ctl->tempty[a], 8); }
+        tc::fence_barrier_init();
+    }
+    if (warp == 1) tc::tmem_alloc(&ctl->tmem_base, 512);
+    tc::tc_fence_before();
+    __syncthreads();
+    tc::tc_fence_after();
+    const uint32_t tmem = ctl->tmem_base;
+
+    if (warp == 0) {
+        if (lane == 0) {   // ===== TMA producer
+            int stage = 0; uint32_t phase = 0;
+            for (int t = blockIdx.x; t < total; t += gridDim.x) {
+                const int mb = t / n_tiles, nb = t % n_tiles;
+                for (int kb = 0; kb < nk; ++kb) {
+                    tc::mbar_wait(&ctl->empty[stage], phase ^ 1);
+                    uint8_t* s = smem + (size_t)stage * stage_bytes;
+                    tc::mbar_arrive_expect_tx(&ctl->full[stage], stage_bytes);
+                    for (int q = 0; q < TC_NP; ++q) {
+                        tc::tma_load_2d(&mp.a[q], &ctl->full[stage], s + q * a_bytes, kb * TC_BK, mb * TC_BM);
+                        tc::tma_load_2d(&mp.b[q], &ctl->full[stage], s + TC_NP * a_bytes + q * b_bytes, kb * TC_BK, nb * BN);
+                    }
+                    if (++stage == nstage) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {   // ===== MMA issuer
+            const uint32_t idesc = tc::umma_idesc_bf16(TC_BM, BN);
+            int stage = 0; uint32_t phase = 0; int it = 0;
+            for (int t = blockIdx.x; t < total; t += gridDim.x, ++it) {
+                const int acc = it & 1;
+                tc::mbar_wait(&ctl->tempty[acc], ((it >> 1) & 1) ^ 1);
+                tc::tc_fence_after();
+                const uint32_t dcol = tmem + (uint32_t)acc * 256;
+                for (int kb = 0; kb < nk; ++kb) {
+                    tc::mbar_wait(&ctl->full[stage], phase);
+                    tc::tc_fence_after();
+                    const uint32_t s = tc::smem_u32(smem + (size_t)stage * stage_bytes);
+#pragma unroll
+                    for (int kk = 0; kk < TC_BK / 16; ++kk) {
+                        uint64_t a[TC_NP], b[TC_NP];
+#pragma unroll
+                        for (int q = 0; q < TC_NP; ++q) {
+                            a[q] = tc::umma_desc_sw128(s + q * a_bytes + kk * 32);
+                            b[q] = tc::umma_desc_sw128(s + TC_NP * a_bytes + q * b_bytes + kk * 32);
+                        }
+                        // BF16x6: all products down to 2^-24 relative
+                        tc::umma_bf16(dcol, a[0], b[0], idesc, (kb | kk) != 0);
+                        tc::umma_bf16(dcol, a[1], b[0], idesc, 1);
+                        tc::umma_bf16(dcol, a[0], b[1], idesc, 1);
+                        tc::umma_bf16(dcol, a[1], b[1], idesc, 1);
+                        tc::umma_bf16(dcol, a[2], b[0], idesc, 1);
+                        tc::umma_bf16(dcol, a[0], b[2], idesc, 1);
+                    }
+                    tc::umma_commit(&ctl->empty[stage]);
+                    if (++stage == nstage) { stage = 0; phase ^= 1; }
+                }
+                tc::umma_commit(&ctl->tfull[acc]);
+            }
+        }
+    } else {               // ===== epilogue warps
+        const int e = warp - TC_EPI_WARP0;       // 0..7
+        const int quad = warp & 3;               // TMEM lane quadrant this warp may access
+        const int half = e >> 2;                 // column half
+        int it = 0;
+        for (int t = blockIdx.x; t < total; t += gridDim.x, ++it) {
+            const int mb = t / n_tiles, nb = t % n_tiles;
+            const int acc = it & 1;
+            tc::mbar_wait(&ctl->tfull[acc], (it >> 1) & 1);
+            tc::tc_fence_after();
+            const long long rloc = (long long)mb * TC_BM + quad * 32 + lane;   // row inside the chunk
+            const long long grow = ep.row0 + rloc;                               // global sample
+            const uint32_t tbase = tmem + ((uint32_t)(quad * 32) << 16) + (uint32_t)acc * 256;
+            const bool last_kind = (ep.kind == TC_FWD_LAST || ep.kind == TC_BWD_LAST || ep.kind == TC_JVP_LAST);
+            const int nchunk = (BN + 31) / 32;
+            if (!last_kind) {
+                // column chunks are split between the two warps of a quadrant
+                for (int ch = half; ch < nchunk; ch += 2) {
+                    const int c0 = ch * 32, ng = nb * BN + c0;   // global column of v[0]
+                    uint32_t v[32];
+                    tc::tmem_ld_32x32(tbase + c0, v);
+                    tc::tmem_ld_wait();
+                    if (ng >= ep.N) continue;
+                    float x[32];
+                    if (ep.kind == TC_FWD_HIDDEN) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) x[j] = cnf_tanh_fastpath(__uint_as_float(v[j]) + __ldg(ep.bias + ng + j));
+                    } else {   // BWD_HIDDEN: acc .* (1 - h^2)
+                        float h[32];
+                        tc_load_planes32(ep.hp, rloc * ep.ld_h + ng, h);
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) x[j] = __uint_as_float(v[j]) * fmaf(-h[j], h[j], 1.0f);
+                    }
+                    tc_store_planes32(x, ep.out, rloc * ep.ld_out + ng);
+                }
+            } else if (half == 0) {
+                // per-sample reductions over all D columns: one warp per quadrant walks every chunk
+                float s0 = 0.0f, s1 = 0.0f;
+                for (int ch = 0; ch < nchunk; ++ch) {
+                    const int c0 = ch * 32;
+                    uint32_t v[32];
+                    tc::tmem_ld_32x32(tbase + c0, v);
+                    tc::tmem_ld_wait();
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const int n = c0 + j;
+                        if (n < ep.D) {
+                            const float a = __uint_as_float(v[j]);
+                            if (ep.kind == TC_FWD_LAST) {
+                                const float y = cnf_tanh_fastpath(a + __ldg(ep.bias + n));
+                                ep.kout[(long long)n * ep.Bs + grow] = y;
+                                s0 = fmaf(y, y, s0);
+                                if (ep.vjp) {
+                                    const float g = ep.eps[(long long)n * ep.Bs + grow] * fmaf(-y, y, 1.0f);
+                                    __nv_bfloat16 gp[3];
+                                    tc_split(g, gp);
+#pragma unroll
+                                    for (int q = 0; q < 3; ++q) ep.out[q][rloc * ep.ld_out + n] = gp[q];
+                                }
+                            } else {
+                                float vv = a;
+                                if (ep.kind == TC_JVP_LAST) {
+                                    const float y = ep.kout[(long long)n * ep.Bs + grow];
+                                    vv = a * fmaf(-y, y, 1.0f);
+                                }
+                                s0 = fmaf(-vv, ep.eps[(long long)n * ep.Bs + grow], s0);
+                                s1 = fmaf(vv, vv, s1);
+                            }
+                        }
+                    }
+                }
+                if (ep.kind == TC_FWD_LAST) {
+                    ep.kout[(long long)(ep.D + 1) * ep.Bs + grow] = (ep.flags & CNF_FLAG_NORM_Z) ? sqrtf(s0) : 0.0f;
+                } else {
+                    ep.kout[(long long)ep.D * ep.Bs + grow] = s0;
+                    ep.kout[(long long)(ep.D + 2) * ep.Bs + grow] = (ep.flags & CNF_FLAG_NORM_J) ? sqrtf(s1) : 0.0f;
+                }
+            }
+            tc::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive(&ctl->tempty[acc]);
+        }
+    }
+    tc::tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tc::tmem_dealloc(tmem, 512);
+}
+
+// ------------------------------------------------------------------ small helper kernels
+// fp32 weights (Julia column-major dout x din) -> bf16 hi/lo planes [rows x ld], zero padded.
+// transpose = 0: plane[o][i] = W[o,i] (forward B operand); 1: plane[i][o] = W[o,i] (VJP B operand)
+__global__ void k_tc_weights(const float* __restrict__ W, int dout, int din, __nv_bfloat16* __restrict__ p0,
+                             __nv_bfloat16* __restrict__ p1, __nv_bfloat16* __restrict__ p2, int rows, int ld,
+                             int transpose) {
+    const long long n = (long long)rows * ld;
+    for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += (long long)gridDim.x * blockDim.x) {
+        int r = (int)(p / ld), c = (int)(p % ld);
+        int o = transpose ? c : r, i = transpose ? r : c;
+        float w = (o < dout && i < din) ? W[(long long)i * dout + o] : 0.0f;
+        __nv_bfloat16 sp[3];
+        tc_split(w, sp);
+        p0[p] = sp[0];
+        p1[p] = sp[1];
+        p2[p] = sp[2];
+    }
+}
+
+struct TcDyn { float* kout; };
+
+// stage input rows (SoA, D x Bs) [+ condition rows] -> bf16 hi/lo planes [mc x ld] of this chunk;
+// also resolves the device-side output buffer of this evaluation (kidx: 0 -> K[k1idx], 6 -> K[6-k1idx])
+__global__ void k_tc_prep(const CnfCtrl* __restrict__ c, CnfBufs bf, const float* __restrict__ src, int nsrc,
+                          const float* __restrict__ src2, int nsrc2, long long row0, int mc,
+                          __nv_bfloat16* __restrict__ p0, __nv_bfloat16* __restrict__ p1,
+                          __nv_bfloat16* __restrict__ p2, int ld, int kidx,
+                          float* kout_fixed, TcDyn* dyn, int check_done) {
+    if (check_done && c->done) return;
+    if (blockIdx.x == 0 && threadIdx.x == 0 && dyn) {
+        float* k = kout_fixed;
+        if (!k) k = (kidx == 6) ? bf.K[6 - c->k1idx] : (kidx == 0 ? bf.K[c->k1idx] : bf.K[kidx]);
+        dyn->kout = k;
+    }
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= mc) return;
+    const long long b = row0 + r;
+    const int ntot = nsrc + nsrc2;
+    for (int c0 = 0; c0 < ntot; c0 += 8) {
+        uint32_t pk[3][4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            __nv_bfloat16 sp[2][3];
+#pragma unroll
+            for (int t = 0; t < 2; ++t) {
+                const int i = c0 + 2 * j + t;
+                float v = 0.0f;
+                if (i < nsrc) v = src[(long long)i * bf.Bs + b];
+                else if (i < ntot) v = src2[(long long)(i - nsrc) * bf.Bs + b];
+                tc_split(v, sp[t]);
+            }
+#pragma unroll
+            for (int q = 0; q < 3; ++q) pk[q][j] = tc_pack(sp[0][q], sp[1][q]);
+        }
+        __nv_bfloat16* dst[3] = {p0, p1, p2};
+#pragma unroll
+        for (int q = 0; q < 3; ++q)
+            *reinterpret_cast<uint4*>(dst[q] + (long long)r * ld + c0) = make_uint4(pk[q][0], pk[q][1], pk[q][2], pk[q][3]);
+    }
+}
+
+// ------------------------------------------------------------------ host side
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static PFN_encodeTiled tc_encode_fn() {
+    static PFN_encodeTiled fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess) fn = (PFN_encodeTiled)p;
+    }
+    return fn;
+}
+// 2D bf16 tensor [rows x cols] row-major (ld elements), box = [box_rows x 64 cols], SWIZZLE_128B
+static bool tc_make_map(CUtensorMap* m, const void* base, long long rows, long long cols, long long ld, int box_rows) {
+    PFN_encodeTiled fn = tc_encode_fn();
+    if (!fn) return false;
+    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+    cuuint32_t box[2] = {TC_BK, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    return fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+static inline int pad_to(int x, int m) { return (x + m - 1) / m * m; }
+
+struct TcPlane {
+    __nv_bfloat16* p[3] = {nullptr, nullptr, nullptr};
+    int rows = 0, ld = 0;
+    CUtensorMap map[3];
+};
+struct TcWeight {
+    TcPlane p;
+    int N = 0, K = 0, BN = 0, n_tiles = 0;
+};
+struct TcState {
+    int L = 0, Mc = 0;
+    TcWeight wf[CNF_MAX_LAYERS], wb[CNF_MAX_LAYERS];
+    TcPlane H[CNF_MAX_LAYERS + 1], G[CNF_MAX_LAYERS + 1];
+    TcDyn* dyn = nullptr;
+    int sms = 148;
+    bool weights_ok = false, acts_ok = false;
+};
+
+static void tc_free_plane(TcPlane& p) {
+    for (int q = 0; q < 3; ++q) { cudaFree(p.p[q]); p.p[q] = nullptr; }
+}
+static int tc_alloc_plane(cnf_handle* h, TcPlane& p, int rows, int ld, int box_rows) {
+    tc_free_plane(p);
+    p.rows = rows; p.ld = ld;
+    size_t bytes = (size_t)rows * ld * sizeof(__nv_bfloat16);
+    for (int q = 0; q < 3; ++q) {
+        CNF_CUDA(cudaMalloc(&p.p[q], bytes));
+        CNF_CUDA(cudaMemsetAsync(p.p[q], 0, bytes, h->stream));
+        if (!tc_make_map(&p.map[q], p.p[q], rows, ld, ld, box_rows)) {
+            h->err = "cuTensorMapEncodeTiled failed";
+            return CNF_ERR_CUDA;
+        }
+    }
+    return CNF_OK;
+}
+
+// the tensor path covers TrainMode (Hutchinson) on chains of >= 2 layers whose hidden widths are
+// multiples of 32 and >= 128 (auto) — or any multiple of 32 when forced with kernel_path = 3
+bool tc_supported(const cnf_config& c, int mode) {
+    if (mode != CNF_MODE_TRAIN || c.n_layers < 2 || c.D > 256) return false;
+    bool wide = true;
+    for (int l = 1; l < c.n_layers; ++l) {
+        if (c.dims[l] % 32 != 0) return false;
+        if (c.dims[l] < 128) wide = false;
+    }
+    return c.kernel_path == 3 || (c.kernel_path == 0 && wide);
+}
+
+void tc_free(cnf_handle* h) {
+    TcState* s = (TcState*)h->tc_state;
+    if (!s) return;
+    for (int l = 0; l < CNF_MAX_LAYERS; ++l) { tc_free_plane(s->wf[l].p); tc_free_plane(s->wb[l].p); }
+    for (int l = 0; l <= CNF_MAX_LAYERS; ++l) { tc_free_plane(s->H[l]); tc_free_plane(s->G[l]); }
+    cudaFree(s->dyn);
+    delete s;
+    h->tc_state = nullptr;
+}
+
+static int tc_setup_weight(cnf_handle* h, TcWeight& w, const float* W, int dout, int din, int transpose, int Nvalid) {
+    // operand B: [N rows x K cols]; forward: N = dout, K = din; VJP: N = din (or D), K = dout
+    w.N = Nvalid;
+    w.K = pad_to(transpose ? dout : din, TC_BK);
+    int n16 = pad_to(Nvalid, 16);
+    w.BN = n16 < 128 ? n16 : 128;   // 3 planes of A and B per stage: 96 KB at BN = 128
+    w.n_tiles = (n16 + w.BN - 1) / w.BN;
+    int rows = w.n_tiles * w.BN;
+    if (w.p.rows != rows || w.p.ld != w.K) {
+        int rc = tc_alloc_plane(h, w.p, rows, w.K, w.BN);
+        if (rc) return rc;
+    }
+    k_tc_weights<<<296, 256, 0, h->stream>>>(W, dout, din, w.p.p[0], w.p.p[1], w.p.p[2], rows, w.K, transpose);
+    h->launches++;
+    return CNF_OK;
+}
+
+// called from set_params (device theta is in place)
+int tc_set_params(cnf_handle* h) {
+    const cnf_config& c = h->cfg;
+    if (!tc_supported(c, CNF_MODE_TRAIN)) return CNF_OK;
+    if (!h->tc_state) {
+        TcState* s = new TcState();
+        h->tc_state = s;
+        cudaDeviceProp prop;
+        if (cudaGetDeviceProperties(&prop, h->device) == cudaSuccess) s->sms = prop.multiProcessorCount;
+        CNF_CUDA(cudaMalloc(&s->dyn, sizeof(TcDyn)));
+        CNF_CUDA(cudaFuncSetAttribute(k_tc_gemm, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    }
+    TcState* s = (TcState*)h->tc_state;
+    s->L = c.n_layers;
+    int rc;
+    for (int l = 0; l < c.n_layers; ++l) {
+        const float* W = h->d_theta + h->w_off[l];
+        int dout = c.dims[l + 1], din = c.dims[l];
+        if ((rc = tc_setup_weight(h, s->wf[l], W, dout, din, 0, dout))) return rc;
+        if ((rc = tc_setup_weight(h, s->wb[l], W, dout, din, 1, l == 0 ? c.D : din))) return rc;
+    }
+    s->weights_ok = true;
+    return CNF_OK;
+}
+
+static int tc_ensure_acts(cnf_handle* h, TcState* s, long long Bs) {
+    const cnf_config& c = h->cfg;
+    // chunk of samples per GEMM launch: as large as a 6 GB activation budget allows (whole waves of
+    // 128-sample tiles), so the per-launch pipeline fill / TMEM allocation is amortised
+    long long sumw = 0;
+    for (int l = 0; l <= c.n_layers; ++l) sumw += 2LL * pad_to(c.dims[l], TC_BK);
+    long long rows_budget = (6LL << 30) / (sumw * 3 * 2);
+    long long wave = (long long)s->sms * TC_BM;
+    long long want = rows_budget / wave * wave;
+    if (want < 2 * wave) want = 2 * wave;
+    if (want > Bs) want = Bs;
+    if (s->acts_ok && s->Mc == (int)want) return CNF_OK;
+    int rc;
+    s->Mc = (int)want;
+    for (int l = 0; l < c.n_layers; ++l)
+        if ((rc = tc_alloc_plane(h, s->H[l], s->Mc, pad_to(c.dims[l], TC_BK), TC_BM))) return rc;
+    for (int l = 1; l <= c.n_layers; ++l)
+        if ((rc = tc_alloc_plane(h, s->G[l], s->Mc, pad_to(c.dims[l], TC_BK), TC_BM))) return rc;
+    if ((rc = tc_alloc_plane(h, s->G[0], s->Mc, pad_to(c.dims[0], TC_BK), TC_BM))) return rc;   // JVP seed planes [eps; 0]
+    s->acts_ok = true;
+    return CNF_OK;
+}
+
+static void tc_launch_gemm(cnf_handle* h, TcState* s, const TcPlane& A, const TcWeight& B, int mc, const TcEpi& ep) {
+    const int m_tiles = mc / TC_BM;
+    const int nk = B.K / TC_BK;
+    const int stage_bytes = TC_NP * (TC_BM * 128 + B.BN * 128);
+    int nstage = (220 * 1024 - 1024) / stage_bytes;
+    if (nstage > 6) nstage = 6;
+    if (nstage < 2) nstage = 2;
+    const int smem = nstage * stage_bytes + 1024 + (int)sizeof(TcSmemCtl) + 64;
+    int grid = m_tiles * B.n_tiles;
+    if (grid > s->sms) grid = s->sms;
+    TcMaps mp;
+    for (int q = 0; q < 3; ++q) { mp.a[q] = A.map[q]; mp.b[q] = B.p.map[q]; }
+    k_tc_gemm<<<grid, TC_THREADS, smem, h->stream>>>(mp, m_tiles, B.n_tiles, B.BN, nk, nstage, ep);
+    h->launches++;
+}
+
+// du = augmented_f(src) in TrainMode on the tensor path.  src: D x Bs z rows (host-known pointer);
+// output buffer either fixed (kout_fixed) or resolved on the device from kidx (FSAL index).
+int tc_eval(cnf_handle* h, const CnfBufs& bf, const float* src, int kidx, float* kout_fixed, int check_done) {
+    TcState* s = (TcState*)h->tc_state;
+    if (!s || !s->weights_ok) { h->err = "tensor path: parameters not set"; return CNF_ERR_UNSUPPORTED; }
+    const cnf_config& c = h->cfg;
+    int rc;
+    if ((rc = tc_ensure_acts(h, s, bf.Bs))) return rc;
+    const int L = c.n_layers;
+    const bool jvp = c.trace_mode == CNF_TRACE_JVP;
+    for (long long row0 = 0; row0 < bf.Bs; row0 += s->Mc) {
+        const int mc = (int)((bf.Bs - row0) < s->Mc ? (bf.Bs - row0) : s->Mc);
+        TcEpi base;
+        memset(&base, 0, sizeof(base));
+        base.eps = bf.eps; base.Bs = bf.Bs; base.row0 = row0; base.D = c.D; base.flags = c.flags;
+        base.kout_ind = &s->dyn->kout;
+        base.ctrl = check_done ? h->d_ctrl : nullptr;
+        // h_0 = [z; ys] planes (+ resolve the output buffer)
+        k_tc_prep<<<(mc + 255) / 256, 256, 0, h->stream>>>(h->d_ctrl, bf, src, c.D, bf.ys, c.C, row0, mc, s->H[0].p[0],
+                                                          s->H[0].p[1], s->H[0].p[2], s->H[0].ld, kidx, kout_fixed, s->dyn, check_done);
+        h->launches++;
+        for (int l = 0; l < L; ++l) {   // forward chain
+            TcEpi ep = base;
+            ep.bias = h->d_theta + h->b_off[l];
+            ep.N = c.dims[l + 1];
+            if (l < L - 1) {
+                ep.kind = TC_FWD_HIDDEN;
+                for (int q = 0; q < 3; ++q) ep.out[q] = s->H[l + 1].p[q];
+                ep.ld_out = s->H[l + 1].ld;
+            } else {
+                ep.kind = TC_FWD_LAST;
+                ep.vjp = jvp ? 0 : 1;
+                for (int q = 0; q < 3; ++q) ep.out[q] = s->G[L].p[q];
+                ep.ld_out = s->G[L].ld;
+            }
+            tc_launch_gemm(h, s, s->H[l], s->wf[l], mc, ep);
+        }
+        if (!jvp) {
+            // reverse chain: g_{l} = (g_{l+1} W_{l+1}) .* (1 - h_l^2), v = (g_1 W_1)[0:D]
+            for (int l = L - 1; l >= 0; --l) {
+                TcEpi ep = base;
+                if (l > 0) {
+                    ep.kind = TC_BWD_HIDDEN;
+                    ep.N = c.dims[l];
+                    for (int q = 0; q < 3; ++q) { ep.hp[q] = s->H[l].p[q]; ep.out[q] = s->G[l].p[q]; }
+                    ep.ld_h = s->H[l].ld; ep.ld_out = s->G[l].ld;
+                } else {
+                    ep.kind = TC_BWD_LAST;
+                    ep.N = c.D;
+                }
+                tc_launch_gemm(h, s, s->G[l + 1], s->wb[l], mc, ep);
+            }
+        } else {
+            // tangent chain: tau_0 = eps, tau_l = (tau_{l-1} W_l^T) .* (1 - h_l^2), J eps = tau_L
+            k_tc_prep<<<(mc + 255) / 256, 256, 0, h->stream>>>(h->d_ctrl, bf, bf.eps, c.D, nullptr, 0, row0, mc,
+                                                              s->G[0].p[0], s->G[0].p[1], s->G[0].p[2], s->G[0].ld, 0,
+                                                              nullptr, nullptr,
+                                                              check_done);
+            h->launches++;
+            for (int l = 0; l < L; ++l) {
+                TcEpi ep = base;
+                ep.N = c.dims[l + 1];
+                if (l < L - 1) {
+                    ep.kind = TC_BWD_HIDDEN;
+                    for (int q = 0; q < 3; ++q) { ep.hp[q] = s->H[l + 1].p[q]; ep.out[q] = s->G[l + 1].p[q]; }
+                    ep.ld_h = s->H[l + 1].ld; ep.ld_out = s->G[l + 1].ld;
+                } else {
+                    ep.kind = TC_JVP_LAST;
+                }
+                // the seed planes G[0] = [eps; 0] have the first layer's padded K width, so the
+                // condition columns of W_1 meet zeros (Jacobian w.r.t. z only)
+                tc_launch_gemm(h, s, l == 0 ? s->G[0] : s->G[l], s->wf[l], mc, ep);
+            }
+        }
+    }
+    return CNF_OK;
+}

@@ -26,7 +26,9 @@ def test_augmented_f(cid, B, trace_mode, mode):
     du = np.asarray(cnf.augmented_f(icnf, m, u.T, *args_of(inp), eps=inp["eps"].T)).T
     ref = O.augmented_f(oracle_cfg(cid, trace_mode=trace_mode), inp["theta"], mode, u, inp["ys"], inp["eps"])
     scale = np.maximum(np.abs(ref).max(axis=0, keepdims=True), 1e-6)
-    assert np.max(np.abs(du - ref) / scale) < 2e-5
+    # tensor path (wide nets, TrainMode) computes the layer GEMMs with BF16x3 operand splitting
+    tol = 1e-4 if (mode == 1 and cid in ("C3", "C4")) else 2e-5
+    assert np.max(np.abs(du - ref) / scale) < tol
 
 
 @pytest.mark.parametrize("cid,B", SMALL)
@@ -109,3 +111,33 @@ def test_device_pointers_match_host_buffers():
     lp_d, _ = cnf.inference(icnf, cnf.TestMode(), xd, inp["theta"], {})
     assert lp_d.is_cuda
     assert np.array_equal(lp_d.cpu().numpy(), lp_h)
+
+
+@pytest.mark.parametrize("cid,B", [("C3", 256), ("C4", 1024)])
+def test_forced_generic_path_on_wide_nets(cid, B):
+    """kernel_path = 1 keeps the FP32 SIMT kernels reachable for the wide configs (and checks that the
+    tensor path and the generic path agree with each other through a whole solve)"""
+    inp = wl.make_inputs(cid, B=B)
+    c = wl.CONFIGS[cid]
+    out = {}
+    for kp in (1, 3):
+        icnf = make_icnf(cid, kernel_path=kp)
+        val, g = cnf.loss_and_grad(icnf, cnf.TrainMode(), inp["xs"].T, *args_of(inp), eps=inp["eps"].T)
+        st = cnf.last_stats(icnf)
+        assert st["kernel_path"] == kp
+        out[kp] = (val, g, st["naccept"])
+    assert abs(out[1][2] - out[3][2]) <= 1
+    if out[1][2] == out[3][2]:
+        assert abs(out[1][0] - out[3][0]) / abs(out[1][0]) < 1e-4
+        assert relnorm(out[3][1], out[1][1]) < 1e-3
+
+
+def test_tensor_path_is_selected_for_wide_train_and_narrow_for_c2():
+    inp = wl.make_inputs("C3", B=256)
+    icnf = make_icnf("C3")
+    cnf.inference(icnf, cnf.TrainMode(), inp["xs"].T, inp["theta"], {}, eps=inp["eps"].T)
+    assert cnf.last_stats(icnf)["kernel_path"] == 3
+    inp = wl.make_inputs("C2", B=256)
+    icnf = make_icnf("C2")
+    cnf.inference(icnf, cnf.TestMode(), inp["xs"].T, inp["theta"], {})
+    assert cnf.last_stats(icnf)["kernel_path"] == 2
