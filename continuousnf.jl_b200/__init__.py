@@ -4,7 +4,8 @@ ContinuousNormalizingFlows.jl behind the reference's own operator interface.
 The directory name contains a dot, so import it through `cnfb200_loader.load_package()` (repo
 root) or importlib; the module registers itself as `cnfb200`.
 """
-from . import _cabi, parallel, workloads  # noqa: F401
+from . import _cabi, adapters, parallel, workloads  # noqa: F401
+from .adapters import CondICNFDist, CondICNFModel, ICNFDist, ICNFModel, Lion, fit, transform  # noqa: F401
 from .api import (  # noqa: F401
     B200Libs, Chain, CondFFJORD, CondRNODE, Dense, DIJacVecMatrixMode, DIJacVecVectorMode,
     DIVecJacMatrixMode, DIVecJacVectorMode, FFJORD, ICNF, RNODE, TestMode, TrainMode, augmented_f,
