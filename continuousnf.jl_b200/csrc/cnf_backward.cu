@@ -294,6 +294,7 @@ static int launch_vjp_generic_stage(cnf_handle* h, const CnfBufs& bf, const floa
 
 // forward re-evaluation used by the stage checkpointing: tensor path when available
 static int bw_eval(cnf_handle* h, const CnfBufs& bf, const float* src, float* kout) {
+    if (tc_bw_supported(h)) return tc_eval_z(h, bf, src, kout);   // only the zdot rows feed the stage inputs
     if (tc_supported(h->cfg, CNF_MODE_TRAIN) && h->tc_state) return tc_eval(h, bf, src, -1, kout, 0);
     return launch_eval_generic(h, bf, CNF_MODE_TRAIN, src, kout);
 }
@@ -315,6 +316,7 @@ static int backward_sweep(cnf_handle* h, const CnfBufs& bf, long long naccept, l
     const float invB = 1.0f / (float)Bglobal;
     const float c_l = invB, c_E = c.lambda1 * invB, c_n = c.lambda2 * invB;
     int rc;
+    const bool tcb = tc_bw_supported(h);
     for (long long n = naccept - 1; n >= 0; --n) {
         const float* un = h->slots[n];
         const float* dtp = h->d_dts + n;
@@ -329,7 +331,9 @@ static int backward_sweep(cnf_handle* h, const CnfBufs& bf, long long naccept, l
         h->launches++;
         for (int i = 5; i >= 0; --i) {
             const float* src = (i == 0) ? un : w[i - 1];
-            if ((rc = launch_vjp_generic_stage(h, bf, src, kb[i], i, dtp, c_l, c_E, c_n, ubar, kb, h->d_grad))) return rc;
+            if (tcb) rc = tc_vjp_stage(h, bf, src, kb[i], i, dtp, c_l, c_E, c_n, ubar, kb, h->d_grad);
+            else rc = launch_vjp_generic_stage(h, bf, src, kb[i], i, dtp, c_l, c_E, c_n, ubar, kb, h->d_grad);
+            if (rc) return rc;
         }
     }
     return CNF_OK;

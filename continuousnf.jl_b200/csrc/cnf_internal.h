@@ -51,6 +51,8 @@ struct cnf_handle {
     long long n_stage = 0;
     int path_used = 0;
     void* tc_state = nullptr;   // tensor-core path state (cnf_stage_tc.cu)
+    bool tc_bw_off = false;     // option "tc_backward" = 0: reverse sweep on the generic SIMT kernels
+    long long wg_lbo = 0, wg_sbo = 0;   // debug override of the MN-major descriptor strides (0 = default)
     void* narrow_w = nullptr;   // host copy of the packed kernel-parameter weights (narrow path)
 };
 
@@ -100,6 +102,12 @@ bool tc_supported(const cnf_config& cfg, int mode);
 int tc_set_params(cnf_handle* h);
 void tc_free(cnf_handle* h);
 int tc_eval(cnf_handle* h, const CnfBufs& bf, const float* src, int kidx, float* kout_fixed, int check_done);
+int tc_eval_z(cnf_handle* h, const CnfBufs& bf, const float* src, float* kout);   // zdot rows only (BF16x3)
+
+// ---- cnf_backward_tc.cu : reverse sweep on the tensor path (VecJac)
+bool tc_bw_supported(cnf_handle* h);
+int tc_vjp_stage(cnf_handle* h, const CnfBufs& bf, const float* src, const float* abar, int stage,
+                 const float* dtp, float c_l, float c_E, float c_n, float* ubar, float** kb, float* grad);
 
 // ---- cnf_nccl.cu
 int cnf_nccl_allreduce_f64(cnf_handle* h, double* dptr, int n);

@@ -4,6 +4,7 @@
 #include "cnf_stage_generic.cu"
 #include "cnf_stage_narrow.cu"
 #include "cnf_stage_tc.cu"
+#include "cnf_backward_tc.cu"
 #include "cnf_backward.cu"
 #include "cnf_nccl.cu"
 #include "cnf_api.cu"

@@ -1,14 +1,16 @@
 // cnf_stage_tc.cu — tensor-core path for wide nets (hidden >= 128, TrainMode Hutchinson).
-// Every layer product of the Dense/tanh chain and of its VJP / JVP chain is a TMA-fed
-// tcgen05.mma GEMM with the batch as the M dimension (128 samples per tile, one TMEM lane per
-// sample), FP32 accumulators in TMEM, and the layer's elementwise work fused into the
-// TMEM->register epilogue (bias + tanh, the (1-h^2) Hadamard factor, the eps dot product and
-// the un-squared norms of reference src/icnf.jl:335-348).
-// Precision: BF16x6 operand splitting (x = p0 + p1 + p2 in bf16; products p0p0 + p1p0 + p0p1 +
-// p1p1 + p2p0 + p0p2, FP32 accumulate) = FP32-level accuracy (1e-8 relative on log-density in
-// scripts/precision_study.py).  BF16x3 (1e-6..4e-6) meets the 1e-4 value tolerance but its 1e-5
-// noise in f is amplified by the abstol = 1e-6 rows of the error norm and changes the accepted-step
-// count by 5-7 steps; plain TF32 (1e-4..2e-4) misses the value tolerance as well.
+// Every layer product of the Dense/tanh chain, of its VJP / JVP chain and (cnf_backward_tc.cu) of
+// the second-order reverse sweep is a TMA-fed tcgen05.mma GEMM with the batch as the M dimension
+// (128 samples per tile, one TMEM lane per sample), FP32 accumulators in TMEM, and the layer's
+// elementwise work fused into the TMEM->register epilogue (bias + tanh, the (1-h^2) Hadamard
+// factor, the eps dot product and the un-squared norms of reference src/icnf.jl:335-348).
+// Precision of the forward solve (NP = 3): BF16x6 operand splitting (x = p0 + p1 + p2 in bf16;
+// products p0p0 + p1p0 + p0p1 + p1p1 + p2p0 + p0p2, FP32 accumulate) = FP32-level accuracy (1e-8
+// relative on log-density in scripts/precision_study.py).  BF16x3 (1e-6..4e-6) meets the 1e-4 value
+// tolerance but its 1e-5 noise in f is amplified by the abstol = 1e-6 rows of the error norm and
+// changes the accepted-step count by 5-7 steps; plain TF32 (1e-4..2e-4) misses the value
+// tolerance as well.  The reverse sweep (gradient tolerance 1e-3) runs BF16x3 (NP = 2: p0p0 + p1p0
+// + p0p1, ~1e-5) with half the MMAs and two thirds of the plane traffic.
 // Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (one elected thread), warps 2..9 =
 // epilogue (two warps per TMEM lane quadrant, half of the columns each); two TMEM accumulator
 // buffers so the epilogue of tile i overlaps the MMAs of tile i+1.
@@ -21,7 +23,17 @@
 #define TC_THREADS 320      // 10 warps
 #define TC_EPI_WARP0 2
 
-enum { TC_FWD_HIDDEN = 0, TC_FWD_LAST = 1, TC_BWD_HIDDEN = 2, TC_BWD_LAST = 3, TC_JVP_LAST = 4 };
+enum {
+    TC_FWD_HIDDEN = 0, TC_FWD_LAST = 1, TC_BWD_HIDDEN = 2, TC_BWD_LAST = 3, TC_JVP_LAST = 4,
+    // reverse-sweep kinds (VecJac; maths in DESIGN.md "Backward")
+    TCB_FWD_LAST = 8,      // y, g_L = eps (1-y^2), ybar = abar + beta y/|y|
+    TCB_BWD_HIDDEN = 9,    // q_{l+1} kept (fp32), g_l = q_{l+1} (1-h_l^2)
+    TCB_BWD_LAST = 10,     // v -> vbar = -alpha eps + gamma v/|v|  (planes of qbar_1)
+    TCB_GBAR_HIDDEN = 11,  // gbar_l: dbar_l = gbar_l q_{l+1} (fp32, in place), qbar_{l+1} = gbar_l (1-h_l^2)
+    TCB_GBAR_LAST = 12,    // gbar_L: dbar_L = gbar_L eps, pbar_L = (ybar - 2 y dbar_L)(1-y^2)
+    TCB_HBAR_HIDDEN = 13,  // hbar_l: pbar_l = (hbar_l - 2 h_l dbar_l)(1-h_l^2)
+    TCB_ZBAR = 14          // zbar: ubar += zbar, kbar_j += dt a_ij zbar
+};
 
 struct TcEpi {
     int kind;
@@ -39,10 +51,20 @@ struct TcEpi {
     long long row0;                // first sample of this chunk
     int D;
     unsigned flags;
-    int vjp;                       // FWD_LAST: also emit g_L = eps .* (1-y^2) planes
+    int vjp;                       // FWD_LAST: also emit g_L = eps .* (1-y^2) planes; 2: z rows only
+    // ---- reverse sweep
+    float* f32a;                   // fp32 side array [rows x ld_f] (q_{l+1} / dbar_l ; y)
+    float* f32b;                   // second fp32 side array (ybar)
+    int ld_f;
+    const float* abar;             // D x Bs cotangent of this stage's zdot rows
+    float* ubar;                   // D x Bs
+    float* kb[5];                  // cotangents of the earlier stages
+    const float* dtp;              // accepted dt of this step (device)
+    int stage;                     // 0..5
+    float c_l, c_E, c_n;           // cotangents of the quadrature rows (1/B, lambda1/B, lambda2/B)
+    int B;                         // live samples (rows >= B are padding)
 };
 
-#define TC_NP 3   // bf16 planes per operand
 __device__ __forceinline__ void tc_split(float x, __nv_bfloat16 (&p)[3]) {
     p[0] = __float2bfloat16_rn(x);
     float r = x - __bfloat162float(p[0]);
@@ -62,29 +84,31 @@ struct TcSmemCtl {
 };
 
 // ---- epilogue helpers: one thread = one sample row; v = 32 accumulator columns c0..c0+31
+template <int NP>
 __device__ __forceinline__ void tc_store_planes32(const float (&x)[32], __nv_bfloat16* const (&dst)[3], long long off) {
-    uint32_t pk[3][16];
+    uint32_t pk[NP][16];
 #pragma unroll
     for (int j = 0; j < 16; ++j) {
         __nv_bfloat16 a[3], b[3];
         tc_split(x[2 * j], a);
         tc_split(x[2 * j + 1], b);
 #pragma unroll
-        for (int q = 0; q < 3; ++q) pk[q][j] = tc_pack(a[q], b[q]);
+        for (int q = 0; q < NP; ++q) pk[q][j] = tc_pack(a[q], b[q]);
     }
 #pragma unroll
-    for (int q = 0; q < 3; ++q) {
+    for (int q = 0; q < NP; ++q) {
         uint4* d = reinterpret_cast<uint4*>(dst[q] + off);
 #pragma unroll
         for (int j = 0; j < 4; ++j) d[j] = make_uint4(pk[q][4 * j], pk[q][4 * j + 1], pk[q][4 * j + 2], pk[q][4 * j + 3]);
     }
 }
 
+template <int NP>
 __device__ __forceinline__ void tc_load_planes32(const __nv_bfloat16* const (&src)[3], long long off, float (&h)[32]) {
 #pragma unroll
     for (int j = 0; j < 32; ++j) h[j] = 0.0f;
 #pragma unroll
-    for (int q = 2; q >= 0; --q) {   // smallest plane first
+    for (int q = NP - 1; q >= 0; --q) {   // smallest plane first
         const uint4* sp = reinterpret_cast<const uint4*>(src[q] + off);
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -99,7 +123,240 @@ __device__ __forceinline__ void tc_load_planes32(const __nv_bfloat16* const (&sr
     }
 }
 
+__device__ __forceinline__ void tc_load_f32x32(const float* src, float (&x)[32]) {
+    const float4* p = reinterpret_cast<const float4*>(src);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        float4 v = p[j];
+        x[4 * j] = v.x; x[4 * j + 1] = v.y; x[4 * j + 2] = v.z; x[4 * j + 3] = v.w;
+    }
+}
+__device__ __forceinline__ void tc_store_f32x32(float* dst, const float (&x)[32]) {
+    float4* p = reinterpret_cast<float4*>(dst);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) p[j] = make_float4(x[4 * j], x[4 * j + 1], x[4 * j + 2], x[4 * j + 3]);
+}
+
+// ---- forward-solve epilogue of one 128 x BN tile (kinds TC_*)
+template <int NP>
+__device__ __forceinline__ void tc_epilogue_fwd(const TcEpi& ep, uint32_t tbase, int mb, int nb, int BN,
+                                                int quad, int half, int lane) {
+    const long long rloc = (long long)mb * TC_BM + quad * 32 + lane;   // row inside the chunk
+    const long long grow = ep.row0 + rloc;                               // global sample
+    const bool last_kind = (ep.kind == TC_FWD_LAST || ep.kind == TC_BWD_LAST || ep.kind == TC_JVP_LAST);
+    const int nchunk = (BN + 31) / 32;
+    if (!last_kind) {
+        // column chunks are split between the two warps of a quadrant
+        for (int ch = half; ch < nchunk; ch += 2) {
+            const int c0 = ch * 32, ng = nb * BN + c0;   // global column of v[0]
+            uint32_t v[32];
+            tc::tmem_ld_32x32(tbase + c0, v);
+            tc::tmem_ld_wait();
+            if (ng >= ep.N) continue;
+            float x[32];
+            if (ep.kind == TC_FWD_HIDDEN) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) x[j] = cnf_tanh_fastpath(__uint_as_float(v[j]) + __ldg(ep.bias + ng + j));
+            } else {   // BWD_HIDDEN: acc .* (1 - h^2)
+                float h[32];
+                tc_load_planes32<NP>(ep.hp, rloc * ep.ld_h + ng, h);
+#pragma unroll
+                for (int j = 0; j < 32; ++j) x[j] = __uint_as_float(v[j]) * fmaf(-h[j], h[j], 1.0f);
+            }
+            tc_store_planes32<NP>(x, ep.out, rloc * ep.ld_out + ng);
+        }
+    } else if (half == 0) {
+        // per-sample reductions over all D columns: one warp per quadrant walks every chunk
+        float s0 = 0.0f, s1 = 0.0f;
+        for (int ch = 0; ch < nchunk; ++ch) {
+            const int c0 = ch * 32;
+            uint32_t v[32];
+            tc::tmem_ld_32x32(tbase + c0, v);
+            tc::tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                const int n = c0 + j;
+                if (n < ep.D) {
+                    const float a = __uint_as_float(v[j]);
+                    if (ep.kind == TC_FWD_LAST) {
+                        const float y = cnf_tanh_fastpath(a + __ldg(ep.bias + n));
+                        ep.kout[(long long)n * ep.Bs + grow] = y;
+                        s0 = fmaf(y, y, s0);
+                        if (ep.vjp == 1) {
+                            const float g = ep.eps[(long long)n * ep.Bs + grow] * fmaf(-y, y, 1.0f);
+                            __nv_bfloat16 gp[3];
+                            tc_split(g, gp);
+#pragma unroll
+                            for (int q = 0; q < NP; ++q) ep.out[q][rloc * ep.ld_out + n] = gp[q];
+                        }
+                    } else {
+                        float vv = a;
+                        if (ep.kind == TC_JVP_LAST) {
+                            const float y = ep.kout[(long long)n * ep.Bs + grow];
+                            vv = a * fmaf(-y, y, 1.0f);
+                        }
+                        s0 = fmaf(-vv, ep.eps[(long long)n * ep.Bs + grow], s0);
+                        s1 = fmaf(vv, vv, s1);
+                    }
+                }
+            }
+        }
+        if (ep.kind == TC_FWD_LAST) {
+            if (ep.vjp != 2)
+                ep.kout[(long long)(ep.D + 1) * ep.Bs + grow] = (ep.flags & CNF_FLAG_NORM_Z) ? sqrtf(s0) : 0.0f;
+        } else {
+            ep.kout[(long long)ep.D * ep.Bs + grow] = s0;
+            ep.kout[(long long)(ep.D + 2) * ep.Bs + grow] = (ep.flags & CNF_FLAG_NORM_J) ? sqrtf(s1) : 0.0f;
+        }
+    }
+}
+
+// ---- reverse-sweep epilogue of one 128 x BN tile (kinds TCB_*, two bf16 planes)
+__device__ __forceinline__ void tc_epilogue_bwd(const TcEpi& ep, uint32_t tbase, int mb, int nb, int BN,
+                                                int quad, int half, int lane) {
+    const long long rloc = (long long)mb * TC_BM + quad * 32 + lane;
+    const long long grow = ep.row0 + rloc;
+    const bool live = grow < (long long)ep.B;
+    const int nchunk = (BN + 31) / 32;
+    const float dt = *ep.dtp;
+    const float wgt = dt * c_A[6][ep.stage];
+    if (ep.kind == TCB_FWD_LAST) {
+        if (half != 0) return;
+        float s0 = 0.0f;
+        for (int ch = 0; ch < nchunk; ++ch) {
+            const int c0 = ch * 32;
+            uint32_t v[32];
+            tc::tmem_ld_32x32(tbase + c0, v);
+            tc::tmem_ld_wait();
+            float y[32], g[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                const int n = c0 + j;
+                y[j] = 0.0f; g[j] = 0.0f;
+                if (n < ep.D) {
+                    y[j] = cnf_tanh_fastpath(__uint_as_float(v[j]) + __ldg(ep.bias + n));
+                    s0 = fmaf(y[j], y[j], s0);
+                    g[j] = ep.eps[(long long)n * ep.Bs + grow] * fmaf(-y[j], y[j], 1.0f);
+                }
+            }
+            tc_store_f32x32(ep.f32a + rloc * ep.ld_f + c0, y);
+            tc_store_planes32<2>(g, ep.out, rloc * ep.ld_out + c0);
+        }
+        const float inv = (live && (ep.flags & CNF_FLAG_NORM_Z) && s0 > 0.0f) ? wgt * ep.c_E / sqrtf(s0) : 0.0f;
+        for (int ch = 0; ch < nchunk; ++ch) {
+            const int c0 = ch * 32;
+            float y[32], yb[32];
+            tc_load_f32x32(ep.f32a + rloc * ep.ld_f + c0, y);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                const int n = c0 + j;
+                yb[j] = (live && n < ep.D) ? fmaf(inv, y[j], ep.abar[(long long)n * ep.Bs + grow]) : 0.0f;
+            }
+            tc_store_f32x32(ep.f32b + rloc * ep.ld_f + c0, yb);
+        }
+        return;
+    }
+    if (ep.kind == TCB_BWD_LAST) {
+        if (half != 0) return;
+        float s1 = 0.0f;
+        for (int ch = 0; ch < nchunk; ++ch) {
+            const int c0 = ch * 32;
+            uint32_t v[32];
+            tc::tmem_ld_32x32(tbase + c0, v);
+            tc::tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+                if (c0 + j < ep.D) s1 = fmaf(__uint_as_float(v[j]), __uint_as_float(v[j]), s1);
+        }
+        const float inv = (live && (ep.flags & CNF_FLAG_NORM_J) && s1 > 0.0f) ? wgt * ep.c_n / sqrtf(s1) : 0.0f;
+        const float al = live ? wgt * ep.c_l : 0.0f;
+        for (int ch = 0; ch < nchunk; ++ch) {
+            const int c0 = ch * 32;
+            uint32_t v[32];
+            tc::tmem_ld_32x32(tbase + c0, v);
+            tc::tmem_ld_wait();
+            float x[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                const int n = c0 + j;
+                x[j] = (n < ep.D) ? fmaf(inv, __uint_as_float(v[j]), -al * ep.eps[(long long)n * ep.Bs + grow]) : 0.0f;
+            }
+            tc_store_planes32<2>(x, ep.out, rloc * ep.ld_out + c0);
+        }
+        return;
+    }
+    // column-wise kinds: chunks are split between the two warps of a quadrant
+    for (int ch = half; ch < nchunk; ch += 2) {
+        const int c0 = ch * 32, ng = nb * BN + c0;
+        uint32_t v[32];
+        tc::tmem_ld_32x32(tbase + c0, v);
+        tc::tmem_ld_wait();
+        if (ng >= ep.N) continue;
+        float x[32];
+        if (ep.kind == TCB_ZBAR) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                const int n = ng + j;
+                if (n < ep.D) {
+                    const float zb = __uint_as_float(v[j]);
+                    const long long at = (long long)n * ep.Bs + grow;
+                    ep.ubar[at] += zb;
+#pragma unroll
+                    for (int s = 0; s < 5; ++s)
+                        if (s < ep.stage) ep.kb[s][at] = fmaf(dt * c_A[ep.stage][s], zb, ep.kb[s][at]);
+                }
+            }
+            continue;
+        }
+        if (ep.kind == TCB_GBAR_LAST) {
+            float y[32], yb[32];
+            tc_load_f32x32(ep.f32a + rloc * ep.ld_f + ng, y);
+            tc_load_f32x32(ep.f32b + rloc * ep.ld_f + ng, yb);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                const int n = ng + j;
+                x[j] = 0.0f;
+                if (n < ep.D) {
+                    const float db = __uint_as_float(v[j]) * ep.eps[(long long)n * ep.Bs + grow];
+                    x[j] = fmaf(-2.0f * y[j], db, yb[j]) * fmaf(-y[j], y[j], 1.0f);
+                }
+            }
+        } else {
+            float h[32];
+            tc_load_planes32<2>(ep.hp, rloc * ep.ld_h + ng, h);
+            if (ep.kind == TCB_BWD_HIDDEN) {
+                float q[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    q[j] = __uint_as_float(v[j]);
+                    x[j] = q[j] * fmaf(-h[j], h[j], 1.0f);
+                }
+                tc_store_f32x32(ep.f32a + rloc * ep.ld_f + ng, q);
+            } else if (ep.kind == TCB_GBAR_HIDDEN) {
+                float q[32];
+                tc_load_f32x32(ep.f32a + rloc * ep.ld_f + ng, q);
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    const float gb = __uint_as_float(v[j]);
+                    q[j] *= gb;                                // dbar_l
+                    x[j] = gb * fmaf(-h[j], h[j], 1.0f);      // qbar_{l+1}
+                }
+                tc_store_f32x32(ep.f32a + rloc * ep.ld_f + ng, q);
+            } else {   // TCB_HBAR_HIDDEN
+                float db[32];
+                tc_load_f32x32(ep.f32a + rloc * ep.ld_f + ng, db);
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                    x[j] = fmaf(-2.0f * h[j], db[j], __uint_as_float(v[j])) * fmaf(-h[j], h[j], 1.0f);
+            }
+        }
+        tc_store_planes32<2>(x, ep.out, rloc * ep.ld_out + ng);
+    }
+}
+
 // BM x BN output tile per (m_blk, n_blk); K in blocks of 64 bf16; persistent over tiles.
+// NP = bf16 planes per operand (3: BF16x6 forward solve, 2: BF16x3 reverse sweep).
+template <int NP, bool BWD>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, int nk, int nstage, TcEpi ep) {
     if (ep.ctrl && ep.ctrl->done) return;
@@ -108,13 +365,13 @@ k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, i
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     const uint32_t a_bytes = TC_BM * 128;          // one plane of A per stage
     const uint32_t b_bytes = (uint32_t)BN * 128;   // one plane of B per stage
-    const uint32_t stage_bytes = TC_NP * (a_bytes + b_bytes);
+    const uint32_t stage_bytes = NP * (a_bytes + b_bytes);
     TcSmemCtl* ctl = reinterpret_cast<TcSmemCtl*>(smem + (size_t)nstage * stage_bytes);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int total = m_tiles * n_tiles;
 
     if (warp == 0 && lane == 0) {
-        for (int q = 0; q < TC_NP; ++q) { tc::tma_prefetch_desc(&mp.a[q]); tc::tma_prefetch_desc(&mp.b[q]); }
+        for (int q = 0; q < NP; ++q) { tc::tma_prefetch_desc(&mp.a[q]); tc::tma_prefetch_desc(&mp.b[q]); }
         for (int s = 0; s < nstage; ++s) { tc::mbar_init(&ctl->full[s], 1); tc::mbar_init(&ctl->empty[s], 1); }
         for (int a = 0; a < 2; ++a) { tc::mbar_init(&ctl->tfull[a], 1); tc::mbar_init(&ctl->tempty[a], 8); }
         tc::fence_barrier_init();
@@ -134,9 +391,9 @@ k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, i
                     tc::mbar_wait(&ctl->empty[stage], phase ^ 1);
                     uint8_t* s = smem + (size_t)stage * stage_bytes;
                     tc::mbar_arrive_expect_tx(&ctl->full[stage], stage_bytes);
-                    for (int q = 0; q < TC_NP; ++q) {
+                    for (int q = 0; q < NP; ++q) {
                         tc::tma_load_2d(&mp.a[q], &ctl->full[stage], s + q * a_bytes, kb * TC_BK, mb * TC_BM);
-                        tc::tma_load_2d(&mp.b[q], &ctl->full[stage], s + TC_NP * a_bytes + q * b_bytes, kb * TC_BK, nb * BN);
+                        tc::tma_load_2d(&mp.b[q], &ctl->full[stage], s + NP * a_bytes + q * b_bytes, kb * TC_BK, nb * BN);
                     }
                     if (++stage == nstage) { stage = 0; phase ^= 1; }
                 }
@@ -157,19 +414,20 @@ k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, i
                     const uint32_t s = tc::smem_u32(smem + (size_t)stage * stage_bytes);
 #pragma unroll
                     for (int kk = 0; kk < TC_BK / 16; ++kk) {
-                        uint64_t a[TC_NP], b[TC_NP];
+                        uint64_t a[NP], b[NP];
 #pragma unroll
-                        for (int q = 0; q < TC_NP; ++q) {
+                        for (int q = 0; q < NP; ++q) {
                             a[q] = tc::umma_desc_sw128(s + q * a_bytes + kk * 32);
-                            b[q] = tc::umma_desc_sw128(s + TC_NP * a_bytes + q * b_bytes + kk * 32);
+                            b[q] = tc::umma_desc_sw128(s + NP * a_bytes + q * b_bytes + kk * 32);
                         }
-                        // BF16x6: all products down to 2^-24 relative
                         tc::umma_bf16(dcol, a[0], b[0], idesc, (kb | kk) != 0);
                         tc::umma_bf16(dcol, a[1], b[0], idesc, 1);
                         tc::umma_bf16(dcol, a[0], b[1], idesc, 1);
-                        tc::umma_bf16(dcol, a[1], b[1], idesc, 1);
-                        tc::umma_bf16(dcol, a[2], b[0], idesc, 1);
-                        tc::umma_bf16(dcol, a[0], b[2], idesc, 1);
+                        if (NP == 3) {   // BF16x6: all products down to 2^-24 relative
+                            tc::umma_bf16(dcol, a[1], b[1], idesc, 1);
+                            tc::umma_bf16(dcol, a[NP - 1], b[0], idesc, 1);
+                            tc::umma_bf16(dcol, a[0], b[NP - 1], idesc, 1);
+                        }
                     }
                     tc::umma_commit(&ctl->empty[stage]);
                     if (++stage == nstage) { stage = 0; phase ^= 1; }
@@ -187,74 +445,9 @@ k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, i
             const int acc = it & 1;
             tc::mbar_wait(&ctl->tfull[acc], (it >> 1) & 1);
             tc::tc_fence_after();
-            const long long rloc = (long long)mb * TC_BM + quad * 32 + lane;   // row inside the chunk
-            const long long grow = ep.row0 + rloc;                               // global sample
             const uint32_t tbase = tmem + ((uint32_t)(quad * 32) << 16) + (uint32_t)acc * 256;
-            const bool last_kind = (ep.kind == TC_FWD_LAST || ep.kind == TC_BWD_LAST || ep.kind == TC_JVP_LAST);
-            const int nchunk = (BN + 31) / 32;
-            if (!last_kind) {
-                // column chunks are split between the two warps of a quadrant
-                for (int ch = half; ch < nchunk; ch += 2) {
-                    const int c0 = ch * 32, ng = nb * BN + c0;   // global column of v[0]
-                    uint32_t v[32];
-                    tc::tmem_ld_32x32(tbase + c0, v);
-                    tc::tmem_ld_wait();
-                    if (ng >= ep.N) continue;
-                    float x[32];
-                    if (ep.kind == TC_FWD_HIDDEN) {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) x[j] = cnf_tanh_fastpath(__uint_as_float(v[j]) + __ldg(ep.bias + ng + j));
-                    } else {   // BWD_HIDDEN: acc .* (1 - h^2)
-                        float h[32];
-                        tc_load_planes32(ep.hp, rloc * ep.ld_h + ng, h);
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) x[j] = __uint_as_float(v[j]) * fmaf(-h[j], h[j], 1.0f);
-                    }
-                    tc_store_planes32(x, ep.out, rloc * ep.ld_out + ng);
-                }
-            } else if (half == 0) {
-                // per-sample reductions over all D columns: one warp per quadrant walks every chunk
-                float s0 = 0.0f, s1 = 0.0f;
-                for (int ch = 0; ch < nchunk; ++ch) {
-                    const int c0 = ch * 32;
-                    uint32_t v[32];
-                    tc::tmem_ld_32x32(tbase + c0, v);
-                    tc::tmem_ld_wait();
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        const int n = c0 + j;
-                        if (n < ep.D) {
-                            const float a = __uint_as_float(v[j]);
-                            if (ep.kind == TC_FWD_LAST) {
-                                const float y = cnf_tanh_fastpath(a + __ldg(ep.bias + n));
-                                ep.kout[(long long)n * ep.Bs + grow] = y;
-                                s0 = fmaf(y, y, s0);
-                                if (ep.vjp) {
-                                    const float g = ep.eps[(long long)n * ep.Bs + grow] * fmaf(-y, y, 1.0f);
-                                    __nv_bfloat16 gp[3];
-                                    tc_split(g, gp);
-#pragma unroll
-                                    for (int q = 0; q < 3; ++q) ep.out[q][rloc * ep.ld_out + n] = gp[q];
-                                }
-                            } else {
-                                float vv = a;
-                                if (ep.kind == TC_JVP_LAST) {
-                                    const float y = ep.kout[(long long)n * ep.Bs + grow];
-                                    vv = a * fmaf(-y, y, 1.0f);
-                                }
-                                s0 = fmaf(-vv, ep.eps[(long long)n * ep.Bs + grow], s0);
-                                s1 = fmaf(vv, vv, s1);
-                            }
-                        }
-                    }
-                }
-                if (ep.kind == TC_FWD_LAST) {
-                    ep.kout[(long long)(ep.D + 1) * ep.Bs + grow] = (ep.flags & CNF_FLAG_NORM_Z) ? sqrtf(s0) : 0.0f;
-                } else {
-                    ep.kout[(long long)ep.D * ep.Bs + grow] = s0;
-                    ep.kout[(long long)(ep.D + 2) * ep.Bs + grow] = (ep.flags & CNF_FLAG_NORM_J) ? sqrtf(s1) : 0.0f;
-                }
-            }
+            if (BWD) tc_epilogue_bwd(ep, tbase, mb, nb, BN, quad, half, lane);
+            else tc_epilogue_fwd<NP>(ep, tbase, mb, nb, BN, quad, half, lane);
             tc::tc_fence_before();
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(&ctl->tempty[acc]);
@@ -356,17 +549,29 @@ static inline int pad_to(int x, int m) { return (x + m - 1) / m * m; }
 
 struct TcPlane {
     __nv_bfloat16* p[3] = {nullptr, nullptr, nullptr};
-    int rows = 0, ld = 0;
-    CUtensorMap map[3];
+    int rows = 0, ld = 0, np = 0;
+    CUtensorMap map[3];    // box [128 rows x 64 cols]: K-major A operand of the layer GEMMs
+    CUtensorMap mapk[3];   // box [ 64 rows x 64 cols]: MN-major operand of the weight-gradient GEMMs
 };
 struct TcWeight {
     TcPlane p;
-    int N = 0, K = 0, BN = 0, n_tiles = 0;
+    int N = 0, K = 0;
+    int BN[2] = {0, 0}, n_tiles[2] = {0, 0};   // variant 0: NP = 3 (BN <= 128), 1: NP = 2 (BN <= 256)
+    CUtensorMap mapv[2][3];
+};
+struct TcF32 {
+    float* p = nullptr;
+    int rows = 0, ld = 0;
 };
 struct TcState {
     int L = 0, Mc = 0;
     TcWeight wf[CNF_MAX_LAYERS], wb[CNF_MAX_LAYERS];
     TcPlane H[CNF_MAX_LAYERS + 1], G[CNF_MAX_LAYERS + 1];
+    // reverse sweep (cnf_backward_tc.cu): qbar_l, pbar_l planes (l = 1..L), q_{l+1}/dbar_l (l = 1..L-1), y, ybar
+    TcPlane QB[CNF_MAX_LAYERS + 1], PB[CNF_MAX_LAYERS + 1];
+    TcF32 Q[CNF_MAX_LAYERS + 1], Y, YB;
+    __nv_bfloat16* ones = nullptr;   // 2 KB of bf16 1.0: B operand of the bias-gradient MMAs
+    bool bw_ok = false;
     TcDyn* dyn = nullptr;
     int sms = 148;
     bool weights_ok = false, acts_ok = false;
@@ -374,19 +579,29 @@ struct TcState {
 
 static void tc_free_plane(TcPlane& p) {
     for (int q = 0; q < 3; ++q) { cudaFree(p.p[q]); p.p[q] = nullptr; }
+    p.rows = p.ld = p.np = 0;
 }
-static int tc_alloc_plane(cnf_handle* h, TcPlane& p, int rows, int ld, int box_rows) {
+static void tc_free_f32(TcF32& f) { cudaFree(f.p); f.p = nullptr; f.rows = f.ld = 0; }
+static int tc_alloc_plane(cnf_handle* h, TcPlane& p, int rows, int ld, int box_rows, int np = 3, bool kmap = true) {
     tc_free_plane(p);
-    p.rows = rows; p.ld = ld;
+    p.rows = rows; p.ld = ld; p.np = np;
     size_t bytes = (size_t)rows * ld * sizeof(__nv_bfloat16);
-    for (int q = 0; q < 3; ++q) {
+    for (int q = 0; q < np; ++q) {
         CNF_CUDA(cudaMalloc(&p.p[q], bytes));
         CNF_CUDA(cudaMemsetAsync(p.p[q], 0, bytes, h->stream));
-        if (!tc_make_map(&p.map[q], p.p[q], rows, ld, ld, box_rows)) {
+        if (!tc_make_map(&p.map[q], p.p[q], rows, ld, ld, box_rows) ||
+            (kmap && !tc_make_map(&p.mapk[q], p.p[q], rows, ld, ld, 64))) {
             h->err = "cuTensorMapEncodeTiled failed";
             return CNF_ERR_CUDA;
         }
     }
+    return CNF_OK;
+}
+static int tc_alloc_f32(cnf_handle* h, TcF32& f, int rows, int ld) {
+    tc_free_f32(f);
+    f.rows = rows; f.ld = ld;
+    CNF_CUDA(cudaMalloc(&f.p, (size_t)rows * ld * sizeof(float)));
+    CNF_CUDA(cudaMemsetAsync(f.p, 0, (size_t)rows * ld * sizeof(float), h->stream));
     return CNF_OK;
 }
 
@@ -406,7 +621,12 @@ void tc_free(cnf_handle* h) {
     TcState* s = (TcState*)h->tc_state;
     if (!s) return;
     for (int l = 0; l < CNF_MAX_LAYERS; ++l) { tc_free_plane(s->wf[l].p); tc_free_plane(s->wb[l].p); }
-    for (int l = 0; l <= CNF_MAX_LAYERS; ++l) { tc_free_plane(s->H[l]); tc_free_plane(s->G[l]); }
+    for (int l = 0; l <= CNF_MAX_LAYERS; ++l) {
+        tc_free_plane(s->H[l]); tc_free_plane(s->G[l]); tc_free_plane(s->QB[l]); tc_free_plane(s->PB[l]);
+        tc_free_f32(s->Q[l]);
+    }
+    tc_free_f32(s->Y); tc_free_f32(s->YB);
+    cudaFree(s->ones);
     cudaFree(s->dyn);
     delete s;
     h->tc_state = nullptr;
@@ -416,13 +636,23 @@ static int tc_setup_weight(cnf_handle* h, TcWeight& w, const float* W, int dout,
     // operand B: [N rows x K cols]; forward: N = dout, K = din; VJP: N = din (or D), K = dout
     w.N = Nvalid;
     w.K = pad_to(transpose ? dout : din, TC_BK);
-    int n16 = pad_to(Nvalid, 16);
-    w.BN = n16 < 128 ? n16 : 128;   // 3 planes of A and B per stage: 96 KB at BN = 128
-    w.n_tiles = (n16 + w.BN - 1) / w.BN;
-    int rows = w.n_tiles * w.BN;
+    const int n16 = pad_to(Nvalid, 16);
+    int rows = 0;
+    for (int v = 0; v < 2; ++v) {
+        const int cap = v == 0 ? 128 : 256;   // NP = 3: 3 planes of A and B per stage, 96 KB at BN = 128
+        w.BN[v] = n16 < cap ? n16 : cap;
+        w.n_tiles[v] = (n16 + w.BN[v] - 1) / w.BN[v];
+        if (w.n_tiles[v] * w.BN[v] > rows) rows = w.n_tiles[v] * w.BN[v];
+    }
     if (w.p.rows != rows || w.p.ld != w.K) {
-        int rc = tc_alloc_plane(h, w.p, rows, w.K, w.BN);
+        int rc = tc_alloc_plane(h, w.p, rows, w.K, w.BN[0], 3, false);
         if (rc) return rc;
+        for (int v = 0; v < 2; ++v)
+            for (int q = 0; q < 3; ++q)
+                if (!tc_make_map(&w.mapv[v][q], w.p.p[q], rows, w.K, w.K, w.BN[v])) {
+                    h->err = "cuTensorMapEncodeTiled failed";
+                    return CNF_ERR_CUDA;
+                }
     }
     k_tc_weights<<<296, 256, 0, h->stream>>>(W, dout, din, w.p.p[0], w.p.p[1], w.p.p[2], rows, w.K, transpose);
     h->launches++;
@@ -439,7 +669,9 @@ int tc_set_params(cnf_handle* h) {
         cudaDeviceProp prop;
         if (cudaGetDeviceProperties(&prop, h->device) == cudaSuccess) s->sms = prop.multiProcessorCount;
         CNF_CUDA(cudaMalloc(&s->dyn, sizeof(TcDyn)));
-        CNF_CUDA(cudaFuncSetAttribute(k_tc_gemm, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        CNF_CUDA(cudaFuncSetAttribute(k_tc_gemm<3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        CNF_CUDA(cudaFuncSetAttribute(k_tc_gemm<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        CNF_CUDA(cudaFuncSetAttribute(k_tc_gemm<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     }
     TcState* s = (TcState*)h->tc_state;
     s->L = c.n_layers;
@@ -454,13 +686,21 @@ int tc_set_params(cnf_handle* h) {
     return CNF_OK;
 }
 
+// bytes of activation workspace per sample row: forward planes (3) + reverse-sweep planes (2) and fp32 side arrays
+static long long tc_row_bytes(const cnf_config& c) {
+    long long b = 0;
+    for (int l = 0; l <= c.n_layers; ++l) b += 2LL * pad_to(c.dims[l], TC_BK) * 3 * 2;
+    for (int l = 1; l <= c.n_layers; ++l) b += (long long)(pad_to(c.dims[l - 1], TC_BK) + pad_to(c.dims[l], TC_BK)) * 2 * 2;
+    for (int l = 1; l < c.n_layers; ++l) b += 4LL * pad_to(c.dims[l], TC_BK);
+    b += 8LL * pad_to(c.D, TC_BK);
+    return b;
+}
+
 static int tc_ensure_acts(cnf_handle* h, TcState* s, long long Bs) {
     const cnf_config& c = h->cfg;
-    // chunk of samples per GEMM launch: as large as a 6 GB activation budget allows (whole waves of
+    // chunk of samples per GEMM launch: as large as a 16 GB activation budget allows (whole waves of
     // 128-sample tiles), so the per-launch pipeline fill / TMEM allocation is amortised
-    long long sumw = 0;
-    for (int l = 0; l <= c.n_layers; ++l) sumw += 2LL * pad_to(c.dims[l], TC_BK);
-    long long rows_budget = (6LL << 30) / (sumw * 3 * 2);
+    long long rows_budget = (16LL << 30) / tc_row_bytes(c);
     long long wave = (long long)s->sms * TC_BM;
     long long want = rows_budget / wave * wave;
     if (want < 2 * wave) want = 2 * wave;
@@ -468,6 +708,7 @@ static int tc_ensure_acts(cnf_handle* h, TcState* s, long long Bs) {
     if (s->acts_ok && s->Mc == (int)want) return CNF_OK;
     int rc;
     s->Mc = (int)want;
+    s->bw_ok = false;
     for (int l = 0; l < c.n_layers; ++l)
         if ((rc = tc_alloc_plane(h, s->H[l], s->Mc, pad_to(c.dims[l], TC_BK), TC_BM))) return rc;
     for (int l = 1; l <= c.n_layers; ++l)
@@ -477,20 +718,48 @@ static int tc_ensure_acts(cnf_handle* h, TcState* s, long long Bs) {
     return CNF_OK;
 }
 
+template <int NP, bool BWD>
 static void tc_launch_gemm(cnf_handle* h, TcState* s, const TcPlane& A, const TcWeight& B, int mc, const TcEpi& ep) {
+    const int v = NP == 2 ? 1 : 0;
+    const int BN = B.BN[v], n_tiles = B.n_tiles[v];
     const int m_tiles = mc / TC_BM;
     const int nk = B.K / TC_BK;
-    const int stage_bytes = TC_NP * (TC_BM * 128 + B.BN * 128);
+    const int stage_bytes = NP * (TC_BM * 128 + BN * 128);
     int nstage = (220 * 1024 - 1024) / stage_bytes;
     if (nstage > 6) nstage = 6;
     if (nstage < 2) nstage = 2;
     const int smem = nstage * stage_bytes + 1024 + (int)sizeof(TcSmemCtl) + 64;
-    int grid = m_tiles * B.n_tiles;
+    int grid = m_tiles * n_tiles;
     if (grid > s->sms) grid = s->sms;
     TcMaps mp;
-    for (int q = 0; q < 3; ++q) { mp.a[q] = A.map[q]; mp.b[q] = B.p.map[q]; }
-    k_tc_gemm<<<grid, TC_THREADS, smem, h->stream>>>(mp, m_tiles, B.n_tiles, B.BN, nk, nstage, ep);
+    for (int q = 0; q < NP; ++q) { mp.a[q] = A.map[q]; mp.b[q] = B.mapv[v][q]; }
+    k_tc_gemm<NP, BWD><<<grid, TC_THREADS, smem, h->stream>>>(mp, m_tiles, n_tiles, BN, nk, nstage, ep);
     h->launches++;
+}
+
+static TcEpi tc_base_epi(cnf_handle* h, TcState* s, const CnfBufs& bf, long long row0, int check_done) {
+    TcEpi base;
+    memset(&base, 0, sizeof(base));
+    base.eps = bf.eps; base.Bs = bf.Bs; base.row0 = row0; base.D = h->cfg.D; base.flags = h->cfg.flags;
+    base.kout_ind = &s->dyn->kout;
+    base.ctrl = check_done ? h->d_ctrl : nullptr;
+    base.B = bf.B;
+    return base;
+}
+
+// forward chain h_0 -> h_1 .. h_{L-1} (planes H[l]) of one chunk; the last layer is left to the caller
+template <int NP>
+static void tc_forward_hidden(cnf_handle* h, TcState* s, const TcEpi& base, int mc) {
+    const cnf_config& c = h->cfg;
+    for (int l = 0; l < c.n_layers - 1; ++l) {
+        TcEpi ep = base;
+        ep.bias = h->d_theta + h->b_off[l];
+        ep.N = c.dims[l + 1];
+        ep.kind = TC_FWD_HIDDEN;
+        for (int q = 0; q < 3; ++q) ep.out[q] = s->H[l + 1].p[q];
+        ep.ld_out = s->H[l + 1].ld;
+        tc_launch_gemm<NP, false>(h, s, s->H[l], s->wf[l], mc, ep);
+    }
 }
 
 // du = augmented_f(src) in TrainMode on the tensor path.  src: D x Bs z rows (host-known pointer);
@@ -505,30 +774,21 @@ int tc_eval(cnf_handle* h, const CnfBufs& bf, const float* src, int kidx, float*
     const bool jvp = c.trace_mode == CNF_TRACE_JVP;
     for (long long row0 = 0; row0 < bf.Bs; row0 += s->Mc) {
         const int mc = (int)((bf.Bs - row0) < s->Mc ? (bf.Bs - row0) : s->Mc);
-        TcEpi base;
-        memset(&base, 0, sizeof(base));
-        base.eps = bf.eps; base.Bs = bf.Bs; base.row0 = row0; base.D = c.D; base.flags = c.flags;
-        base.kout_ind = &s->dyn->kout;
-        base.ctrl = check_done ? h->d_ctrl : nullptr;
+        TcEpi base = tc_base_epi(h, s, bf, row0, check_done);
         // h_0 = [z; ys] planes (+ resolve the output buffer)
         k_tc_prep<<<(mc + 255) / 256, 256, 0, h->stream>>>(h->d_ctrl, bf, src, c.D, bf.ys, c.C, row0, mc, s->H[0].p[0],
                                                           s->H[0].p[1], s->H[0].p[2], s->H[0].ld, kidx, kout_fixed, s->dyn, check_done);
         h->launches++;
-        for (int l = 0; l < L; ++l) {   // forward chain
+        tc_forward_hidden<3>(h, s, base, mc);
+        {
             TcEpi ep = base;
-            ep.bias = h->d_theta + h->b_off[l];
-            ep.N = c.dims[l + 1];
-            if (l < L - 1) {
-                ep.kind = TC_FWD_HIDDEN;
-                for (int q = 0; q < 3; ++q) ep.out[q] = s->H[l + 1].p[q];
-                ep.ld_out = s->H[l + 1].ld;
-            } else {
-                ep.kind = TC_FWD_LAST;
-                ep.vjp = jvp ? 0 : 1;
-                for (int q = 0; q < 3; ++q) ep.out[q] = s->G[L].p[q];
-                ep.ld_out = s->G[L].ld;
-            }
-            tc_launch_gemm(h, s, s->H[l], s->wf[l], mc, ep);
+            ep.bias = h->d_theta + h->b_off[L - 1];
+            ep.N = c.dims[L];
+            ep.kind = TC_FWD_LAST;
+            ep.vjp = jvp ? 0 : 1;
+            for (int q = 0; q < 3; ++q) ep.out[q] = s->G[L].p[q];
+            ep.ld_out = s->G[L].ld;
+            tc_launch_gemm<3, false>(h, s, s->H[L - 1], s->wf[L - 1], mc, ep);
         }
         if (!jvp) {
             // reverse chain: g_{l} = (g_{l+1} W_{l+1}) .* (1 - h_l^2), v = (g_1 W_1)[0:D]
@@ -543,7 +803,7 @@ int tc_eval(cnf_handle* h, const CnfBufs& bf, const float* src, int kidx, float*
                     ep.kind = TC_BWD_LAST;
                     ep.N = c.D;
                 }
-                tc_launch_gemm(h, s, s->G[l + 1], s->wb[l], mc, ep);
+                tc_launch_gemm<3, false>(h, s, s->G[l + 1], s->wb[l], mc, ep);
             }
         } else {
             // tangent chain: tau_0 = eps, tau_l = (tau_{l-1} W_l^T) .* (1 - h_l^2), J eps = tau_L
@@ -564,9 +824,35 @@ int tc_eval(cnf_handle* h, const CnfBufs& bf, const float* src, int kidx, float*
                 }
                 // the seed planes G[0] = [eps; 0] have the first layer's padded K width, so the
                 // condition columns of W_1 meet zeros (Jacobian w.r.t. z only)
-                tc_launch_gemm(h, s, l == 0 ? s->G[0] : s->G[l], s->wf[l], mc, ep);
+                tc_launch_gemm<3, false>(h, s, l == 0 ? s->G[0] : s->G[l], s->wf[l], mc, ep);
             }
         }
+    }
+    return CNF_OK;
+}
+
+// zdot rows only (forward chain, BF16x3): the stage-checkpoint recomputation of the reverse sweep
+// needs k_i[0:D] to rebuild the stage inputs, not the trace / regulariser rows.
+int tc_eval_z(cnf_handle* h, const CnfBufs& bf, const float* src, float* kout) {
+    TcState* s = (TcState*)h->tc_state;
+    if (!s || !s->weights_ok) { h->err = "tensor path: parameters not set"; return CNF_ERR_UNSUPPORTED; }
+    const cnf_config& c = h->cfg;
+    int rc;
+    if ((rc = tc_ensure_acts(h, s, bf.Bs))) return rc;
+    const int L = c.n_layers;
+    for (long long row0 = 0; row0 < bf.Bs; row0 += s->Mc) {
+        const int mc = (int)((bf.Bs - row0) < s->Mc ? (bf.Bs - row0) : s->Mc);
+        TcEpi base = tc_base_epi(h, s, bf, row0, 0);
+        k_tc_prep<<<(mc + 255) / 256, 256, 0, h->stream>>>(h->d_ctrl, bf, src, c.D, bf.ys, c.C, row0, mc, s->H[0].p[0],
+                                                          s->H[0].p[1], s->H[0].p[2], s->H[0].ld, -1, kout, s->dyn, 0);
+        h->launches++;
+        tc_forward_hidden<2>(h, s, base, mc);
+        TcEpi ep = base;
+        ep.bias = h->d_theta + h->b_off[L - 1];
+        ep.N = c.dims[L];
+        ep.kind = TC_FWD_LAST;
+        ep.vjp = 2;
+        tc_launch_gemm<2, false>(h, s, s->H[L - 1], s->wf[L - 1], mc, ep);
     }
     return CNF_OK;
 }
