@@ -1,6 +1,6 @@
 // cnf_backward_tc.cu — reverse sweep of the discrete adjoint on the tensor path (wide nets,
 // TrainMode VecJac Hutchinson).  Replaces, per RK stage, the generic SIMT k_vjp_generic by
-//   3L+L layer GEMMs (k_tc_gemm<2,true>: forward chain, eps chain, gbar chain, hbar chain; BF16x3)
+//   3L+L layer GEMMs (k_tc_gemm<1,true>: forward chain, eps chain, gbar chain, hbar chain; BF16x3)
 //   + L weight-gradient GEMMs (k_tc_wgrad: dW_l += pbar_l^T h_{l-1} + g_l^T qbar_l, db_l += sum pbar_l).
 // Same maths as cnf_backward.cu / DESIGN.md "Backward"; reference call sites of the gradient:
 // src/exts/mlj_ext/core_icnf.jl:59-63, test/call_tests.jl:239-251 (Enzyme + SciMLSensitivity there).
@@ -182,8 +182,8 @@ static int tc_ensure_bw(cnf_handle* h, TcState* s) {
     const int L = c.n_layers;
     int rc;
     for (int l = 1; l <= L; ++l) {
-        if ((rc = tc_alloc_plane(h, s->QB[l], s->Mc, pad_to(c.dims[l - 1], TC_BK), TC_BM, 2))) return rc;
-        if ((rc = tc_alloc_plane(h, s->PB[l], s->Mc, pad_to(c.dims[l], TC_BK), TC_BM, 2))) return rc;
+        if ((rc = tc_alloc_plane(h, s->QB[l], s->Mc, pad_to(c.dims[l - 1], TC_BK), TC_BM))) return rc;
+        if ((rc = tc_alloc_plane(h, s->PB[l], s->Mc, pad_to(c.dims[l], TC_BK), TC_BM))) return rc;
         if (l < L && (rc = tc_alloc_f32(h, s->Q[l], s->Mc, pad_to(c.dims[l], TC_BK)))) return rc;
     }
     if ((rc = tc_alloc_f32(h, s->Y, s->Mc, pad_to(c.D, TC_BK)))) return rc;
@@ -245,10 +245,10 @@ int tc_vjp_stage(cnf_handle* h, const CnfBufs& bf, const float* src, const float
         base.abar = abar; base.ubar = ubar; base.dtp = dtp; base.stage = stage;
         base.c_l = c_l; base.c_E = c_E; base.c_n = c_n;
         for (int j = 0; j < 5; ++j) base.kb[j] = kb[j];
-        k_tc_prep<<<(mc + 255) / 256, 256, 0, h->stream>>>(h->d_ctrl, bf, src, c.D, bf.ys, c.C, row0, mc, s->H[0].p[0],
-                                                          s->H[0].p[1], s->H[0].p[2], s->H[0].ld, -1, nullptr, nullptr, 0);
+        k_tc_prep<1><<<(mc + 255) / 256, 256, 0, h->stream>>>(h->d_ctrl, bf, src, c.D, bf.ys, c.C, row0, mc, s->H[0].p[0],
+                                                          s->H[0].p[1], s->H[0].ld, -1, nullptr, nullptr, 0);
         h->launches++;
-        tc_forward_hidden<2>(h, s, base, mc);
+        tc_forward_hidden<1>(h, s, base, mc);
         {   // y, g_L, ybar
             TcEpi ep = base;
             ep.kind = TCB_FWD_LAST;
@@ -257,7 +257,7 @@ int tc_vjp_stage(cnf_handle* h, const CnfBufs& bf, const float* src, const float
             for (int q = 0; q < 2; ++q) ep.out[q] = s->G[L].p[q];
             ep.ld_out = s->G[L].ld;
             ep.f32a = s->Y.p; ep.f32b = s->YB.p; ep.ld_f = s->Y.ld;
-            tc_launch_gemm<2, true>(h, s, s->H[L - 1], s->wf[L - 1], mc, ep);
+            tc_launch_gemm<1, true>(h, s, s->H[L - 1], s->wf[L - 1], mc, ep);
         }
         for (int l = L; l >= 1; --l) {   // eps chain: q_l = g_l W_l, g_{l-1} = q_l (1-h_{l-1}^2); v = q_1[0:D]
             TcEpi ep = base;
@@ -273,7 +273,7 @@ int tc_vjp_stage(cnf_handle* h, const CnfBufs& bf, const float* src, const float
                 for (int q = 0; q < 2; ++q) ep.out[q] = s->QB[1].p[q];
                 ep.ld_out = s->QB[1].ld;
             }
-            tc_launch_gemm<2, true>(h, s, s->G[l], s->wb[l - 1], mc, ep);
+            tc_launch_gemm<1, true>(h, s, s->G[l], s->wb[l - 1], mc, ep);
         }
         for (int l = 1; l <= L; ++l) {   // adjoint of the eps chain runs forward: gbar_l = qbar_l W_l^T
             TcEpi ep = base;
@@ -290,7 +290,7 @@ int tc_vjp_stage(cnf_handle* h, const CnfBufs& bf, const float* src, const float
                 ep.ld_out = s->PB[L].ld;
                 ep.f32a = s->Y.p; ep.f32b = s->YB.p; ep.ld_f = s->Y.ld;
             }
-            tc_launch_gemm<2, true>(h, s, s->QB[l], s->wf[l - 1], mc, ep);
+            tc_launch_gemm<1, true>(h, s, s->QB[l], s->wf[l - 1], mc, ep);
         }
         for (int l = L; l >= 1; --l) {   // adjoint of the forward chain: hbar_{l-1} = pbar_l W_l
             tc_launch_wgrad(h, s, s->PB[l], s->H[l - 1], &s->G[l], &s->QB[l], mc, c.dims[l], c.dims[l - 1],
@@ -306,7 +306,7 @@ int tc_vjp_stage(cnf_handle* h, const CnfBufs& bf, const float* src, const float
                 ep.kind = TCB_ZBAR;
                 ep.N = c.D;
             }
-            tc_launch_gemm<2, true>(h, s, s->PB[l], s->wb[l - 1], mc, ep);
+            tc_launch_gemm<1, true>(h, s, s->PB[l], s->wb[l - 1], mc, ep);
         }
     }
     return CNF_OK;

@@ -4,13 +4,18 @@
 // (128 samples per tile, one TMEM lane per sample), FP32 accumulators in TMEM, and the layer's
 // elementwise work fused into the TMEM->register epilogue (bias + tanh, the (1-h^2) Hadamard
 // factor, the eps dot product and the un-squared norms of reference src/icnf.jl:335-348).
-// Precision of the forward solve (NP = 3): BF16x6 operand splitting (x = p0 + p1 + p2 in bf16;
-// products p0p0 + p1p0 + p0p1 + p1p1 + p2p0 + p0p2, FP32 accumulate) = FP32-level accuracy (1e-8
-// relative on log-density in scripts/precision_study.py).  BF16x3 (1e-6..4e-6) meets the 1e-4 value
-// tolerance but its 1e-5 noise in f is amplified by the abstol = 1e-6 rows of the error norm and
-// changes the accepted-step count by 5-7 steps; plain TF32 (1e-4..2e-4) misses the value
-// tolerance as well.  The reverse sweep (gradient tolerance 1e-3) runs BF16x3 (NP = 2: p0p0 + p1p0
-// + p0p1, ~1e-5) with half the MMAs and two thirds of the plane traffic.
+// Precision: every operand is split into two 16-bit planes x = hi + lo and a product costs three
+// MMAs (hi*hi + lo*hi + hi*lo, FP32 accumulate).
+//   PREC 0, forward solve: IEEE half planes (FP16x3).  hi + lo carries 22 significand bits for the
+//     O(1) operands of this path (tanh outputs, Glorot-scale weights, the eps chain), so f has
+//     FP32-level noise (rms 2e-7 vs 1.7e-7 for an FP32 SIMT evaluation; scripts/precision_fp16.py).
+//     That level is required: BF16x3 (16 bits, 1e-5 noise in f) meets the 1e-4 value tolerance but
+//     the noise is amplified by the abstol = 1e-6 rows of the error norm and changes the accepted-
+//     step count by 5-7; plain TF32 misses the value tolerance as well.  (The first tensor path
+//     used BF16x6 = three bf16 planes and six MMAs for the same accuracy: 1.5x the plane traffic,
+//     2x the tensor work.)  Inputs are assumed to lie inside the half range (|h_0| < 6e4).
+//   PREC 1, reverse sweep: bfloat16 planes (BF16x3, ~1e-5): cotangents scale with dt/B and need
+//     the FP32 exponent range; the gradient tolerance is 1e-3.
 // Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (one elected thread), warps 2..9 =
 // epilogue (two warps per TMEM lane quadrant, half of the columns each); two TMEM accumulator
 // buffers so the epilogue of tile i overlaps the MMAs of tile i+1.
@@ -39,9 +44,9 @@ struct TcEpi {
     int kind;
     int N;                         // valid output columns
     const float* bias;             // [N]                       (FWD_*)
-    __nv_bfloat16* out[3];         // [rows x ld_out] planes    (hidden kinds; FWD_LAST: g_L planes)
+    __nv_bfloat16* out[2];         // [rows x ld_out] planes    (hidden kinds; FWD_LAST: g_L planes)
     int ld_out;
-    const __nv_bfloat16* hp[3];    // activations for d = 1-h^2 (BWD_HIDDEN)
+    const __nv_bfloat16* hp[2];    // activations for d = 1-h^2 (BWD_HIDDEN)
     int ld_h;
     const float* eps;              // D x Bs (SoA)
     float* kout;                   // R x Bs (SoA); if kout_ind != nullptr the pointer is read from there
@@ -65,18 +70,30 @@ struct TcEpi {
     int B;                         // live samples (rows >= B are padding)
 };
 
-__device__ __forceinline__ void tc_split(float x, __nv_bfloat16 (&p)[3]) {
-    p[0] = __float2bfloat16_rn(x);
-    float r = x - __bfloat162float(p[0]);
-    p[1] = __float2bfloat16_rn(r);
-    r -= __bfloat162float(p[1]);
-    p[2] = __float2bfloat16_rn(r);
+// two floats -> packed (hi, hi) and (lo, lo) 16-bit pairs; element a in the low half-word
+template <int PREC>
+__device__ __forceinline__ void tc_split2(float a, float b, uint32_t& hi, uint32_t& lo) {
+    if (PREC == 0) {
+        __half2 h = __floats2half2_rn(a, b);
+        float2 f = __half22float2(h);
+        __half2 l = __floats2half2_rn(a - f.x, b - f.y);
+        hi = *reinterpret_cast<uint32_t*>(&h);
+        lo = *reinterpret_cast<uint32_t*>(&l);
+    } else {
+        __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+        float2 f = __bfloat1622float2(h);
+        __nv_bfloat162 l = __floats2bfloat162_rn(a - f.x, b - f.y);
+        hi = *reinterpret_cast<uint32_t*>(&h);
+        lo = *reinterpret_cast<uint32_t*>(&l);
+    }
 }
-__device__ __forceinline__ uint32_t tc_pack(__nv_bfloat16 a, __nv_bfloat16 b) {
-    return (uint32_t)__bfloat16_as_ushort(a) | ((uint32_t)__bfloat16_as_ushort(b) << 16);
+template <int PREC>
+__device__ __forceinline__ float2 tc_unpack2(uint32_t w) {
+    if (PREC == 0) return __half22float2(*reinterpret_cast<__half2*>(&w));
+    return make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u));
 }
 
-struct TcMaps { CUtensorMap a[3], b[3]; };   // A planes, B planes
+struct TcMaps { CUtensorMap a[2], b[2]; };   // A planes, B planes
 
 struct TcSmemCtl {
     uint64_t full[8], empty[8], tfull[2], tempty[2];
@@ -84,41 +101,32 @@ struct TcSmemCtl {
 };
 
 // ---- epilogue helpers: one thread = one sample row; v = 32 accumulator columns c0..c0+31
-template <int NP>
-__device__ __forceinline__ void tc_store_planes32(const float (&x)[32], __nv_bfloat16* const (&dst)[3], long long off) {
-    uint32_t pk[NP][16];
+template <int PREC>
+__device__ __forceinline__ void tc_store_planes32(const float (&x)[32], __nv_bfloat16* const (&dst)[2], long long off) {
+    uint32_t pk[2][16];
 #pragma unroll
-    for (int j = 0; j < 16; ++j) {
-        __nv_bfloat16 a[3], b[3];
-        tc_split(x[2 * j], a);
-        tc_split(x[2 * j + 1], b);
+    for (int j = 0; j < 16; ++j) tc_split2<PREC>(x[2 * j], x[2 * j + 1], pk[0][j], pk[1][j]);
 #pragma unroll
-        for (int q = 0; q < NP; ++q) pk[q][j] = tc_pack(a[q], b[q]);
-    }
-#pragma unroll
-    for (int q = 0; q < NP; ++q) {
+    for (int q = 0; q < 2; ++q) {
         uint4* d = reinterpret_cast<uint4*>(dst[q] + off);
 #pragma unroll
         for (int j = 0; j < 4; ++j) d[j] = make_uint4(pk[q][4 * j], pk[q][4 * j + 1], pk[q][4 * j + 2], pk[q][4 * j + 3]);
     }
 }
 
-template <int NP>
-__device__ __forceinline__ void tc_load_planes32(const __nv_bfloat16* const (&src)[3], long long off, float (&h)[32]) {
+template <int PREC>
+__device__ __forceinline__ void tc_load_planes32(const __nv_bfloat16* const (&src)[2], long long off, float (&h)[32]) {
+    const uint4* s0 = reinterpret_cast<const uint4*>(src[0] + off);
+    const uint4* s1 = reinterpret_cast<const uint4*>(src[1] + off);
 #pragma unroll
-    for (int j = 0; j < 32; ++j) h[j] = 0.0f;
+    for (int j = 0; j < 4; ++j) {
+        const uint4 a = __ldg(s0 + j), b = __ldg(s1 + j);
+        const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, bw[4] = {b.x, b.y, b.z, b.w};
 #pragma unroll
-    for (int q = NP - 1; q >= 0; --q) {   // smallest plane first
-        const uint4* sp = reinterpret_cast<const uint4*>(src[q] + off);
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            uint4 a = __ldg(sp + j);
-            const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                h[8 * j + 2 * k] += __uint_as_float(aw[k] << 16);
-                h[8 * j + 2 * k + 1] += __uint_as_float(aw[k] & 0xffff0000u);
-            }
+        for (int k = 0; k < 4; ++k) {
+            const float2 hi = tc_unpack2<PREC>(aw[k]), lo = tc_unpack2<PREC>(bw[k]);
+            h[8 * j + 2 * k] = hi.x + lo.x;
+            h[8 * j + 2 * k + 1] = hi.y + lo.y;
         }
     }
 }
@@ -138,7 +146,7 @@ __device__ __forceinline__ void tc_store_f32x32(float* dst, const float (&x)[32]
 }
 
 // ---- forward-solve epilogue of one 128 x BN tile (kinds TC_*)
-template <int NP>
+template <int PREC>
 __device__ __forceinline__ void tc_epilogue_fwd(const TcEpi& ep, uint32_t tbase, int mb, int nb, int BN,
                                                 int quad, int half, int lane) {
     const long long rloc = (long long)mb * TC_BM + quad * 32 + lane;   // row inside the chunk
@@ -159,11 +167,11 @@ __device__ __forceinline__ void tc_epilogue_fwd(const TcEpi& ep, uint32_t tbase,
                 for (int j = 0; j < 32; ++j) x[j] = cnf_tanh_fastpath(__uint_as_float(v[j]) + __ldg(ep.bias + ng + j));
             } else {   // BWD_HIDDEN: acc .* (1 - h^2)
                 float h[32];
-                tc_load_planes32<NP>(ep.hp, rloc * ep.ld_h + ng, h);
+                tc_load_planes32<PREC>(ep.hp, rloc * ep.ld_h + ng, h);
 #pragma unroll
                 for (int j = 0; j < 32; ++j) x[j] = __uint_as_float(v[j]) * fmaf(-h[j], h[j], 1.0f);
             }
-            tc_store_planes32<NP>(x, ep.out, rloc * ep.ld_out + ng);
+            tc_store_planes32<PREC>(x, ep.out, rloc * ep.ld_out + ng);
         }
     } else if (half == 0) {
         // per-sample reductions over all D columns: one warp per quadrant walks every chunk
@@ -173,27 +181,29 @@ __device__ __forceinline__ void tc_epilogue_fwd(const TcEpi& ep, uint32_t tbase,
             uint32_t v[32];
             tc::tmem_ld_32x32(tbase + c0, v);
             tc::tmem_ld_wait();
+            if (ep.kind == TC_FWD_LAST) {
+                float g[32];
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-                const int n = c0 + j;
-                if (n < ep.D) {
-                    const float a = __uint_as_float(v[j]);
-                    if (ep.kind == TC_FWD_LAST) {
-                        const float y = cnf_tanh_fastpath(a + __ldg(ep.bias + n));
+                for (int j = 0; j < 32; ++j) {
+                    const int n = c0 + j;
+                    g[j] = 0.0f;
+                    if (n < ep.D) {
+                        const float y = cnf_tanh_fastpath(__uint_as_float(v[j]) + __ldg(ep.bias + n));
                         ep.kout[(long long)n * ep.Bs + grow] = y;
                         s0 = fmaf(y, y, s0);
-                        if (ep.vjp == 1) {
-                            const float g = ep.eps[(long long)n * ep.Bs + grow] * fmaf(-y, y, 1.0f);
-                            __nv_bfloat16 gp[3];
-                            tc_split(g, gp);
+                        if (ep.vjp == 1) g[j] = ep.eps[(long long)n * ep.Bs + grow] * fmaf(-y, y, 1.0f);
+                    }
+                }
+                if (ep.vjp == 1) tc_store_planes32<PREC>(g, ep.out, rloc * ep.ld_out + c0);
+            } else {
 #pragma unroll
-                            for (int q = 0; q < NP; ++q) ep.out[q][rloc * ep.ld_out + n] = gp[q];
-                        }
-                    } else {
-                        float vv = a;
+                for (int j = 0; j < 32; ++j) {
+                    const int n = c0 + j;
+                    if (n < ep.D) {
+                        float vv = __uint_as_float(v[j]);
                         if (ep.kind == TC_JVP_LAST) {
                             const float y = ep.kout[(long long)n * ep.Bs + grow];
-                            vv = a * fmaf(-y, y, 1.0f);
+                            vv *= fmaf(-y, y, 1.0f);
                         }
                         s0 = fmaf(-vv, ep.eps[(long long)n * ep.Bs + grow], s0);
                         s1 = fmaf(vv, vv, s1);
@@ -240,7 +250,7 @@ __device__ __forceinline__ void tc_epilogue_bwd(const TcEpi& ep, uint32_t tbase,
                 }
             }
             tc_store_f32x32(ep.f32a + rloc * ep.ld_f + c0, y);
-            tc_store_planes32<2>(g, ep.out, rloc * ep.ld_out + c0);
+            tc_store_planes32<1>(g, ep.out, rloc * ep.ld_out + c0);
         }
         const float inv = (live && (ep.flags & CNF_FLAG_NORM_Z) && s0 > 0.0f) ? wgt * ep.c_E / sqrtf(s0) : 0.0f;
         for (int ch = 0; ch < nchunk; ++ch) {
@@ -281,7 +291,7 @@ __device__ __forceinline__ void tc_epilogue_bwd(const TcEpi& ep, uint32_t tbase,
                 const int n = c0 + j;
                 x[j] = (n < ep.D) ? fmaf(inv, __uint_as_float(v[j]), -al * ep.eps[(long long)n * ep.Bs + grow]) : 0.0f;
             }
-            tc_store_planes32<2>(x, ep.out, rloc * ep.ld_out + c0);
+            tc_store_planes32<1>(x, ep.out, rloc * ep.ld_out + c0);
         }
         return;
     }
@@ -323,7 +333,7 @@ __device__ __forceinline__ void tc_epilogue_bwd(const TcEpi& ep, uint32_t tbase,
             }
         } else {
             float h[32];
-            tc_load_planes32<2>(ep.hp, rloc * ep.ld_h + ng, h);
+            tc_load_planes32<1>(ep.hp, rloc * ep.ld_h + ng, h);
             if (ep.kind == TCB_BWD_HIDDEN) {
                 float q[32];
 #pragma unroll
@@ -350,13 +360,13 @@ __device__ __forceinline__ void tc_epilogue_bwd(const TcEpi& ep, uint32_t tbase,
                     x[j] = fmaf(-2.0f * h[j], db[j], __uint_as_float(v[j])) * fmaf(-h[j], h[j], 1.0f);
             }
         }
-        tc_store_planes32<2>(x, ep.out, rloc * ep.ld_out + ng);
+        tc_store_planes32<1>(x, ep.out, rloc * ep.ld_out + ng);
     }
 }
 
 // BM x BN output tile per (m_blk, n_blk); K in blocks of 64 bf16; persistent over tiles.
-// NP = bf16 planes per operand (3: BF16x6 forward solve, 2: BF16x3 reverse sweep).
-template <int NP, bool BWD>
+// PREC = operand format of the two hi/lo planes (0: IEEE half, forward solve; 1: bfloat16, reverse sweep).
+template <int PREC, bool BWD>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, int nk, int nstage, TcEpi ep) {
     if (ep.ctrl && ep.ctrl->done) return;
@@ -365,13 +375,13 @@ k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, i
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     const uint32_t a_bytes = TC_BM * 128;          // one plane of A per stage
     const uint32_t b_bytes = (uint32_t)BN * 128;   // one plane of B per stage
-    const uint32_t stage_bytes = NP * (a_bytes + b_bytes);
+    const uint32_t stage_bytes = 2 * (a_bytes + b_bytes);
     TcSmemCtl* ctl = reinterpret_cast<TcSmemCtl*>(smem + (size_t)nstage * stage_bytes);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int total = m_tiles * n_tiles;
 
     if (warp == 0 && lane == 0) {
-        for (int q = 0; q < NP; ++q) { tc::tma_prefetch_desc(&mp.a[q]); tc::tma_prefetch_desc(&mp.b[q]); }
+        for (int q = 0; q < 2; ++q) { tc::tma_prefetch_desc(&mp.a[q]); tc::tma_prefetch_desc(&mp.b[q]); }
         for (int s = 0; s < nstage; ++s) { tc::mbar_init(&ctl->full[s], 1); tc::mbar_init(&ctl->empty[s], 1); }
         for (int a = 0; a < 2; ++a) { tc::mbar_init(&ctl->tfull[a], 1); tc::mbar_init(&ctl->tempty[a], 8); }
         tc::fence_barrier_init();
@@ -391,9 +401,9 @@ k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, i
                     tc::mbar_wait(&ctl->empty[stage], phase ^ 1);
                     uint8_t* s = smem + (size_t)stage * stage_bytes;
                     tc::mbar_arrive_expect_tx(&ctl->full[stage], stage_bytes);
-                    for (int q = 0; q < NP; ++q) {
+                    for (int q = 0; q < 2; ++q) {
                         tc::tma_load_2d(&mp.a[q], &ctl->full[stage], s + q * a_bytes, kb * TC_BK, mb * TC_BM);
-                        tc::tma_load_2d(&mp.b[q], &ctl->full[stage], s + NP * a_bytes + q * b_bytes, kb * TC_BK, nb * BN);
+                        tc::tma_load_2d(&mp.b[q], &ctl->full[stage], s + 2 * a_bytes + q * b_bytes, kb * TC_BK, nb * BN);
                     }
                     if (++stage == nstage) { stage = 0; phase ^= 1; }
                 }
@@ -401,7 +411,7 @@ k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, i
         }
     } else if (warp == 1) {
         if (lane == 0) {   // ===== MMA issuer
-            const uint32_t idesc = tc::umma_idesc_bf16(TC_BM, BN);
+            const uint32_t idesc = tc::umma_idesc_f16(TC_BM, BN, PREC);
             int stage = 0; uint32_t phase = 0; int it = 0;
             for (int t = blockIdx.x; t < total; t += gridDim.x, ++it) {
                 const int acc = it & 1;
@@ -414,20 +424,15 @@ k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, i
                     const uint32_t s = tc::smem_u32(smem + (size_t)stage * stage_bytes);
 #pragma unroll
                     for (int kk = 0; kk < TC_BK / 16; ++kk) {
-                        uint64_t a[NP], b[NP];
+                        uint64_t a[2], b[2];
 #pragma unroll
-                        for (int q = 0; q < NP; ++q) {
+                        for (int q = 0; q < 2; ++q) {
                             a[q] = tc::umma_desc_sw128(s + q * a_bytes + kk * 32);
-                            b[q] = tc::umma_desc_sw128(s + NP * a_bytes + q * b_bytes + kk * 32);
+                            b[q] = tc::umma_desc_sw128(s + 2 * a_bytes + q * b_bytes + kk * 32);
                         }
                         tc::umma_bf16(dcol, a[0], b[0], idesc, (kb | kk) != 0);
                         tc::umma_bf16(dcol, a[1], b[0], idesc, 1);
                         tc::umma_bf16(dcol, a[0], b[1], idesc, 1);
-                        if (NP == 3) {   // BF16x6: all products down to 2^-24 relative
-                            tc::umma_bf16(dcol, a[1], b[1], idesc, 1);
-                            tc::umma_bf16(dcol, a[NP - 1], b[0], idesc, 1);
-                            tc::umma_bf16(dcol, a[0], b[NP - 1], idesc, 1);
-                        }
                     }
                     tc::umma_commit(&ctl->empty[stage]);
                     if (++stage == nstage) { stage = 0; phase ^= 1; }
@@ -447,7 +452,7 @@ k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, i
             tc::tc_fence_after();
             const uint32_t tbase = tmem + ((uint32_t)(quad * 32) << 16) + (uint32_t)acc * 256;
             if (BWD) tc_epilogue_bwd(ep, tbase, mb, nb, BN, quad, half, lane);
-            else tc_epilogue_fwd<NP>(ep, tbase, mb, nb, BN, quad, half, lane);
+            else tc_epilogue_fwd<PREC>(ep, tbase, mb, nb, BN, quad, half, lane);
             tc::tc_fence_before();
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(&ctl->tempty[acc]);
@@ -459,32 +464,37 @@ k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, i
 }
 
 // ------------------------------------------------------------------ small helper kernels
-// fp32 weights (Julia column-major dout x din) -> bf16 hi/lo planes [rows x ld], zero padded.
+// fp32 weights (Julia column-major dout x din) -> hi/lo planes [rows x ld], zero padded, in both
+// formats (half for the forward solve, bfloat16 for the reverse sweep).
 // transpose = 0: plane[o][i] = W[o,i] (forward B operand); 1: plane[i][o] = W[o,i] (VJP B operand)
-__global__ void k_tc_weights(const float* __restrict__ W, int dout, int din, __nv_bfloat16* __restrict__ p0,
-                             __nv_bfloat16* __restrict__ p1, __nv_bfloat16* __restrict__ p2, int rows, int ld,
-                             int transpose) {
+__global__ void k_tc_weights(const float* __restrict__ W, int dout, int din, __nv_bfloat16* __restrict__ h0,
+                             __nv_bfloat16* __restrict__ h1, __nv_bfloat16* __restrict__ b0,
+                             __nv_bfloat16* __restrict__ b1, int rows, int ld, int transpose) {
     const long long n = (long long)rows * ld;
+    unsigned short* o16[4] = {reinterpret_cast<unsigned short*>(h0), reinterpret_cast<unsigned short*>(h1),
+                              reinterpret_cast<unsigned short*>(b0), reinterpret_cast<unsigned short*>(b1)};
     for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += (long long)gridDim.x * blockDim.x) {
         int r = (int)(p / ld), c = (int)(p % ld);
         int o = transpose ? c : r, i = transpose ? r : c;
         float w = (o < dout && i < din) ? W[(long long)i * dout + o] : 0.0f;
-        __nv_bfloat16 sp[3];
-        tc_split(w, sp);
-        p0[p] = sp[0];
-        p1[p] = sp[1];
-        p2[p] = sp[2];
+        uint32_t hi, lo;
+        tc_split2<0>(w, 0.0f, hi, lo);
+        o16[0][p] = (unsigned short)(hi & 0xffff);
+        o16[1][p] = (unsigned short)(lo & 0xffff);
+        tc_split2<1>(w, 0.0f, hi, lo);
+        o16[2][p] = (unsigned short)(hi & 0xffff);
+        o16[3][p] = (unsigned short)(lo & 0xffff);
     }
 }
 
 struct TcDyn { float* kout; };
 
-// stage input rows (SoA, D x Bs) [+ condition rows] -> bf16 hi/lo planes [mc x ld] of this chunk;
+// stage input rows (SoA, D x Bs) [+ condition rows] -> hi/lo planes [mc x ld] of this chunk;
 // also resolves the device-side output buffer of this evaluation (kidx: 0 -> K[k1idx], 6 -> K[6-k1idx])
+template <int PREC>
 __global__ void k_tc_prep(const CnfCtrl* __restrict__ c, CnfBufs bf, const float* __restrict__ src, int nsrc,
                           const float* __restrict__ src2, int nsrc2, long long row0, int mc,
-                          __nv_bfloat16* __restrict__ p0, __nv_bfloat16* __restrict__ p1,
-                          __nv_bfloat16* __restrict__ p2, int ld, int kidx,
+                          __nv_bfloat16* __restrict__ p0, __nv_bfloat16* __restrict__ p1, int ld, int kidx,
                           float* kout_fixed, TcDyn* dyn, int check_done) {
     if (check_done && c->done) return;
     if (blockIdx.x == 0 && threadIdx.x == 0 && dyn) {
@@ -497,24 +507,22 @@ __global__ void k_tc_prep(const CnfCtrl* __restrict__ c, CnfBufs bf, const float
     const long long b = row0 + r;
     const int ntot = nsrc + nsrc2;
     for (int c0 = 0; c0 < ntot; c0 += 8) {
-        uint32_t pk[3][4];
+        uint32_t pk[2][4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            __nv_bfloat16 sp[2][3];
+            float v[2];
 #pragma unroll
             for (int t = 0; t < 2; ++t) {
                 const int i = c0 + 2 * j + t;
-                float v = 0.0f;
-                if (i < nsrc) v = src[(long long)i * bf.Bs + b];
-                else if (i < ntot) v = src2[(long long)(i - nsrc) * bf.Bs + b];
-                tc_split(v, sp[t]);
+                v[t] = 0.0f;
+                if (i < nsrc) v[t] = src[(long long)i * bf.Bs + b];
+                else if (i < ntot) v[t] = src2[(long long)(i - nsrc) * bf.Bs + b];
             }
-#pragma unroll
-            for (int q = 0; q < 3; ++q) pk[q][j] = tc_pack(sp[0][q], sp[1][q]);
+            tc_split2<PREC>(v[0], v[1], pk[0][j], pk[1][j]);
         }
-        __nv_bfloat16* dst[3] = {p0, p1, p2};
+        __nv_bfloat16* dst[2] = {p0, p1};
 #pragma unroll
-        for (int q = 0; q < 3; ++q)
+        for (int q = 0; q < 2; ++q)
             *reinterpret_cast<uint4*>(dst[q] + (long long)r * ld + c0) = make_uint4(pk[q][0], pk[q][1], pk[q][2], pk[q][3]);
     }
 }
@@ -548,16 +556,14 @@ static bool tc_make_map(CUtensorMap* m, const void* base, long long rows, long l
 static inline int pad_to(int x, int m) { return (x + m - 1) / m * m; }
 
 struct TcPlane {
-    __nv_bfloat16* p[3] = {nullptr, nullptr, nullptr};
-    int rows = 0, ld = 0, np = 0;
-    CUtensorMap map[3];    // box [128 rows x 64 cols]: K-major A operand of the layer GEMMs
-    CUtensorMap mapk[3];   // box [ 64 rows x 64 cols]: MN-major operand of the weight-gradient GEMMs
+    __nv_bfloat16* p[2] = {nullptr, nullptr};   // hi / lo plane (16-bit storage; half or bfloat16 by use)
+    int rows = 0, ld = 0;
+    CUtensorMap map[2];    // box [box_rows x 64 cols]: K-major operand of the layer GEMMs
+    CUtensorMap mapk[2];   // box [ 64 rows x 64 cols]: MN-major operand of the weight-gradient GEMMs
 };
 struct TcWeight {
-    TcPlane p;
-    int N = 0, K = 0;
-    int BN[2] = {0, 0}, n_tiles[2] = {0, 0};   // variant 0: NP = 3 (BN <= 128), 1: NP = 2 (BN <= 256)
-    CUtensorMap mapv[2][3];
+    TcPlane ph, pb;   // half planes (forward solve), bfloat16 planes (reverse sweep); box rows = BN
+    int N = 0, K = 0, BN = 0, n_tiles = 0;
 };
 struct TcF32 {
     float* p = nullptr;
@@ -578,15 +584,15 @@ struct TcState {
 };
 
 static void tc_free_plane(TcPlane& p) {
-    for (int q = 0; q < 3; ++q) { cudaFree(p.p[q]); p.p[q] = nullptr; }
-    p.rows = p.ld = p.np = 0;
+    for (int q = 0; q < 2; ++q) { cudaFree(p.p[q]); p.p[q] = nullptr; }
+    p.rows = p.ld = 0;
 }
 static void tc_free_f32(TcF32& f) { cudaFree(f.p); f.p = nullptr; f.rows = f.ld = 0; }
-static int tc_alloc_plane(cnf_handle* h, TcPlane& p, int rows, int ld, int box_rows, int np = 3, bool kmap = true) {
+static int tc_alloc_plane(cnf_handle* h, TcPlane& p, int rows, int ld, int box_rows, bool kmap = true) {
     tc_free_plane(p);
-    p.rows = rows; p.ld = ld; p.np = np;
+    p.rows = rows; p.ld = ld;
     size_t bytes = (size_t)rows * ld * sizeof(__nv_bfloat16);
-    for (int q = 0; q < np; ++q) {
+    for (int q = 0; q < 2; ++q) {
         CNF_CUDA(cudaMalloc(&p.p[q], bytes));
         CNF_CUDA(cudaMemsetAsync(p.p[q], 0, bytes, h->stream));
         if (!tc_make_map(&p.map[q], p.p[q], rows, ld, ld, box_rows) ||
@@ -620,7 +626,9 @@ bool tc_supported(const cnf_config& c, int mode) {
 void tc_free(cnf_handle* h) {
     TcState* s = (TcState*)h->tc_state;
     if (!s) return;
-    for (int l = 0; l < CNF_MAX_LAYERS; ++l) { tc_free_plane(s->wf[l].p); tc_free_plane(s->wb[l].p); }
+    for (int l = 0; l < CNF_MAX_LAYERS; ++l) {
+        tc_free_plane(s->wf[l].ph); tc_free_plane(s->wf[l].pb); tc_free_plane(s->wb[l].ph); tc_free_plane(s->wb[l].pb);
+    }
     for (int l = 0; l <= CNF_MAX_LAYERS; ++l) {
         tc_free_plane(s->H[l]); tc_free_plane(s->G[l]); tc_free_plane(s->QB[l]); tc_free_plane(s->PB[l]);
         tc_free_f32(s->Q[l]);
@@ -637,24 +645,15 @@ static int tc_setup_weight(cnf_handle* h, TcWeight& w, const float* W, int dout,
     w.N = Nvalid;
     w.K = pad_to(transpose ? dout : din, TC_BK);
     const int n16 = pad_to(Nvalid, 16);
-    int rows = 0;
-    for (int v = 0; v < 2; ++v) {
-        const int cap = v == 0 ? 128 : 256;   // NP = 3: 3 planes of A and B per stage, 96 KB at BN = 128
-        w.BN[v] = n16 < cap ? n16 : cap;
-        w.n_tiles[v] = (n16 + w.BN[v] - 1) / w.BN[v];
-        if (w.n_tiles[v] * w.BN[v] > rows) rows = w.n_tiles[v] * w.BN[v];
+    w.BN = n16 < 256 ? n16 : 256;   // two planes of A and B per stage: 96 KB at BN = 256
+    w.n_tiles = (n16 + w.BN - 1) / w.BN;
+    const int rows = w.n_tiles * w.BN;
+    if (w.ph.rows != rows || w.ph.ld != w.K) {
+        int rc;
+        if ((rc = tc_alloc_plane(h, w.ph, rows, w.K, w.BN, false))) return rc;
+        if ((rc = tc_alloc_plane(h, w.pb, rows, w.K, w.BN, false))) return rc;
     }
-    if (w.p.rows != rows || w.p.ld != w.K) {
-        int rc = tc_alloc_plane(h, w.p, rows, w.K, w.BN[0], 3, false);
-        if (rc) return rc;
-        for (int v = 0; v < 2; ++v)
-            for (int q = 0; q < 3; ++q)
-                if (!tc_make_map(&w.mapv[v][q], w.p.p[q], rows, w.K, w.K, w.BN[v])) {
-                    h->err = "cuTensorMapEncodeTiled failed";
-                    return CNF_ERR_CUDA;
-                }
-    }
-    k_tc_weights<<<296, 256, 0, h->stream>>>(W, dout, din, w.p.p[0], w.p.p[1], w.p.p[2], rows, w.K, transpose);
+    k_tc_weights<<<296, 256, 0, h->stream>>>(W, dout, din, w.ph.p[0], w.ph.p[1], w.pb.p[0], w.pb.p[1], rows, w.K, transpose);
     h->launches++;
     return CNF_OK;
 }
@@ -669,9 +668,9 @@ int tc_set_params(cnf_handle* h) {
         cudaDeviceProp prop;
         if (cudaGetDeviceProperties(&prop, h->device) == cudaSuccess) s->sms = prop.multiProcessorCount;
         CNF_CUDA(cudaMalloc(&s->dyn, sizeof(TcDyn)));
-        CNF_CUDA(cudaFuncSetAttribute(k_tc_gemm<3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        CNF_CUDA(cudaFuncSetAttribute(k_tc_gemm<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        CNF_CUDA(cudaFuncSetAttribute(k_tc_gemm<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        CNF_CUDA(cudaFuncSetAttribute(k_tc_gemm<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        CNF_CUDA(cudaFuncSetAttribute(k_tc_gemm<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        CNF_CUDA(cudaFuncSetAttribute(k_tc_gemm<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     }
     TcState* s = (TcState*)h->tc_state;
     s->L = c.n_layers;
@@ -686,10 +685,10 @@ int tc_set_params(cnf_handle* h) {
     return CNF_OK;
 }
 
-// bytes of activation workspace per sample row: forward planes (3) + reverse-sweep planes (2) and fp32 side arrays
+// bytes of activation workspace per sample row: H/G planes + reverse-sweep planes and fp32 side arrays
 static long long tc_row_bytes(const cnf_config& c) {
     long long b = 0;
-    for (int l = 0; l <= c.n_layers; ++l) b += 2LL * pad_to(c.dims[l], TC_BK) * 3 * 2;
+    for (int l = 0; l <= c.n_layers; ++l) b += 2LL * pad_to(c.dims[l], TC_BK) * 2 * 2;
     for (int l = 1; l <= c.n_layers; ++l) b += (long long)(pad_to(c.dims[l - 1], TC_BK) + pad_to(c.dims[l], TC_BK)) * 2 * 2;
     for (int l = 1; l < c.n_layers; ++l) b += 4LL * pad_to(c.dims[l], TC_BK);
     b += 8LL * pad_to(c.D, TC_BK);
@@ -718,22 +717,22 @@ static int tc_ensure_acts(cnf_handle* h, TcState* s, long long Bs) {
     return CNF_OK;
 }
 
-template <int NP, bool BWD>
+template <int PREC, bool BWD>
 static void tc_launch_gemm(cnf_handle* h, TcState* s, const TcPlane& A, const TcWeight& B, int mc, const TcEpi& ep) {
-    const int v = NP == 2 ? 1 : 0;
-    const int BN = B.BN[v], n_tiles = B.n_tiles[v];
+    const int BN = B.BN, n_tiles = B.n_tiles;
     const int m_tiles = mc / TC_BM;
     const int nk = B.K / TC_BK;
-    const int stage_bytes = NP * (TC_BM * 128 + BN * 128);
+    const int stage_bytes = 2 * (TC_BM * 128 + BN * 128);
     int nstage = (220 * 1024 - 1024) / stage_bytes;
     if (nstage > 6) nstage = 6;
     if (nstage < 2) nstage = 2;
     const int smem = nstage * stage_bytes + 1024 + (int)sizeof(TcSmemCtl) + 64;
     int grid = m_tiles * n_tiles;
     if (grid > s->sms) grid = s->sms;
+    const TcPlane& Bp = PREC == 0 ? B.ph : B.pb;
     TcMaps mp;
-    for (int q = 0; q < NP; ++q) { mp.a[q] = A.map[q]; mp.b[q] = B.mapv[v][q]; }
-    k_tc_gemm<NP, BWD><<<grid, TC_THREADS, smem, h->stream>>>(mp, m_tiles, n_tiles, BN, nk, nstage, ep);
+    for (int q = 0; q < 2; ++q) { mp.a[q] = A.map[q]; mp.b[q] = Bp.map[q]; }
+    k_tc_gemm<PREC, BWD><<<grid, TC_THREADS, smem, h->stream>>>(mp, m_tiles, n_tiles, BN, nk, nstage, ep);
     h->launches++;
 }
 
@@ -748,7 +747,7 @@ static TcEpi tc_base_epi(cnf_handle* h, TcState* s, const CnfBufs& bf, long long
 }
 
 // forward chain h_0 -> h_1 .. h_{L-1} (planes H[l]) of one chunk; the last layer is left to the caller
-template <int NP>
+template <int PREC>
 static void tc_forward_hidden(cnf_handle* h, TcState* s, const TcEpi& base, int mc) {
     const cnf_config& c = h->cfg;
     for (int l = 0; l < c.n_layers - 1; ++l) {
@@ -756,9 +755,9 @@ static void tc_forward_hidden(cnf_handle* h, TcState* s, const TcEpi& base, int 
         ep.bias = h->d_theta + h->b_off[l];
         ep.N = c.dims[l + 1];
         ep.kind = TC_FWD_HIDDEN;
-        for (int q = 0; q < 3; ++q) ep.out[q] = s->H[l + 1].p[q];
+        for (int q = 0; q < 2; ++q) ep.out[q] = s->H[l + 1].p[q];
         ep.ld_out = s->H[l + 1].ld;
-        tc_launch_gemm<NP, false>(h, s, s->H[l], s->wf[l], mc, ep);
+        tc_launch_gemm<PREC, false>(h, s, s->H[l], s->wf[l], mc, ep);
     }
 }
 
@@ -776,19 +775,19 @@ int tc_eval(cnf_handle* h, const CnfBufs& bf, const float* src, int kidx, float*
         const int mc = (int)((bf.Bs - row0) < s->Mc ? (bf.Bs - row0) : s->Mc);
         TcEpi base = tc_base_epi(h, s, bf, row0, check_done);
         // h_0 = [z; ys] planes (+ resolve the output buffer)
-        k_tc_prep<<<(mc + 255) / 256, 256, 0, h->stream>>>(h->d_ctrl, bf, src, c.D, bf.ys, c.C, row0, mc, s->H[0].p[0],
-                                                          s->H[0].p[1], s->H[0].p[2], s->H[0].ld, kidx, kout_fixed, s->dyn, check_done);
+        k_tc_prep<0><<<(mc + 255) / 256, 256, 0, h->stream>>>(h->d_ctrl, bf, src, c.D, bf.ys, c.C, row0, mc, s->H[0].p[0],
+                                                          s->H[0].p[1], s->H[0].ld, kidx, kout_fixed, s->dyn, check_done);
         h->launches++;
-        tc_forward_hidden<3>(h, s, base, mc);
+        tc_forward_hidden<0>(h, s, base, mc);
         {
             TcEpi ep = base;
             ep.bias = h->d_theta + h->b_off[L - 1];
             ep.N = c.dims[L];
             ep.kind = TC_FWD_LAST;
             ep.vjp = jvp ? 0 : 1;
-            for (int q = 0; q < 3; ++q) ep.out[q] = s->G[L].p[q];
+            for (int q = 0; q < 2; ++q) ep.out[q] = s->G[L].p[q];
             ep.ld_out = s->G[L].ld;
-            tc_launch_gemm<3, false>(h, s, s->H[L - 1], s->wf[L - 1], mc, ep);
+            tc_launch_gemm<0, false>(h, s, s->H[L - 1], s->wf[L - 1], mc, ep);
         }
         if (!jvp) {
             // reverse chain: g_{l} = (g_{l+1} W_{l+1}) .* (1 - h_l^2), v = (g_1 W_1)[0:D]
@@ -797,18 +796,18 @@ int tc_eval(cnf_handle* h, const CnfBufs& bf, const float* src, int kidx, float*
                 if (l > 0) {
                     ep.kind = TC_BWD_HIDDEN;
                     ep.N = c.dims[l];
-                    for (int q = 0; q < 3; ++q) { ep.hp[q] = s->H[l].p[q]; ep.out[q] = s->G[l].p[q]; }
+                    for (int q = 0; q < 2; ++q) { ep.hp[q] = s->H[l].p[q]; ep.out[q] = s->G[l].p[q]; }
                     ep.ld_h = s->H[l].ld; ep.ld_out = s->G[l].ld;
                 } else {
                     ep.kind = TC_BWD_LAST;
                     ep.N = c.D;
                 }
-                tc_launch_gemm<3, false>(h, s, s->G[l + 1], s->wb[l], mc, ep);
+                tc_launch_gemm<0, false>(h, s, s->G[l + 1], s->wb[l], mc, ep);
             }
         } else {
             // tangent chain: tau_0 = eps, tau_l = (tau_{l-1} W_l^T) .* (1 - h_l^2), J eps = tau_L
-            k_tc_prep<<<(mc + 255) / 256, 256, 0, h->stream>>>(h->d_ctrl, bf, bf.eps, c.D, nullptr, 0, row0, mc,
-                                                              s->G[0].p[0], s->G[0].p[1], s->G[0].p[2], s->G[0].ld, 0,
+            k_tc_prep<0><<<(mc + 255) / 256, 256, 0, h->stream>>>(h->d_ctrl, bf, bf.eps, c.D, nullptr, 0, row0, mc,
+                                                              s->G[0].p[0], s->G[0].p[1], s->G[0].ld, 0,
                                                               nullptr, nullptr,
                                                               check_done);
             h->launches++;
@@ -817,14 +816,14 @@ int tc_eval(cnf_handle* h, const CnfBufs& bf, const float* src, int kidx, float*
                 ep.N = c.dims[l + 1];
                 if (l < L - 1) {
                     ep.kind = TC_BWD_HIDDEN;
-                    for (int q = 0; q < 3; ++q) { ep.hp[q] = s->H[l + 1].p[q]; ep.out[q] = s->G[l + 1].p[q]; }
+                    for (int q = 0; q < 2; ++q) { ep.hp[q] = s->H[l + 1].p[q]; ep.out[q] = s->G[l + 1].p[q]; }
                     ep.ld_h = s->H[l + 1].ld; ep.ld_out = s->G[l + 1].ld;
                 } else {
                     ep.kind = TC_JVP_LAST;
                 }
                 // the seed planes G[0] = [eps; 0] have the first layer's padded K width, so the
                 // condition columns of W_1 meet zeros (Jacobian w.r.t. z only)
-                tc_launch_gemm<3, false>(h, s, l == 0 ? s->G[0] : s->G[l], s->wf[l], mc, ep);
+                tc_launch_gemm<0, false>(h, s, l == 0 ? s->G[0] : s->G[l], s->wf[l], mc, ep);
             }
         }
     }
@@ -843,16 +842,16 @@ int tc_eval_z(cnf_handle* h, const CnfBufs& bf, const float* src, float* kout) {
     for (long long row0 = 0; row0 < bf.Bs; row0 += s->Mc) {
         const int mc = (int)((bf.Bs - row0) < s->Mc ? (bf.Bs - row0) : s->Mc);
         TcEpi base = tc_base_epi(h, s, bf, row0, 0);
-        k_tc_prep<<<(mc + 255) / 256, 256, 0, h->stream>>>(h->d_ctrl, bf, src, c.D, bf.ys, c.C, row0, mc, s->H[0].p[0],
-                                                          s->H[0].p[1], s->H[0].p[2], s->H[0].ld, -1, kout, s->dyn, 0);
+        k_tc_prep<0><<<(mc + 255) / 256, 256, 0, h->stream>>>(h->d_ctrl, bf, src, c.D, bf.ys, c.C, row0, mc, s->H[0].p[0],
+                                                          s->H[0].p[1], s->H[0].ld, -1, kout, s->dyn, 0);
         h->launches++;
-        tc_forward_hidden<2>(h, s, base, mc);
+        tc_forward_hidden<0>(h, s, base, mc);
         TcEpi ep = base;
         ep.bias = h->d_theta + h->b_off[L - 1];
         ep.N = c.dims[L];
         ep.kind = TC_FWD_LAST;
         ep.vjp = 2;
-        tc_launch_gemm<2, false>(h, s, s->H[L - 1], s->wf[L - 1], mc, ep);
+        tc_launch_gemm<0, false>(h, s, s->H[L - 1], s->wf[L - 1], mc, ep);
     }
     return CNF_OK;
 }
