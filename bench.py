@@ -272,7 +272,7 @@ def main():
     except (OSError, ValueError):
         pass
     if st["kernel_path"] == 3:
-        # tensor path: BF16x6 operand splitting executes 6 bf16 MMA flops per algorithmic flop
+        # tensor path: FP16 hi/lo operand splitting executes 3 f16 MMA flops per algorithmic flop
         peaks = {}
         try:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -284,9 +284,9 @@ def main():
                     "kernel": "one augmented_f evaluation = 2L tcgen05 layer GEMMs (k_tc_gemm) + prep",
                     "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (dense bf16, stage timed inside a "
                                    "long step)" if peaks else "fallback 1.4 PFLOP/s sustained (B200_PROFILING.md)",
-                    "note": "achieved counts ALGORITHMIC flops (F_H per sample); the kernels execute 6x that in "
-                            "bf16 MMA flops (BF16x6 split for FP32-level accuracy)",
-                    "executed_bf16_tflops": 6 * achieved, "stage_ms": stage_ms, "stage_launches": n_stage,
+                    "note": "achieved counts ALGORITHMIC flops (F_H per sample); the kernels execute 3x that in "
+                            "f16 MMA flops (FP16 hi/lo split, hi*hi + lo*hi + hi*lo, for FP32-level accuracy)",
+                    "executed_f16_tflops": 3 * achieved, "stage_ms": stage_ms, "stage_launches": n_stage,
                     "kernel_path": 3, "stage_share_of_step": ms_stage / ms_dev if ms_dev else None}
     else:
         roofline = {"bound": "fp32_fma", "achieved": achieved, "peak": pk.value, "unit": "TFLOP/s",
