@@ -16,16 +16,16 @@
 //     2x the tensor work.)  Inputs are assumed to lie inside the half range (|h_0| < 6e4).
 //   PREC 1, reverse sweep: bfloat16 planes (BF16x3, ~1e-5): cotangents scale with dt/B and need
 //     the FP32 exponent range; the gradient tolerance is 1e-3.
-// Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (one elected thread), warps 2..9 =
-// epilogue (two warps per TMEM lane quadrant, half of the columns each); two TMEM accumulator
-// buffers so the epilogue of tile i overlaps the MMAs of tile i+1.
+// Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (one elected thread), warps 2..17 =
+// epilogue (four warps per TMEM lane quadrant, every fourth 16-column chunk each); two TMEM
+// accumulator buffers so the epilogue of tile i overlaps the MMAs of tile i+1.
 #include "cnf_internal.h"
 #include "cnf_tc_ptx.cuh"
 #include <cuda.h>
 
 #define TC_BM 128
 #define TC_BK 64            // bf16 elements per 128-byte swizzled row
-#define TC_THREADS 320      // 10 warps
+#define TC_THREADS 576      // 18 warps: TMA, MMA, 16 epilogue
 #define TC_EPI_WARP0 2
 
 enum {
@@ -98,28 +98,42 @@ struct TcMaps { CUtensorMap a[2], b[2]; };   // A planes, B planes
 struct TcSmemCtl {
     uint64_t full[8], empty[8], tfull[2], tempty[2];
     uint32_t tmem_base;
+    float2 red[2][4][4][32];   // [tile parity][lane quadrant][warp of the quadrant][lane]: row reductions
 };
 
-// ---- epilogue helpers: one thread = one sample row; v = 32 accumulator columns c0..c0+31
+// ---- epilogue helpers: one thread = one sample row, 16 accumulator columns per step.
+// 16 epilogue warps: warp w may touch TMEM lane quadrant w & 3; the four warps of a quadrant take
+// every fourth 16-column chunk, so each scheduler has four epilogue warps to hide latencies with.
+#define TC_CW 16
+
+// tanh(x) = 1 - 2 / (exp(2x) + 1) on the SFU (ex2.approx + rcp.approx): absolute error <= 4e-7,
+// exact saturation; five instructions instead of the sixteen of the NNlib rational
+__device__ __forceinline__ float tc_tanh(float x) {
+    float t, r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(x * 2.8853900817779268f));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(t + 1.0f));
+    return fmaf(-2.0f, r, 1.0f);
+}
+
 template <int PREC>
-__device__ __forceinline__ void tc_store_planes32(const float (&x)[32], __nv_bfloat16* const (&dst)[2], long long off) {
-    uint32_t pk[2][16];
+__device__ __forceinline__ void tc_store_planes16(const float (&x)[TC_CW], __nv_bfloat16* const (&dst)[2], long long off) {
+    uint32_t pk[2][8];
 #pragma unroll
-    for (int j = 0; j < 16; ++j) tc_split2<PREC>(x[2 * j], x[2 * j + 1], pk[0][j], pk[1][j]);
+    for (int j = 0; j < 8; ++j) tc_split2<PREC>(x[2 * j], x[2 * j + 1], pk[0][j], pk[1][j]);
 #pragma unroll
     for (int q = 0; q < 2; ++q) {
         uint4* d = reinterpret_cast<uint4*>(dst[q] + off);
-#pragma unroll
-        for (int j = 0; j < 4; ++j) d[j] = make_uint4(pk[q][4 * j], pk[q][4 * j + 1], pk[q][4 * j + 2], pk[q][4 * j + 3]);
+        d[0] = make_uint4(pk[q][0], pk[q][1], pk[q][2], pk[q][3]);
+        d[1] = make_uint4(pk[q][4], pk[q][5], pk[q][6], pk[q][7]);
     }
 }
 
 template <int PREC>
-__device__ __forceinline__ void tc_load_planes32(const __nv_bfloat16* const (&src)[2], long long off, float (&h)[32]) {
+__device__ __forceinline__ void tc_load_planes16(const __nv_bfloat16* const (&src)[2], long long off, float (&h)[TC_CW]) {
     const uint4* s0 = reinterpret_cast<const uint4*>(src[0] + off);
     const uint4* s1 = reinterpret_cast<const uint4*>(src[1] + off);
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
+    for (int j = 0; j < 2; ++j) {
         const uint4 a = __ldg(s0 + j), b = __ldg(s1 + j);
         const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, bw[4] = {b.x, b.y, b.z, b.w};
 #pragma unroll
@@ -131,181 +145,213 @@ __device__ __forceinline__ void tc_load_planes32(const __nv_bfloat16* const (&sr
     }
 }
 
-__device__ __forceinline__ void tc_load_f32x32(const float* src, float (&x)[32]) {
+__device__ __forceinline__ void tc_load_f32x16(const float* src, float (&x)[TC_CW]) {
     const float4* p = reinterpret_cast<const float4*>(src);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
+    for (int j = 0; j < 4; ++j) {
         float4 v = p[j];
         x[4 * j] = v.x; x[4 * j + 1] = v.y; x[4 * j + 2] = v.z; x[4 * j + 3] = v.w;
     }
 }
-__device__ __forceinline__ void tc_store_f32x32(float* dst, const float (&x)[32]) {
+__device__ __forceinline__ void tc_store_f32x16(float* dst, const float (&x)[TC_CW]) {
     float4* p = reinterpret_cast<float4*>(dst);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) p[j] = make_float4(x[4 * j], x[4 * j + 1], x[4 * j + 2], x[4 * j + 3]);
+    for (int j = 0; j < 4; ++j) p[j] = make_float4(x[4 * j], x[4 * j + 1], x[4 * j + 2], x[4 * j + 3]);
+}
+// 16 consecutive bias values (the same for every lane): vector loads when the caller's layout allows
+__device__ __forceinline__ void tc_load_bias16(const float* b, float (&x)[TC_CW]) {
+    if ((reinterpret_cast<uintptr_t>(b) & 15) == 0) {
+        const float4* p = reinterpret_cast<const float4*>(b);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            float4 v = __ldg(p + j);
+            x[4 * j] = v.x; x[4 * j + 1] = v.y; x[4 * j + 2] = v.z; x[4 * j + 3] = v.w;
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < TC_CW; ++j) x[j] = __ldg(b + j);
+    }
+}
+
+// sum of (a, b) over the four warps of a TMEM lane quadrant (same lane = same sample row);
+// double-buffered by tile parity, so one named barrier per reduction is enough
+__device__ __forceinline__ float2 tc_quad_reduce(TcSmemCtl* ctl, int quad, int sub, int lane, int par, float a, float b) {
+    ctl->red[par][quad][sub][lane] = make_float2(a, b);
+    asm volatile("bar.sync %0, 128;" ::"r"(quad + 1) : "memory");
+    float2 r = make_float2(0.0f, 0.0f);
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+        const float2 p = ctl->red[par][quad][s][lane];
+        r.x += p.x; r.y += p.y;
+    }
+    return r;
 }
 
 // ---- forward-solve epilogue of one 128 x BN tile (kinds TC_*)
 template <int PREC>
-__device__ __forceinline__ void tc_epilogue_fwd(const TcEpi& ep, uint32_t tbase, int mb, int nb, int BN,
-                                                int quad, int half, int lane) {
+__device__ __forceinline__ void tc_epilogue_fwd(const TcEpi& ep, TcSmemCtl* ctl, uint32_t tbase, int mb, int nb, int BN,
+                                                int quad, int sub, int lane, int par) {
     const long long rloc = (long long)mb * TC_BM + quad * 32 + lane;   // row inside the chunk
     const long long grow = ep.row0 + rloc;                               // global sample
     const bool last_kind = (ep.kind == TC_FWD_LAST || ep.kind == TC_BWD_LAST || ep.kind == TC_JVP_LAST);
-    const int nchunk = (BN + 31) / 32;
+    const int nchunk = (BN + TC_CW - 1) / TC_CW;
     if (!last_kind) {
-        // column chunks are split between the two warps of a quadrant
-        for (int ch = half; ch < nchunk; ch += 2) {
-            const int c0 = ch * 32, ng = nb * BN + c0;   // global column of v[0]
-            uint32_t v[32];
-            tc::tmem_ld_32x32(tbase + c0, v);
+        for (int ch = sub; ch < nchunk; ch += 4) {
+            const int c0 = ch * TC_CW, ng = nb * BN + c0;   // global column of v[0]
+            uint32_t v[TC_CW];
+            tc::tmem_ld_32x16(tbase + c0, v);
             tc::tmem_ld_wait();
             if (ng >= ep.N) continue;
-            float x[32];
+            float x[TC_CW];
             if (ep.kind == TC_FWD_HIDDEN) {
+                float b[TC_CW];
+                tc_load_bias16(ep.bias + ng, b);
 #pragma unroll
-                for (int j = 0; j < 32; ++j) x[j] = cnf_tanh_fastpath(__uint_as_float(v[j]) + __ldg(ep.bias + ng + j));
+                for (int j = 0; j < TC_CW; ++j) x[j] = tc_tanh(__uint_as_float(v[j]) + b[j]);
             } else {   // BWD_HIDDEN: acc .* (1 - h^2)
-                float h[32];
-                tc_load_planes32<PREC>(ep.hp, rloc * ep.ld_h + ng, h);
+                float h[TC_CW];
+                tc_load_planes16<PREC>(ep.hp, rloc * ep.ld_h + ng, h);
 #pragma unroll
-                for (int j = 0; j < 32; ++j) x[j] = __uint_as_float(v[j]) * fmaf(-h[j], h[j], 1.0f);
+                for (int j = 0; j < TC_CW; ++j) x[j] = __uint_as_float(v[j]) * fmaf(-h[j], h[j], 1.0f);
             }
-            tc_store_planes32<PREC>(x, ep.out, rloc * ep.ld_out + ng);
+            tc_store_planes16<PREC>(x, ep.out, rloc * ep.ld_out + ng);
         }
-    } else if (half == 0) {
-        // per-sample reductions over all D columns: one warp per quadrant walks every chunk
-        float s0 = 0.0f, s1 = 0.0f;
-        for (int ch = 0; ch < nchunk; ++ch) {
-            const int c0 = ch * 32;
-            uint32_t v[32];
-            tc::tmem_ld_32x32(tbase + c0, v);
-            tc::tmem_ld_wait();
-            if (ep.kind == TC_FWD_LAST) {
-                float g[32];
-#pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                    const int n = c0 + j;
-                    g[j] = 0.0f;
-                    if (n < ep.D) {
-                        const float y = cnf_tanh_fastpath(__uint_as_float(v[j]) + __ldg(ep.bias + n));
-                        ep.kout[(long long)n * ep.Bs + grow] = y;
-                        s0 = fmaf(y, y, s0);
-                        if (ep.vjp == 1) g[j] = ep.eps[(long long)n * ep.Bs + grow] * fmaf(-y, y, 1.0f);
-                    }
-                }
-                if (ep.vjp == 1) tc_store_planes32<PREC>(g, ep.out, rloc * ep.ld_out + c0);
-            } else {
-#pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                    const int n = c0 + j;
-                    if (n < ep.D) {
-                        float vv = __uint_as_float(v[j]);
-                        if (ep.kind == TC_JVP_LAST) {
-                            const float y = ep.kout[(long long)n * ep.Bs + grow];
-                            vv *= fmaf(-y, y, 1.0f);
-                        }
-                        s0 = fmaf(-vv, ep.eps[(long long)n * ep.Bs + grow], s0);
-                        s1 = fmaf(vv, vv, s1);
-                    }
-                }
-            }
-        }
+        return;
+    }
+    // per-sample reductions over all D columns: partial sums per warp, combined per quadrant
+    float s0 = 0.0f, s1 = 0.0f;
+    for (int ch = sub; ch < nchunk; ch += 4) {
+        const int c0 = ch * TC_CW;
+        uint32_t v[TC_CW];
+        tc::tmem_ld_32x16(tbase + c0, v);
+        tc::tmem_ld_wait();
+        if (c0 >= ep.D) continue;
         if (ep.kind == TC_FWD_LAST) {
-            if (ep.vjp != 2)
-                ep.kout[(long long)(ep.D + 1) * ep.Bs + grow] = (ep.flags & CNF_FLAG_NORM_Z) ? sqrtf(s0) : 0.0f;
+            float g[TC_CW];
+#pragma unroll
+            for (int j = 0; j < TC_CW; ++j) {
+                const int n = c0 + j;
+                g[j] = 0.0f;
+                if (n < ep.D) {
+                    const float y = tc_tanh(__uint_as_float(v[j]) + __ldg(ep.bias + n));
+                    ep.kout[(long long)n * ep.Bs + grow] = y;
+                    s0 = fmaf(y, y, s0);
+                    if (ep.vjp == 1) g[j] = ep.eps[(long long)n * ep.Bs + grow] * fmaf(-y, y, 1.0f);
+                }
+            }
+            if (ep.vjp == 1) tc_store_planes16<PREC>(g, ep.out, rloc * ep.ld_out + c0);
         } else {
-            ep.kout[(long long)ep.D * ep.Bs + grow] = s0;
-            ep.kout[(long long)(ep.D + 2) * ep.Bs + grow] = (ep.flags & CNF_FLAG_NORM_J) ? sqrtf(s1) : 0.0f;
+#pragma unroll
+            for (int j = 0; j < TC_CW; ++j) {
+                const int n = c0 + j;
+                if (n < ep.D) {
+                    float vv = __uint_as_float(v[j]);
+                    if (ep.kind == TC_JVP_LAST) {
+                        const float y = ep.kout[(long long)n * ep.Bs + grow];
+                        vv *= fmaf(-y, y, 1.0f);
+                    }
+                    s0 = fmaf(-vv, ep.eps[(long long)n * ep.Bs + grow], s0);
+                    s1 = fmaf(vv, vv, s1);
+                }
+            }
         }
+    }
+    if (ep.kind == TC_FWD_LAST && ep.vjp == 2) return;   // zdot rows only
+    const float2 r = tc_quad_reduce(ctl, quad, sub, lane, par, s0, s1);
+    if (sub != 0) return;
+    if (ep.kind == TC_FWD_LAST) {
+        ep.kout[(long long)(ep.D + 1) * ep.Bs + grow] = (ep.flags & CNF_FLAG_NORM_Z) ? sqrtf(r.x) : 0.0f;
+    } else {
+        ep.kout[(long long)ep.D * ep.Bs + grow] = r.x;
+        ep.kout[(long long)(ep.D + 2) * ep.Bs + grow] = (ep.flags & CNF_FLAG_NORM_J) ? sqrtf(r.y) : 0.0f;
     }
 }
 
-// ---- reverse-sweep epilogue of one 128 x BN tile (kinds TCB_*, two bf16 planes)
-__device__ __forceinline__ void tc_epilogue_bwd(const TcEpi& ep, uint32_t tbase, int mb, int nb, int BN,
-                                                int quad, int half, int lane) {
+// ---- reverse-sweep epilogue of one 128 x BN tile (kinds TCB_*, bfloat16 planes)
+__device__ __forceinline__ void tc_epilogue_bwd(const TcEpi& ep, TcSmemCtl* ctl, uint32_t tbase, int mb, int nb, int BN,
+                                                int quad, int sub, int lane, int par) {
     const long long rloc = (long long)mb * TC_BM + quad * 32 + lane;
     const long long grow = ep.row0 + rloc;
     const bool live = grow < (long long)ep.B;
-    const int nchunk = (BN + 31) / 32;
+    const int nchunk = (BN + TC_CW - 1) / TC_CW;
     const float dt = *ep.dtp;
     const float wgt = dt * c_A[6][ep.stage];
     if (ep.kind == TCB_FWD_LAST) {
-        if (half != 0) return;
         float s0 = 0.0f;
-        for (int ch = 0; ch < nchunk; ++ch) {
-            const int c0 = ch * 32;
-            uint32_t v[32];
-            tc::tmem_ld_32x32(tbase + c0, v);
+        for (int ch = sub; ch < nchunk; ch += 4) {
+            const int c0 = ch * TC_CW;
+            uint32_t v[TC_CW];
+            tc::tmem_ld_32x16(tbase + c0, v);
             tc::tmem_ld_wait();
-            float y[32], g[32];
+            float y[TC_CW], g[TC_CW];
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
+            for (int j = 0; j < TC_CW; ++j) {
                 const int n = c0 + j;
                 y[j] = 0.0f; g[j] = 0.0f;
                 if (n < ep.D) {
-                    y[j] = cnf_tanh_fastpath(__uint_as_float(v[j]) + __ldg(ep.bias + n));
+                    y[j] = tc_tanh(__uint_as_float(v[j]) + __ldg(ep.bias + n));
                     s0 = fmaf(y[j], y[j], s0);
                     g[j] = ep.eps[(long long)n * ep.Bs + grow] * fmaf(-y[j], y[j], 1.0f);
                 }
             }
-            tc_store_f32x32(ep.f32a + rloc * ep.ld_f + c0, y);
-            tc_store_planes32<1>(g, ep.out, rloc * ep.ld_out + c0);
+            tc_store_f32x16(ep.f32a + rloc * ep.ld_f + c0, y);
+            tc_store_planes16<1>(g, ep.out, rloc * ep.ld_out + c0);
         }
-        const float inv = (live && (ep.flags & CNF_FLAG_NORM_Z) && s0 > 0.0f) ? wgt * ep.c_E / sqrtf(s0) : 0.0f;
-        for (int ch = 0; ch < nchunk; ++ch) {
-            const int c0 = ch * 32;
-            float y[32], yb[32];
-            tc_load_f32x32(ep.f32a + rloc * ep.ld_f + c0, y);
+        const float2 r = tc_quad_reduce(ctl, quad, sub, lane, par, s0, 0.0f);
+        const float inv = (live && (ep.flags & CNF_FLAG_NORM_Z) && r.x > 0.0f) ? wgt * ep.c_E / sqrtf(r.x) : 0.0f;
+        for (int ch = sub; ch < nchunk; ch += 4) {
+            const int c0 = ch * TC_CW;
+            float y[TC_CW], yb[TC_CW];
+            tc_load_f32x16(ep.f32a + rloc * ep.ld_f + c0, y);
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
+            for (int j = 0; j < TC_CW; ++j) {
                 const int n = c0 + j;
                 yb[j] = (live && n < ep.D) ? fmaf(inv, y[j], ep.abar[(long long)n * ep.Bs + grow]) : 0.0f;
             }
-            tc_store_f32x32(ep.f32b + rloc * ep.ld_f + c0, yb);
+            tc_store_f32x16(ep.f32b + rloc * ep.ld_f + c0, yb);
         }
         return;
     }
     if (ep.kind == TCB_BWD_LAST) {
-        if (half != 0) return;
         float s1 = 0.0f;
-        for (int ch = 0; ch < nchunk; ++ch) {
-            const int c0 = ch * 32;
-            uint32_t v[32];
-            tc::tmem_ld_32x32(tbase + c0, v);
+        for (int ch = sub; ch < nchunk; ch += 4) {
+            const int c0 = ch * TC_CW;
+            uint32_t v[TC_CW];
+            tc::tmem_ld_32x16(tbase + c0, v);
             tc::tmem_ld_wait();
 #pragma unroll
-            for (int j = 0; j < 32; ++j)
+            for (int j = 0; j < TC_CW; ++j)
                 if (c0 + j < ep.D) s1 = fmaf(__uint_as_float(v[j]), __uint_as_float(v[j]), s1);
         }
-        const float inv = (live && (ep.flags & CNF_FLAG_NORM_J) && s1 > 0.0f) ? wgt * ep.c_n / sqrtf(s1) : 0.0f;
+        const float2 r = tc_quad_reduce(ctl, quad, sub, lane, par, s1, 0.0f);
+        const float inv = (live && (ep.flags & CNF_FLAG_NORM_J) && r.x > 0.0f) ? wgt * ep.c_n / sqrtf(r.x) : 0.0f;
         const float al = live ? wgt * ep.c_l : 0.0f;
-        for (int ch = 0; ch < nchunk; ++ch) {
-            const int c0 = ch * 32;
-            uint32_t v[32];
-            tc::tmem_ld_32x32(tbase + c0, v);
+        for (int ch = sub; ch < nchunk; ch += 4) {
+            const int c0 = ch * TC_CW;
+            uint32_t v[TC_CW];
+            tc::tmem_ld_32x16(tbase + c0, v);
             tc::tmem_ld_wait();
-            float x[32];
+            float x[TC_CW];
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
+            for (int j = 0; j < TC_CW; ++j) {
                 const int n = c0 + j;
                 x[j] = (n < ep.D) ? fmaf(inv, __uint_as_float(v[j]), -al * ep.eps[(long long)n * ep.Bs + grow]) : 0.0f;
             }
-            tc_store_planes32<1>(x, ep.out, rloc * ep.ld_out + c0);
+            tc_store_planes16<1>(x, ep.out, rloc * ep.ld_out + c0);
         }
         return;
     }
-    // column-wise kinds: chunks are split between the two warps of a quadrant
-    for (int ch = half; ch < nchunk; ch += 2) {
-        const int c0 = ch * 32, ng = nb * BN + c0;
-        uint32_t v[32];
-        tc::tmem_ld_32x32(tbase + c0, v);
+    // column-wise kinds
+    for (int ch = sub; ch < nchunk; ch += 4) {
+        const int c0 = ch * TC_CW, ng = nb * BN + c0;
+        uint32_t v[TC_CW];
+        tc::tmem_ld_32x16(tbase + c0, v);
         tc::tmem_ld_wait();
         if (ng >= ep.N) continue;
-        float x[32];
+        float x[TC_CW];
         if (ep.kind == TCB_ZBAR) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
+            for (int j = 0; j < TC_CW; ++j) {
                 const int n = ng + j;
                 if (n < ep.D) {
                     const float zb = __uint_as_float(v[j]);
@@ -319,11 +365,11 @@ __device__ __forceinline__ void tc_epilogue_bwd(const TcEpi& ep, uint32_t tbase,
             continue;
         }
         if (ep.kind == TCB_GBAR_LAST) {
-            float y[32], yb[32];
-            tc_load_f32x32(ep.f32a + rloc * ep.ld_f + ng, y);
-            tc_load_f32x32(ep.f32b + rloc * ep.ld_f + ng, yb);
+            float y[TC_CW], yb[TC_CW];
+            tc_load_f32x16(ep.f32a + rloc * ep.ld_f + ng, y);
+            tc_load_f32x16(ep.f32b + rloc * ep.ld_f + ng, yb);
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
+            for (int j = 0; j < TC_CW; ++j) {
                 const int n = ng + j;
                 x[j] = 0.0f;
                 if (n < ep.D) {
@@ -332,35 +378,35 @@ __device__ __forceinline__ void tc_epilogue_bwd(const TcEpi& ep, uint32_t tbase,
                 }
             }
         } else {
-            float h[32];
-            tc_load_planes32<1>(ep.hp, rloc * ep.ld_h + ng, h);
+            float h[TC_CW];
+            tc_load_planes16<1>(ep.hp, rloc * ep.ld_h + ng, h);
             if (ep.kind == TCB_BWD_HIDDEN) {
-                float q[32];
+                float q[TC_CW];
 #pragma unroll
-                for (int j = 0; j < 32; ++j) {
+                for (int j = 0; j < TC_CW; ++j) {
                     q[j] = __uint_as_float(v[j]);
                     x[j] = q[j] * fmaf(-h[j], h[j], 1.0f);
                 }
-                tc_store_f32x32(ep.f32a + rloc * ep.ld_f + ng, q);
+                tc_store_f32x16(ep.f32a + rloc * ep.ld_f + ng, q);
             } else if (ep.kind == TCB_GBAR_HIDDEN) {
-                float q[32];
-                tc_load_f32x32(ep.f32a + rloc * ep.ld_f + ng, q);
+                float q[TC_CW];
+                tc_load_f32x16(ep.f32a + rloc * ep.ld_f + ng, q);
 #pragma unroll
-                for (int j = 0; j < 32; ++j) {
+                for (int j = 0; j < TC_CW; ++j) {
                     const float gb = __uint_as_float(v[j]);
                     q[j] *= gb;                                // dbar_l
                     x[j] = gb * fmaf(-h[j], h[j], 1.0f);      // qbar_{l+1}
                 }
-                tc_store_f32x32(ep.f32a + rloc * ep.ld_f + ng, q);
+                tc_store_f32x16(ep.f32a + rloc * ep.ld_f + ng, q);
             } else {   // TCB_HBAR_HIDDEN
-                float db[32];
-                tc_load_f32x32(ep.f32a + rloc * ep.ld_f + ng, db);
+                float db[TC_CW];
+                tc_load_f32x16(ep.f32a + rloc * ep.ld_f + ng, db);
 #pragma unroll
-                for (int j = 0; j < 32; ++j)
+                for (int j = 0; j < TC_CW; ++j)
                     x[j] = fmaf(-2.0f * h[j], db[j], __uint_as_float(v[j])) * fmaf(-h[j], h[j], 1.0f);
             }
         }
-        tc_store_planes32<1>(x, ep.out, rloc * ep.ld_out + ng);
+        tc_store_planes16<1>(x, ep.out, rloc * ep.ld_out + ng);
     }
 }
 
@@ -383,7 +429,7 @@ k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, i
     if (warp == 0 && lane == 0) {
         for (int q = 0; q < 2; ++q) { tc::tma_prefetch_desc(&mp.a[q]); tc::tma_prefetch_desc(&mp.b[q]); }
         for (int s = 0; s < nstage; ++s) { tc::mbar_init(&ctl->full[s], 1); tc::mbar_init(&ctl->empty[s], 1); }
-        for (int a = 0; a < 2; ++a) { tc::mbar_init(&ctl->tfull[a], 1); tc::mbar_init(&ctl->tempty[a], 8); }
+        for (int a = 0; a < 2; ++a) { tc::mbar_init(&ctl->tfull[a], 1); tc::mbar_init(&ctl->tempty[a], 16); }
         tc::fence_barrier_init();
     }
     if (warp == 1) tc::tmem_alloc(&ctl->tmem_base, 512);
@@ -441,9 +487,8 @@ k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, i
             }
         }
     } else {               // ===== epilogue warps
-        const int e = warp - TC_EPI_WARP0;       // 0..7
-        const int quad = warp & 3;               // TMEM lane quadrant this warp may access
-        const int half = e >> 2;                 // column half
+        const int quad = warp & 3;                    // TMEM lane quadrant this warp may access
+        const int sub = (warp - TC_EPI_WARP0) >> 2;   // 0..3: which chunks of the quadrant's columns
         int it = 0;
         for (int t = blockIdx.x; t < total; t += gridDim.x, ++it) {
             const int mb = t / n_tiles, nb = t % n_tiles;
@@ -451,8 +496,8 @@ k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, i
             tc::mbar_wait(&ctl->tfull[acc], (it >> 1) & 1);
             tc::tc_fence_after();
             const uint32_t tbase = tmem + ((uint32_t)(quad * 32) << 16) + (uint32_t)acc * 256;
-            if (BWD) tc_epilogue_bwd(ep, tbase, mb, nb, BN, quad, half, lane);
-            else tc_epilogue_fwd<PREC>(ep, tbase, mb, nb, BN, quad, half, lane);
+            if (BWD) tc_epilogue_bwd(ep, ctl, tbase, mb, nb, BN, quad, sub, lane, it & 1);
+            else tc_epilogue_fwd<PREC>(ep, ctl, tbase, mb, nb, BN, quad, sub, lane, it & 1);
             tc::tc_fence_before();
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(&ctl->tempty[acc]);
