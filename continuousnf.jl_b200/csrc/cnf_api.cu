@@ -600,7 +600,7 @@ static int ensure_bw(cnf_handle* h, long long Bs) {
     const long long need = (long long)h->cfg.D * Bs;
     if (need <= h->cap_bw) return CNF_OK;
     CNF_CUDA(cudaStreamSynchronize(h->stream));
-    for (int j = 0; j < 12; ++j) {
+    for (int j = 0; j < 13; ++j) {   // [12]: zbar scratch of the tensor-path reverse sweep
         cudaFree(h->d_bw[j]);
         h->d_bw[j] = nullptr;
         CNF_CUDA(cudaMalloc(&h->d_bw[j], (size_t)need * sizeof(float)));

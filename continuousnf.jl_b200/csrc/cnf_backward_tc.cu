@@ -170,6 +170,21 @@ k_tc_wgrad(const __grid_constant__ WgMaps mp, WgArgs ar) {
     if (warp == 1) tc::tmem_dealloc(tmem, 512);
 }
 
+// zbar (D x Bs scratch written by the TCB_ZBAR epilogue) -> ubar += zbar, kbar_j += dt a_{stage,j} zbar
+__global__ void k_zbar_apply(const float* __restrict__ zbar, const float* __restrict__ dtp, int stage,
+                             float* __restrict__ ubar, float* kb0, float* kb1, float* kb2, float* kb3, float* kb4,
+                             long long n) {
+    const float dt = *dtp;
+    float* kb[5] = {kb0, kb1, kb2, kb3, kb4};
+    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (long long)gridDim.x * blockDim.x) {
+        const float zb = zbar[e];
+        ubar[e] += zb;
+#pragma unroll
+        for (int s = 0; s < 5; ++s)
+            if (s < stage) kb[s][e] = fmaf(dt * c_A[stage][s], zb, kb[s][e]);
+    }
+}
+
 // ------------------------------------------------------------------ host side
 bool tc_bw_supported(cnf_handle* h) {
     return tc_supported(h->cfg, CNF_MODE_TRAIN) && h->tc_state != nullptr && h->cfg.trace_mode == CNF_TRACE_VJP &&
@@ -242,7 +257,7 @@ int tc_vjp_stage(cnf_handle* h, const CnfBufs& bf, const float* src, const float
         const int mc = (int)((bf.Bs - row0) < s->Mc ? (bf.Bs - row0) : s->Mc);
         TcEpi base = tc_base_epi(h, s, bf, row0, 0);
         base.kout_ind = nullptr;
-        base.abar = abar; base.ubar = ubar; base.dtp = dtp; base.stage = stage;
+        base.abar = abar; base.ubar = h->d_bw[12]; base.dtp = dtp; base.stage = stage;   // ubar field = zbar scratch
         base.c_l = c_l; base.c_E = c_E; base.c_n = c_n;
         for (int j = 0; j < 5; ++j) base.kb[j] = kb[j];
         k_tc_prep<1><<<(mc + 255) / 256, 256, 0, h->stream>>>(h->d_ctrl, bf, src, c.D, bf.ys, c.C, row0, mc, s->H[0].p[0],
@@ -308,6 +323,13 @@ int tc_vjp_stage(cnf_handle* h, const CnfBufs& bf, const float* src, const float
             }
             tc_launch_gemm<1, true>(h, s, s->PB[l], s->wb[l - 1], mc, ep);
         }
+    }
+    {
+        const long long nz = (long long)c.D * bf.Bs;
+        long long g = (nz + 255) / 256;
+        if (g > 148LL * 16) g = 148LL * 16;
+        k_zbar_apply<<<(unsigned)g, 256, 0, h->stream>>>(h->d_bw[12], dtp, stage, ubar, kb[0], kb[1], kb[2], kb[3], kb[4], nz);
+        h->launches++;
     }
     return CNF_OK;
 }

@@ -16,8 +16,8 @@
 //     2x the tensor work.)  Inputs are assumed to lie inside the half range (|h_0| < 6e4).
 //   PREC 1, reverse sweep: bfloat16 planes (BF16x3, ~1e-5): cotangents scale with dt/B and need
 //     the FP32 exponent range; the gradient tolerance is 1e-3.
-// Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (one elected thread), warps 2..17 =
-// epilogue (four warps per TMEM lane quadrant, every fourth 16-column chunk each); two TMEM
+// Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (one elected thread), warps 2..13 =
+// epilogue (three warps per TMEM lane quadrant, every third 16-column chunk each); two TMEM
 // accumulator buffers so the epilogue of tile i overlaps the MMAs of tile i+1.
 #include "cnf_internal.h"
 #include "cnf_tc_ptx.cuh"
@@ -25,7 +25,7 @@
 
 #define TC_BM 128
 #define TC_BK 64            // bf16 elements per 128-byte swizzled row
-#define TC_THREADS 576      // 18 warps: TMA, MMA, 16 epilogue
+#define TC_THREADS 448      // 14 warps: TMA, MMA, 12 epilogue
 #define TC_EPI_WARP0 2
 
 enum {
@@ -98,13 +98,51 @@ struct TcMaps { CUtensorMap a[2], b[2]; };   // A planes, B planes
 struct TcSmemCtl {
     uint64_t full[8], empty[8], tfull[2], tempty[2];
     uint32_t tmem_base;
-    float2 red[2][4][4][32];   // [tile parity][lane quadrant][warp of the quadrant][lane]: row reductions
+    float2 red[2][4][3][32];   // [tile parity][lane quadrant][warp of the quadrant][lane]: row reductions
 };
 
 // ---- epilogue helpers: one thread = one sample row, 16 accumulator columns per step.
-// 16 epilogue warps: warp w may touch TMEM lane quadrant w & 3; the four warps of a quadrant take
-// every fourth 16-column chunk, so each scheduler has four epilogue warps to hide latencies with.
+// 12 epilogue warps: warp w may touch TMEM lane quadrant w & 3; the three warps of a quadrant take
+// every third 16-column chunk, so each scheduler has three epilogue warps to hide latencies with.
+// Whatever a chunk needs from global memory besides the accumulator (the h planes for 1-h^2, the
+// fp32 side arrays, eps rows, bias) is loaded one chunk ahead into registers (TcAux) — for the
+// first chunk of a tile before the wait on the MMA — with 256-bit loads; an in-order warp that
+// loads at the point of use pays the DRAM latency once per chunk (ncu: 12 % of all stall samples
+// on the first use of the h planes) or, behind possibly-aliasing stores, once per column.
 #define TC_CW 16
+#define TC_NSUB 3
+
+struct TcAux {
+    uint32_t p[2][8];   // 16 columns of the hi / lo plane
+    float f[TC_CW];     // fp32 side array, eps rows or bias
+};
+
+__device__ __forceinline__ void tc_ld256_nc(const void* p, uint32_t (&r)[8]) {
+    asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                 : "l"(p));
+}
+__device__ __forceinline__ void tc_ld256(const float* p, float* r) {
+    asm volatile("ld.global.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(r[0]), "=f"(r[1]), "=f"(r[2]), "=f"(r[3]), "=f"(r[4]), "=f"(r[5]), "=f"(r[6]), "=f"(r[7])
+                 : "l"(p)
+                 : "memory");
+}
+__device__ __forceinline__ void tc_ld256_ncf(const float* p, float* r) {
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(r[0]), "=f"(r[1]), "=f"(r[2]), "=f"(r[3]), "=f"(r[4]), "=f"(r[5]), "=f"(r[6]), "=f"(r[7])
+                 : "l"(p));
+}
+__device__ __forceinline__ void tc_st256(void* p, const uint32_t (&r)[8]) {
+    asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(r[0]), "r"(r[1]), "r"(r[2]),
+                 "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+                 : "memory");
+}
+__device__ __forceinline__ void tc_st256f(float* p, const float* r) {
+    asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(r[0]), "f"(r[1]), "f"(r[2]),
+                 "f"(r[3]), "f"(r[4]), "f"(r[5]), "f"(r[6]), "f"(r[7])
+                 : "memory");
+}
 
 // tanh(x) = 1 - 2 / (exp(2x) + 1) on the SFU (ex2.approx + rcp.approx): absolute error <= 4e-7,
 // exact saturation; five instructions instead of the sixteen of the NNlib rational
@@ -115,148 +153,142 @@ __device__ __forceinline__ float tc_tanh(float x) {
     return fmaf(-2.0f, r, 1.0f);
 }
 
+// 16 values -> one 32-byte store per plane
 template <int PREC>
 __device__ __forceinline__ void tc_store_planes16(const float (&x)[TC_CW], __nv_bfloat16* const (&dst)[2], long long off) {
     uint32_t pk[2][8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) tc_split2<PREC>(x[2 * j], x[2 * j + 1], pk[0][j], pk[1][j]);
-#pragma unroll
-    for (int q = 0; q < 2; ++q) {
-        uint4* d = reinterpret_cast<uint4*>(dst[q] + off);
-        d[0] = make_uint4(pk[q][0], pk[q][1], pk[q][2], pk[q][3]);
-        d[1] = make_uint4(pk[q][4], pk[q][5], pk[q][6], pk[q][7]);
-    }
+    tc_st256(dst[0] + off, pk[0]);
+    tc_st256(dst[1] + off, pk[1]);
 }
-
 template <int PREC>
-__device__ __forceinline__ void tc_load_planes16(const __nv_bfloat16* const (&src)[2], long long off, float (&h)[TC_CW]) {
-    const uint4* s0 = reinterpret_cast<const uint4*>(src[0] + off);
-    const uint4* s1 = reinterpret_cast<const uint4*>(src[1] + off);
+__device__ __forceinline__ void tc_unpack_planes16(const uint32_t (&p)[2][8], float (&h)[TC_CW]) {
 #pragma unroll
-    for (int j = 0; j < 2; ++j) {
-        const uint4 a = __ldg(s0 + j), b = __ldg(s1 + j);
-        const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, bw[4] = {b.x, b.y, b.z, b.w};
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const float2 hi = tc_unpack2<PREC>(aw[k]), lo = tc_unpack2<PREC>(bw[k]);
-            h[8 * j + 2 * k] = hi.x + lo.x;
-            h[8 * j + 2 * k + 1] = hi.y + lo.y;
-        }
+    for (int k = 0; k < 8; ++k) {
+        const float2 hi = tc_unpack2<PREC>(p[0][k]), lo = tc_unpack2<PREC>(p[1][k]);
+        h[2 * k] = hi.x + lo.x;
+        h[2 * k + 1] = hi.y + lo.y;
     }
 }
-
 __device__ __forceinline__ void tc_load_f32x16(const float* src, float (&x)[TC_CW]) {
-    const float4* p = reinterpret_cast<const float4*>(src);
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        float4 v = p[j];
-        x[4 * j] = v.x; x[4 * j + 1] = v.y; x[4 * j + 2] = v.z; x[4 * j + 3] = v.w;
-    }
+    tc_ld256(src, x);
+    tc_ld256(src + 8, x + 8);
 }
 __device__ __forceinline__ void tc_store_f32x16(float* dst, const float (&x)[TC_CW]) {
-    float4* p = reinterpret_cast<float4*>(dst);
-#pragma unroll
-    for (int j = 0; j < 4; ++j) p[j] = make_float4(x[4 * j], x[4 * j + 1], x[4 * j + 2], x[4 * j + 3]);
+    tc_st256f(dst, x);
+    tc_st256f(dst + 8, x + 8);
 }
-// 16 consecutive bias values (the same for every lane): vector loads when the caller's layout allows
-__device__ __forceinline__ void tc_load_bias16(const float* b, float (&x)[TC_CW]) {
-    if ((reinterpret_cast<uintptr_t>(b) & 15) == 0) {
-        const float4* p = reinterpret_cast<const float4*>(b);
+
+// 16 rows n0..n0+15 of a read-only SoA buffer (row stride Bs) for this thread's sample; rows >= nmax read as 0
+__device__ __forceinline__ void tc_load_soa16(const float* __restrict__ base, long long Bs, long long grow, int n0,
+                                              int nmax, float (&x)[TC_CW]) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            float4 v = __ldg(p + j);
-            x[4 * j] = v.x; x[4 * j + 1] = v.y; x[4 * j + 2] = v.z; x[4 * j + 3] = v.w;
+    for (int j = 0; j < TC_CW; ++j) x[j] = (n0 + j < nmax) ? __ldg(base + (long long)(n0 + j) * Bs + grow) : 0.0f;
+}
+
+// what chunk (nb, ch) of this thread's row needs besides the accumulator, by kind
+template <int PREC, bool BWD>
+__device__ __forceinline__ void tc_aux_load(const TcEpi& ep, long long rloc, long long grow, int ng, TcAux& a) {
+    const int k = ep.kind;
+    if (!BWD) {
+        if (k == TC_FWD_HIDDEN) {
+            const float* b = ep.bias + ng;
+            if ((reinterpret_cast<uintptr_t>(b) & 31) == 0) { tc_ld256_ncf(b, a.f); tc_ld256_ncf(b + 8, a.f + 8); }
+            else {
+#pragma unroll
+                for (int j = 0; j < TC_CW; ++j) a.f[j] = __ldg(b + j);
+            }
+        } else if (k == TC_BWD_HIDDEN) {
+            tc_ld256_nc(ep.hp[0] + rloc * ep.ld_h + ng, a.p[0]);
+            tc_ld256_nc(ep.hp[1] + rloc * ep.ld_h + ng, a.p[1]);
+        } else if (k != TC_FWD_LAST || ep.vjp == 1) {
+            tc_load_soa16(ep.eps, ep.Bs, grow, ng, ep.D, a.f);
         }
     } else {
-#pragma unroll
-        for (int j = 0; j < TC_CW; ++j) x[j] = __ldg(b + j);
+        if (k == TCB_BWD_HIDDEN || k == TCB_GBAR_HIDDEN || k == TCB_HBAR_HIDDEN) {
+            tc_ld256_nc(ep.hp[0] + rloc * ep.ld_h + ng, a.p[0]);
+            tc_ld256_nc(ep.hp[1] + rloc * ep.ld_h + ng, a.p[1]);
+            if (k != TCB_BWD_HIDDEN) tc_load_f32x16(ep.f32a + rloc * ep.ld_f + ng, a.f);
+        } else if (k == TCB_FWD_LAST || k == TCB_GBAR_LAST) {
+            tc_load_soa16(ep.eps, ep.Bs, grow, ng, ep.D, a.f);
+        }
     }
 }
 
-// sum of (a, b) over the four warps of a TMEM lane quadrant (same lane = same sample row);
+// sum of (a, b) over the warps of a TMEM lane quadrant (same lane = same sample row);
 // double-buffered by tile parity, so one named barrier per reduction is enough
 __device__ __forceinline__ float2 tc_quad_reduce(TcSmemCtl* ctl, int quad, int sub, int lane, int par, float a, float b) {
     ctl->red[par][quad][sub][lane] = make_float2(a, b);
-    asm volatile("bar.sync %0, 128;" ::"r"(quad + 1) : "memory");
+    asm volatile("bar.sync %0, %1;" ::"r"(quad + 1), "n"(32 * TC_NSUB) : "memory");
     float2 r = make_float2(0.0f, 0.0f);
 #pragma unroll
-    for (int s = 0; s < 4; ++s) {
+    for (int s = 0; s < TC_NSUB; ++s) {
         const float2 p = ctl->red[par][quad][s][lane];
         r.x += p.x; r.y += p.y;
     }
     return r;
 }
 
-// ---- forward-solve epilogue of one 128 x BN tile (kinds TC_*)
+// ---- forward-solve epilogue of one 128 x BN tile (kinds TC_*); cur = aux of this warp's first chunk
 template <int PREC>
 __device__ __forceinline__ void tc_epilogue_fwd(const TcEpi& ep, TcSmemCtl* ctl, uint32_t tbase, int mb, int nb, int BN,
-                                                int quad, int sub, int lane, int par) {
+                                                int quad, int sub, int lane, int par, TcAux& cur) {
     const long long rloc = (long long)mb * TC_BM + quad * 32 + lane;   // row inside the chunk
     const long long grow = ep.row0 + rloc;                               // global sample
     const bool last_kind = (ep.kind == TC_FWD_LAST || ep.kind == TC_BWD_LAST || ep.kind == TC_JVP_LAST);
     const int nchunk = (BN + TC_CW - 1) / TC_CW;
-    if (!last_kind) {
-        for (int ch = sub; ch < nchunk; ch += 4) {
-            const int c0 = ch * TC_CW, ng = nb * BN + c0;   // global column of v[0]
-            uint32_t v[TC_CW];
-            tc::tmem_ld_32x16(tbase + c0, v);
-            tc::tmem_ld_wait();
-            if (ng >= ep.N) continue;
-            float x[TC_CW];
-            if (ep.kind == TC_FWD_HIDDEN) {
-                float b[TC_CW];
-                tc_load_bias16(ep.bias + ng, b);
-#pragma unroll
-                for (int j = 0; j < TC_CW; ++j) x[j] = tc_tanh(__uint_as_float(v[j]) + b[j]);
-            } else {   // BWD_HIDDEN: acc .* (1 - h^2)
-                float h[TC_CW];
-                tc_load_planes16<PREC>(ep.hp, rloc * ep.ld_h + ng, h);
-#pragma unroll
-                for (int j = 0; j < TC_CW; ++j) x[j] = __uint_as_float(v[j]) * fmaf(-h[j], h[j], 1.0f);
-            }
-            tc_store_planes16<PREC>(x, ep.out, rloc * ep.ld_out + ng);
-        }
-        return;
-    }
-    // per-sample reductions over all D columns: partial sums per warp, combined per quadrant
+    const int nmax = last_kind ? ep.D : ep.N;
     float s0 = 0.0f, s1 = 0.0f;
-    for (int ch = sub; ch < nchunk; ch += 4) {
-        const int c0 = ch * TC_CW;
+    for (int ch = sub; ch < nchunk; ch += TC_NSUB) {
+        const int c0 = ch * TC_CW, ng = nb * BN + c0;   // global column of v[0]
+        if (ng >= nmax) break;
+        TcAux nxt;
+        if (ch + TC_NSUB < nchunk && ng + TC_NSUB * TC_CW < nmax)
+            tc_aux_load<PREC, false>(ep, rloc, grow, ng + TC_NSUB * TC_CW, nxt);
         uint32_t v[TC_CW];
         tc::tmem_ld_32x16(tbase + c0, v);
         tc::tmem_ld_wait();
-        if (c0 >= ep.D) continue;
-        if (ep.kind == TC_FWD_LAST) {
-            float g[TC_CW];
+        float x[TC_CW];
+        if (ep.kind == TC_FWD_HIDDEN) {
+#pragma unroll
+            for (int j = 0; j < TC_CW; ++j) x[j] = tc_tanh(__uint_as_float(v[j]) + cur.f[j]);
+            tc_store_planes16<PREC>(x, ep.out, rloc * ep.ld_out + ng);
+        } else if (ep.kind == TC_BWD_HIDDEN) {   // acc .* (1 - h^2)
+            float h[TC_CW];
+            tc_unpack_planes16<PREC>(cur.p, h);
+#pragma unroll
+            for (int j = 0; j < TC_CW; ++j) x[j] = __uint_as_float(v[j]) * fmaf(-h[j], h[j], 1.0f);
+            tc_store_planes16<PREC>(x, ep.out, rloc * ep.ld_out + ng);
+        } else if (ep.kind == TC_FWD_LAST) {
 #pragma unroll
             for (int j = 0; j < TC_CW; ++j) {
-                const int n = c0 + j;
-                g[j] = 0.0f;
-                if (n < ep.D) {
-                    const float y = tc_tanh(__uint_as_float(v[j]) + __ldg(ep.bias + n));
-                    ep.kout[(long long)n * ep.Bs + grow] = y;
+                x[j] = 0.0f;
+                if (c0 + j < ep.D) {
+                    const float y = tc_tanh(__uint_as_float(v[j]) + __ldg(ep.bias + c0 + j));
+                    ep.kout[(long long)(c0 + j) * ep.Bs + grow] = y;
                     s0 = fmaf(y, y, s0);
-                    if (ep.vjp == 1) g[j] = ep.eps[(long long)n * ep.Bs + grow] * fmaf(-y, y, 1.0f);
+                    if (ep.vjp == 1) x[j] = cur.f[j] * fmaf(-y, y, 1.0f);
                 }
             }
-            if (ep.vjp == 1) tc_store_planes16<PREC>(g, ep.out, rloc * ep.ld_out + c0);
-        } else {
+            if (ep.vjp == 1) tc_store_planes16<PREC>(x, ep.out, rloc * ep.ld_out + c0);
+        } else {   // TC_BWD_LAST / TC_JVP_LAST: -eps . v and |v|^2
+            float y[TC_CW];
+            if (ep.kind == TC_JVP_LAST) tc_load_soa16(ep.kout, ep.Bs, grow, c0, ep.D, y);
 #pragma unroll
             for (int j = 0; j < TC_CW; ++j) {
-                const int n = c0 + j;
-                if (n < ep.D) {
+                if (c0 + j < ep.D) {
                     float vv = __uint_as_float(v[j]);
-                    if (ep.kind == TC_JVP_LAST) {
-                        const float y = ep.kout[(long long)n * ep.Bs + grow];
-                        vv *= fmaf(-y, y, 1.0f);
-                    }
-                    s0 = fmaf(-vv, ep.eps[(long long)n * ep.Bs + grow], s0);
+                    if (ep.kind == TC_JVP_LAST) vv *= fmaf(-y[j], y[j], 1.0f);
+                    s0 = fmaf(-vv, cur.f[j], s0);
                     s1 = fmaf(vv, vv, s1);
                 }
             }
         }
+        cur = nxt;
     }
-    if (ep.kind == TC_FWD_LAST && ep.vjp == 2) return;   // zdot rows only
+    if (!last_kind || (ep.kind == TC_FWD_LAST && ep.vjp == 2)) return;   // (vjp 2: zdot rows only)
+    // per-sample reductions over all D columns: partial sums per warp, combined per quadrant
     const float2 r = tc_quad_reduce(ctl, quad, sub, lane, par, s0, s1);
     if (sub != 0) return;
     if (ep.kind == TC_FWD_LAST) {
@@ -269,7 +301,7 @@ __device__ __forceinline__ void tc_epilogue_fwd(const TcEpi& ep, TcSmemCtl* ctl,
 
 // ---- reverse-sweep epilogue of one 128 x BN tile (kinds TCB_*, bfloat16 planes)
 __device__ __forceinline__ void tc_epilogue_bwd(const TcEpi& ep, TcSmemCtl* ctl, uint32_t tbase, int mb, int nb, int BN,
-                                                int quad, int sub, int lane, int par) {
+                                                int quad, int sub, int lane, int par, TcAux& cur) {
     const long long rloc = (long long)mb * TC_BM + quad * 32 + lane;
     const long long grow = ep.row0 + rloc;
     const bool live = grow < (long long)ep.B;
@@ -278,44 +310,48 @@ __device__ __forceinline__ void tc_epilogue_bwd(const TcEpi& ep, TcSmemCtl* ctl,
     const float wgt = dt * c_A[6][ep.stage];
     if (ep.kind == TCB_FWD_LAST) {
         float s0 = 0.0f;
-        for (int ch = sub; ch < nchunk; ch += 4) {
+        for (int ch = sub; ch < nchunk; ch += TC_NSUB) {
             const int c0 = ch * TC_CW;
+            if (c0 >= ep.D) break;
+            TcAux nxt;
+            if (ch + TC_NSUB < nchunk && c0 + TC_NSUB * TC_CW < ep.D)
+                tc_aux_load<1, true>(ep, rloc, grow, c0 + TC_NSUB * TC_CW, nxt);
             uint32_t v[TC_CW];
             tc::tmem_ld_32x16(tbase + c0, v);
             tc::tmem_ld_wait();
             float y[TC_CW], g[TC_CW];
 #pragma unroll
             for (int j = 0; j < TC_CW; ++j) {
-                const int n = c0 + j;
                 y[j] = 0.0f; g[j] = 0.0f;
-                if (n < ep.D) {
-                    y[j] = tc_tanh(__uint_as_float(v[j]) + __ldg(ep.bias + n));
+                if (c0 + j < ep.D) {
+                    y[j] = tc_tanh(__uint_as_float(v[j]) + __ldg(ep.bias + c0 + j));
                     s0 = fmaf(y[j], y[j], s0);
-                    g[j] = ep.eps[(long long)n * ep.Bs + grow] * fmaf(-y[j], y[j], 1.0f);
+                    g[j] = cur.f[j] * fmaf(-y[j], y[j], 1.0f);
                 }
             }
             tc_store_f32x16(ep.f32a + rloc * ep.ld_f + c0, y);
             tc_store_planes16<1>(g, ep.out, rloc * ep.ld_out + c0);
+            cur = nxt;
         }
         const float2 r = tc_quad_reduce(ctl, quad, sub, lane, par, s0, 0.0f);
         const float inv = (live && (ep.flags & CNF_FLAG_NORM_Z) && r.x > 0.0f) ? wgt * ep.c_E / sqrtf(r.x) : 0.0f;
-        for (int ch = sub; ch < nchunk; ch += 4) {
+        for (int ch = sub; ch < nchunk; ch += TC_NSUB) {
             const int c0 = ch * TC_CW;
-            float y[TC_CW], yb[TC_CW];
+            if (c0 >= ep.D) break;
+            float y[TC_CW], yb[TC_CW], ab[TC_CW];
+            tc_load_soa16(ep.abar, ep.Bs, grow, c0, ep.D, ab);
             tc_load_f32x16(ep.f32a + rloc * ep.ld_f + c0, y);
 #pragma unroll
-            for (int j = 0; j < TC_CW; ++j) {
-                const int n = c0 + j;
-                yb[j] = (live && n < ep.D) ? fmaf(inv, y[j], ep.abar[(long long)n * ep.Bs + grow]) : 0.0f;
-            }
+            for (int j = 0; j < TC_CW; ++j) yb[j] = (live && c0 + j < ep.D) ? fmaf(inv, y[j], ab[j]) : 0.0f;
             tc_store_f32x16(ep.f32b + rloc * ep.ld_f + c0, yb);
         }
         return;
     }
     if (ep.kind == TCB_BWD_LAST) {
         float s1 = 0.0f;
-        for (int ch = sub; ch < nchunk; ch += 4) {
+        for (int ch = sub; ch < nchunk; ch += TC_NSUB) {
             const int c0 = ch * TC_CW;
+            if (c0 >= ep.D) break;
             uint32_t v[TC_CW];
             tc::tmem_ld_32x16(tbase + c0, v);
             tc::tmem_ld_wait();
@@ -326,60 +362,54 @@ __device__ __forceinline__ void tc_epilogue_bwd(const TcEpi& ep, TcSmemCtl* ctl,
         const float2 r = tc_quad_reduce(ctl, quad, sub, lane, par, s1, 0.0f);
         const float inv = (live && (ep.flags & CNF_FLAG_NORM_J) && r.x > 0.0f) ? wgt * ep.c_n / sqrtf(r.x) : 0.0f;
         const float al = live ? wgt * ep.c_l : 0.0f;
-        for (int ch = sub; ch < nchunk; ch += 4) {
+        for (int ch = sub; ch < nchunk; ch += TC_NSUB) {
             const int c0 = ch * TC_CW;
+            if (c0 >= ep.D) break;
             uint32_t v[TC_CW];
+            float x[TC_CW], e[TC_CW];
+            tc_load_soa16(ep.eps, ep.Bs, grow, c0, ep.D, e);
             tc::tmem_ld_32x16(tbase + c0, v);
             tc::tmem_ld_wait();
-            float x[TC_CW];
 #pragma unroll
-            for (int j = 0; j < TC_CW; ++j) {
-                const int n = c0 + j;
-                x[j] = (n < ep.D) ? fmaf(inv, __uint_as_float(v[j]), -al * ep.eps[(long long)n * ep.Bs + grow]) : 0.0f;
-            }
+            for (int j = 0; j < TC_CW; ++j) x[j] = (c0 + j < ep.D) ? fmaf(inv, __uint_as_float(v[j]), -al * e[j]) : 0.0f;
             tc_store_planes16<1>(x, ep.out, rloc * ep.ld_out + c0);
         }
         return;
     }
     // column-wise kinds
-    for (int ch = sub; ch < nchunk; ch += 4) {
+    for (int ch = sub; ch < nchunk; ch += TC_NSUB) {
         const int c0 = ch * TC_CW, ng = nb * BN + c0;
+        if (ng >= ep.N) break;
+        TcAux nxt;
+        if (ch + TC_NSUB < nchunk && ng + TC_NSUB * TC_CW < ep.N)
+            tc_aux_load<1, true>(ep, rloc, grow, ng + TC_NSUB * TC_CW, nxt);
+        float y[TC_CW], yb[TC_CW];
+        if (ep.kind == TCB_GBAR_LAST) {
+            tc_load_f32x16(ep.f32a + rloc * ep.ld_f + ng, y);
+            tc_load_f32x16(ep.f32b + rloc * ep.ld_f + ng, yb);
+        }
         uint32_t v[TC_CW];
         tc::tmem_ld_32x16(tbase + c0, v);
         tc::tmem_ld_wait();
-        if (ng >= ep.N) continue;
         float x[TC_CW];
-        if (ep.kind == TCB_ZBAR) {
+        if (ep.kind == TCB_ZBAR) {   // zbar goes to an SoA scratch; k_zbar_apply streams it into ubar / kbar_j
 #pragma unroll
-            for (int j = 0; j < TC_CW; ++j) {
-                const int n = ng + j;
-                if (n < ep.D) {
-                    const float zb = __uint_as_float(v[j]);
-                    const long long at = (long long)n * ep.Bs + grow;
-                    ep.ubar[at] += zb;
-#pragma unroll
-                    for (int s = 0; s < 5; ++s)
-                        if (s < ep.stage) ep.kb[s][at] = fmaf(dt * c_A[ep.stage][s], zb, ep.kb[s][at]);
-                }
-            }
+            for (int j = 0; j < TC_CW; ++j)
+                if (ng + j < ep.D) ep.ubar[(long long)(ng + j) * ep.Bs + grow] = __uint_as_float(v[j]);
             continue;
         }
         if (ep.kind == TCB_GBAR_LAST) {
-            float y[TC_CW], yb[TC_CW];
-            tc_load_f32x16(ep.f32a + rloc * ep.ld_f + ng, y);
-            tc_load_f32x16(ep.f32b + rloc * ep.ld_f + ng, yb);
 #pragma unroll
             for (int j = 0; j < TC_CW; ++j) {
-                const int n = ng + j;
                 x[j] = 0.0f;
-                if (n < ep.D) {
-                    const float db = __uint_as_float(v[j]) * ep.eps[(long long)n * ep.Bs + grow];
+                if (ng + j < ep.D) {
+                    const float db = __uint_as_float(v[j]) * cur.f[j];
                     x[j] = fmaf(-2.0f * y[j], db, yb[j]) * fmaf(-y[j], y[j], 1.0f);
                 }
             }
         } else {
             float h[TC_CW];
-            tc_load_planes16<1>(ep.hp, rloc * ep.ld_h + ng, h);
+            tc_unpack_planes16<1>(cur.p, h);
             if (ep.kind == TCB_BWD_HIDDEN) {
                 float q[TC_CW];
 #pragma unroll
@@ -390,23 +420,21 @@ __device__ __forceinline__ void tc_epilogue_bwd(const TcEpi& ep, TcSmemCtl* ctl,
                 tc_store_f32x16(ep.f32a + rloc * ep.ld_f + ng, q);
             } else if (ep.kind == TCB_GBAR_HIDDEN) {
                 float q[TC_CW];
-                tc_load_f32x16(ep.f32a + rloc * ep.ld_f + ng, q);
 #pragma unroll
                 for (int j = 0; j < TC_CW; ++j) {
                     const float gb = __uint_as_float(v[j]);
-                    q[j] *= gb;                                // dbar_l
+                    q[j] = cur.f[j] * gb;                      // dbar_l
                     x[j] = gb * fmaf(-h[j], h[j], 1.0f);      // qbar_{l+1}
                 }
                 tc_store_f32x16(ep.f32a + rloc * ep.ld_f + ng, q);
             } else {   // TCB_HBAR_HIDDEN
-                float db[TC_CW];
-                tc_load_f32x16(ep.f32a + rloc * ep.ld_f + ng, db);
 #pragma unroll
                 for (int j = 0; j < TC_CW; ++j)
-                    x[j] = fmaf(-2.0f * h[j], db[j], __uint_as_float(v[j])) * fmaf(-h[j], h[j], 1.0f);
+                    x[j] = fmaf(-2.0f * h[j], cur.f[j], __uint_as_float(v[j])) * fmaf(-h[j], h[j], 1.0f);
             }
         }
         tc_store_planes16<1>(x, ep.out, rloc * ep.ld_out + ng);
+        cur = nxt;
     }
 }
 
@@ -429,7 +457,7 @@ k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, i
     if (warp == 0 && lane == 0) {
         for (int q = 0; q < 2; ++q) { tc::tma_prefetch_desc(&mp.a[q]); tc::tma_prefetch_desc(&mp.b[q]); }
         for (int s = 0; s < nstage; ++s) { tc::mbar_init(&ctl->full[s], 1); tc::mbar_init(&ctl->empty[s], 1); }
-        for (int a = 0; a < 2; ++a) { tc::mbar_init(&ctl->tfull[a], 1); tc::mbar_init(&ctl->tempty[a], 16); }
+        for (int a = 0; a < 2; ++a) { tc::mbar_init(&ctl->tfull[a], 1); tc::mbar_init(&ctl->tempty[a], 4 * TC_NSUB); }
         tc::fence_barrier_init();
     }
     if (warp == 1) tc::tmem_alloc(&ctl->tmem_base, 512);
@@ -488,16 +516,22 @@ k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, i
         }
     } else {               // ===== epilogue warps
         const int quad = warp & 3;                    // TMEM lane quadrant this warp may access
-        const int sub = (warp - TC_EPI_WARP0) >> 2;   // 0..3: which chunks of the quadrant's columns
+        const int sub = (warp - TC_EPI_WARP0) >> 2;   // 0..2: which chunks of the quadrant's columns
         int it = 0;
         for (int t = blockIdx.x; t < total; t += gridDim.x, ++it) {
             const int mb = t / n_tiles, nb = t % n_tiles;
             const int acc = it & 1;
+            TcAux aux;   // global operands of this warp's first chunk: in flight while the MMAs finish
+            {
+                const long long rloc = (long long)mb * TC_BM + quad * 32 + lane;
+                const int ng0 = nb * BN + sub * TC_CW;
+                if (sub * TC_CW < BN && ng0 < ep.N) tc_aux_load<PREC, BWD>(ep, rloc, ep.row0 + rloc, ng0, aux);
+            }
             tc::mbar_wait(&ctl->tfull[acc], (it >> 1) & 1);
             tc::tc_fence_after();
             const uint32_t tbase = tmem + ((uint32_t)(quad * 32) << 16) + (uint32_t)acc * 256;
-            if (BWD) tc_epilogue_bwd(ep, ctl, tbase, mb, nb, BN, quad, sub, lane, it & 1);
-            else tc_epilogue_fwd<PREC>(ep, ctl, tbase, mb, nb, BN, quad, sub, lane, it & 1);
+            if (BWD) tc_epilogue_bwd(ep, ctl, tbase, mb, nb, BN, quad, sub, lane, it & 1, aux);
+            else tc_epilogue_fwd<PREC>(ep, ctl, tbase, mb, nb, BN, quad, sub, lane, it & 1, aux);
             tc::tc_fence_before();
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(&ctl->tempty[acc]);
