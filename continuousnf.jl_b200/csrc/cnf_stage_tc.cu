@@ -188,9 +188,9 @@ __device__ __forceinline__ void tc_load_soa16(const float* __restrict__ base, lo
 }
 
 // what chunk (nb, ch) of this thread's row needs besides the accumulator, by kind
-template <int PREC, bool BWD>
+template <int PREC, bool BWD, int KIND>
 __device__ __forceinline__ void tc_aux_load(const TcEpi& ep, long long rloc, long long grow, int ng, TcAux& a) {
-    const int k = ep.kind;
+    constexpr int k = KIND;
     if (!BWD) {
         if (k == TC_FWD_HIDDEN) {
             const float* b = ep.bias + ng;
@@ -231,12 +231,12 @@ __device__ __forceinline__ float2 tc_quad_reduce(TcSmemCtl* ctl, int quad, int s
 }
 
 // ---- forward-solve epilogue of one 128 x BN tile (kinds TC_*); cur = aux of this warp's first chunk
-template <int PREC>
+template <int PREC, int KIND>
 __device__ __forceinline__ void tc_epilogue_fwd(const TcEpi& ep, TcSmemCtl* ctl, uint32_t tbase, int mb, int nb, int BN,
                                                 int quad, int sub, int lane, int par, TcAux& cur) {
     const long long rloc = (long long)mb * TC_BM + quad * 32 + lane;   // row inside the chunk
     const long long grow = ep.row0 + rloc;                               // global sample
-    const bool last_kind = (ep.kind == TC_FWD_LAST || ep.kind == TC_BWD_LAST || ep.kind == TC_JVP_LAST);
+    constexpr bool last_kind = (KIND == TC_FWD_LAST || KIND == TC_BWD_LAST || KIND == TC_JVP_LAST);
     const int nchunk = (BN + TC_CW - 1) / TC_CW;
     const int nmax = last_kind ? ep.D : ep.N;
     float s0 = 0.0f, s1 = 0.0f;
@@ -245,22 +245,22 @@ __device__ __forceinline__ void tc_epilogue_fwd(const TcEpi& ep, TcSmemCtl* ctl,
         if (ng >= nmax) break;
         TcAux nxt;
         if (ch + TC_NSUB < nchunk && ng + TC_NSUB * TC_CW < nmax)
-            tc_aux_load<PREC, false>(ep, rloc, grow, ng + TC_NSUB * TC_CW, nxt);
+            tc_aux_load<PREC, false, KIND>(ep, rloc, grow, ng + TC_NSUB * TC_CW, nxt);
         uint32_t v[TC_CW];
         tc::tmem_ld_32x16(tbase + c0, v);
         tc::tmem_ld_wait();
         float x[TC_CW];
-        if (ep.kind == TC_FWD_HIDDEN) {
+        if (KIND == TC_FWD_HIDDEN) {
 #pragma unroll
             for (int j = 0; j < TC_CW; ++j) x[j] = tc_tanh(__uint_as_float(v[j]) + cur.f[j]);
             tc_store_planes16<PREC>(x, ep.out, rloc * ep.ld_out + ng);
-        } else if (ep.kind == TC_BWD_HIDDEN) {   // acc .* (1 - h^2)
+        } else if (KIND == TC_BWD_HIDDEN) {   // acc .* (1 - h^2)
             float h[TC_CW];
             tc_unpack_planes16<PREC>(cur.p, h);
 #pragma unroll
             for (int j = 0; j < TC_CW; ++j) x[j] = __uint_as_float(v[j]) * fmaf(-h[j], h[j], 1.0f);
             tc_store_planes16<PREC>(x, ep.out, rloc * ep.ld_out + ng);
-        } else if (ep.kind == TC_FWD_LAST) {
+        } else if (KIND == TC_FWD_LAST) {
 #pragma unroll
             for (int j = 0; j < TC_CW; ++j) {
                 x[j] = 0.0f;
@@ -274,12 +274,12 @@ __device__ __forceinline__ void tc_epilogue_fwd(const TcEpi& ep, TcSmemCtl* ctl,
             if (ep.vjp == 1) tc_store_planes16<PREC>(x, ep.out, rloc * ep.ld_out + c0);
         } else {   // TC_BWD_LAST / TC_JVP_LAST: -eps . v and |v|^2
             float y[TC_CW];
-            if (ep.kind == TC_JVP_LAST) tc_load_soa16(ep.kout, ep.Bs, grow, c0, ep.D, y);
+            if (KIND == TC_JVP_LAST) tc_load_soa16(ep.kout, ep.Bs, grow, c0, ep.D, y);
 #pragma unroll
             for (int j = 0; j < TC_CW; ++j) {
                 if (c0 + j < ep.D) {
                     float vv = __uint_as_float(v[j]);
-                    if (ep.kind == TC_JVP_LAST) vv *= fmaf(-y[j], y[j], 1.0f);
+                    if (KIND == TC_JVP_LAST) vv *= fmaf(-y[j], y[j], 1.0f);
                     s0 = fmaf(-vv, cur.f[j], s0);
                     s1 = fmaf(vv, vv, s1);
                 }
@@ -287,11 +287,11 @@ __device__ __forceinline__ void tc_epilogue_fwd(const TcEpi& ep, TcSmemCtl* ctl,
         }
         cur = nxt;
     }
-    if (!last_kind || (ep.kind == TC_FWD_LAST && ep.vjp == 2)) return;   // (vjp 2: zdot rows only)
+    if (!last_kind || (KIND == TC_FWD_LAST && ep.vjp == 2)) return;   // (vjp 2: zdot rows only)
     // per-sample reductions over all D columns: partial sums per warp, combined per quadrant
     const float2 r = tc_quad_reduce(ctl, quad, sub, lane, par, s0, s1);
     if (sub != 0) return;
-    if (ep.kind == TC_FWD_LAST) {
+    if (KIND == TC_FWD_LAST) {
         ep.kout[(long long)(ep.D + 1) * ep.Bs + grow] = (ep.flags & CNF_FLAG_NORM_Z) ? sqrtf(r.x) : 0.0f;
     } else {
         ep.kout[(long long)ep.D * ep.Bs + grow] = r.x;
@@ -300,6 +300,7 @@ __device__ __forceinline__ void tc_epilogue_fwd(const TcEpi& ep, TcSmemCtl* ctl,
 }
 
 // ---- reverse-sweep epilogue of one 128 x BN tile (kinds TCB_*, bfloat16 planes)
+template <int KIND>
 __device__ __forceinline__ void tc_epilogue_bwd(const TcEpi& ep, TcSmemCtl* ctl, uint32_t tbase, int mb, int nb, int BN,
                                                 int quad, int sub, int lane, int par, TcAux& cur) {
     const long long rloc = (long long)mb * TC_BM + quad * 32 + lane;
@@ -308,14 +309,14 @@ __device__ __forceinline__ void tc_epilogue_bwd(const TcEpi& ep, TcSmemCtl* ctl,
     const int nchunk = (BN + TC_CW - 1) / TC_CW;
     const float dt = *ep.dtp;
     const float wgt = dt * c_A[6][ep.stage];
-    if (ep.kind == TCB_FWD_LAST) {
+    if (KIND == TCB_FWD_LAST) {
         float s0 = 0.0f;
         for (int ch = sub; ch < nchunk; ch += TC_NSUB) {
             const int c0 = ch * TC_CW;
             if (c0 >= ep.D) break;
             TcAux nxt;
             if (ch + TC_NSUB < nchunk && c0 + TC_NSUB * TC_CW < ep.D)
-                tc_aux_load<1, true>(ep, rloc, grow, c0 + TC_NSUB * TC_CW, nxt);
+                tc_aux_load<1, true, KIND>(ep, rloc, grow, c0 + TC_NSUB * TC_CW, nxt);
             uint32_t v[TC_CW];
             tc::tmem_ld_32x16(tbase + c0, v);
             tc::tmem_ld_wait();
@@ -347,7 +348,7 @@ __device__ __forceinline__ void tc_epilogue_bwd(const TcEpi& ep, TcSmemCtl* ctl,
         }
         return;
     }
-    if (ep.kind == TCB_BWD_LAST) {
+    if (KIND == TCB_BWD_LAST) {
         float s1 = 0.0f;
         for (int ch = sub; ch < nchunk; ch += TC_NSUB) {
             const int c0 = ch * TC_CW;
@@ -382,9 +383,9 @@ __device__ __forceinline__ void tc_epilogue_bwd(const TcEpi& ep, TcSmemCtl* ctl,
         if (ng >= ep.N) break;
         TcAux nxt;
         if (ch + TC_NSUB < nchunk && ng + TC_NSUB * TC_CW < ep.N)
-            tc_aux_load<1, true>(ep, rloc, grow, ng + TC_NSUB * TC_CW, nxt);
+            tc_aux_load<1, true, KIND>(ep, rloc, grow, ng + TC_NSUB * TC_CW, nxt);
         float y[TC_CW], yb[TC_CW];
-        if (ep.kind == TCB_GBAR_LAST) {
+        if (KIND == TCB_GBAR_LAST) {
             tc_load_f32x16(ep.f32a + rloc * ep.ld_f + ng, y);
             tc_load_f32x16(ep.f32b + rloc * ep.ld_f + ng, yb);
         }
@@ -392,13 +393,13 @@ __device__ __forceinline__ void tc_epilogue_bwd(const TcEpi& ep, TcSmemCtl* ctl,
         tc::tmem_ld_32x16(tbase + c0, v);
         tc::tmem_ld_wait();
         float x[TC_CW];
-        if (ep.kind == TCB_ZBAR) {   // zbar goes to an SoA scratch; k_zbar_apply streams it into ubar / kbar_j
+        if (KIND == TCB_ZBAR) {   // zbar goes to an SoA scratch; k_zbar_apply streams it into ubar / kbar_j
 #pragma unroll
             for (int j = 0; j < TC_CW; ++j)
                 if (ng + j < ep.D) ep.ubar[(long long)(ng + j) * ep.Bs + grow] = __uint_as_float(v[j]);
             continue;
         }
-        if (ep.kind == TCB_GBAR_LAST) {
+        if (KIND == TCB_GBAR_LAST) {
 #pragma unroll
             for (int j = 0; j < TC_CW; ++j) {
                 x[j] = 0.0f;
@@ -410,7 +411,7 @@ __device__ __forceinline__ void tc_epilogue_bwd(const TcEpi& ep, TcSmemCtl* ctl,
         } else {
             float h[TC_CW];
             tc_unpack_planes16<1>(cur.p, h);
-            if (ep.kind == TCB_BWD_HIDDEN) {
+            if (KIND == TCB_BWD_HIDDEN) {
                 float q[TC_CW];
 #pragma unroll
                 for (int j = 0; j < TC_CW; ++j) {
@@ -418,7 +419,7 @@ __device__ __forceinline__ void tc_epilogue_bwd(const TcEpi& ep, TcSmemCtl* ctl,
                     x[j] = q[j] * fmaf(-h[j], h[j], 1.0f);
                 }
                 tc_store_f32x16(ep.f32a + rloc * ep.ld_f + ng, q);
-            } else if (ep.kind == TCB_GBAR_HIDDEN) {
+            } else if (KIND == TCB_GBAR_HIDDEN) {
                 float q[TC_CW];
 #pragma unroll
                 for (int j = 0; j < TC_CW; ++j) {
@@ -440,7 +441,7 @@ __device__ __forceinline__ void tc_epilogue_bwd(const TcEpi& ep, TcSmemCtl* ctl,
 
 // BM x BN output tile per (m_blk, n_blk); K in blocks of 64 bf16; persistent over tiles.
 // PREC = operand format of the two hi/lo planes (0: IEEE half, forward solve; 1: bfloat16, reverse sweep).
-template <int PREC, bool BWD>
+template <int PREC, bool BWD, int KIND>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, int nk, int nstage, TcEpi ep) {
     if (ep.ctrl && ep.ctrl->done) return;
@@ -525,13 +526,13 @@ k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, i
             {
                 const long long rloc = (long long)mb * TC_BM + quad * 32 + lane;
                 const int ng0 = nb * BN + sub * TC_CW;
-                if (sub * TC_CW < BN && ng0 < ep.N) tc_aux_load<PREC, BWD>(ep, rloc, ep.row0 + rloc, ng0, aux);
+                if (sub * TC_CW < BN && ng0 < ep.N) tc_aux_load<PREC, BWD, KIND>(ep, rloc, ep.row0 + rloc, ng0, aux);
             }
             tc::mbar_wait(&ctl->tfull[acc], (it >> 1) & 1);
             tc::tc_fence_after();
             const uint32_t tbase = tmem + ((uint32_t)(quad * 32) << 16) + (uint32_t)acc * 256;
-            if (BWD) tc_epilogue_bwd(ep, ctl, tbase, mb, nb, BN, quad, sub, lane, it & 1, aux);
-            else tc_epilogue_fwd<PREC>(ep, ctl, tbase, mb, nb, BN, quad, sub, lane, it & 1, aux);
+            if (BWD) tc_epilogue_bwd<KIND>(ep, ctl, tbase, mb, nb, BN, quad, sub, lane, it & 1, aux);
+            else tc_epilogue_fwd<PREC, KIND>(ep, ctl, tbase, mb, nb, BN, quad, sub, lane, it & 1, aux);
             tc::tc_fence_before();
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(&ctl->tempty[acc]);
@@ -747,9 +748,6 @@ int tc_set_params(cnf_handle* h) {
         cudaDeviceProp prop;
         if (cudaGetDeviceProperties(&prop, h->device) == cudaSuccess) s->sms = prop.multiProcessorCount;
         CNF_CUDA(cudaMalloc(&s->dyn, sizeof(TcDyn)));
-        CNF_CUDA(cudaFuncSetAttribute(k_tc_gemm<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        CNF_CUDA(cudaFuncSetAttribute(k_tc_gemm<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        CNF_CUDA(cudaFuncSetAttribute(k_tc_gemm<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     }
     TcState* s = (TcState*)h->tc_state;
     s->L = c.n_layers;
@@ -796,6 +794,21 @@ static int tc_ensure_acts(cnf_handle* h, TcState* s, long long Bs) {
     return CNF_OK;
 }
 
+// one kernel instantiation per (format, epilogue kind): each carries only its own epilogue path
+template <int PREC, bool BWD, int KIND>
+static void tc_launch_kind(cnf_handle* h, int grid, int smem, const TcMaps& mp, int m_tiles, int n_tiles, int BN, int nk,
+                           int nstage, const TcEpi& ep) {
+    constexpr bool valid = BWD ? (KIND >= TCB_FWD_LAST && PREC == 1) : (KIND <= TC_JVP_LAST && (PREC == 0 || KIND == TC_FWD_HIDDEN));
+    if constexpr (valid) {
+        static bool attr = false;
+        if (!attr) {
+            cudaFuncSetAttribute(k_tc_gemm<PREC, BWD, KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+            attr = true;
+        }
+        k_tc_gemm<PREC, BWD, KIND><<<grid, TC_THREADS, smem, h->stream>>>(mp, m_tiles, n_tiles, BN, nk, nstage, ep);
+    }
+}
+
 template <int PREC, bool BWD>
 static void tc_launch_gemm(cnf_handle* h, TcState* s, const TcPlane& A, const TcWeight& B, int mc, const TcEpi& ep) {
     const int BN = B.BN, n_tiles = B.n_tiles;
@@ -811,7 +824,14 @@ static void tc_launch_gemm(cnf_handle* h, TcState* s, const TcPlane& A, const Tc
     const TcPlane& Bp = PREC == 0 ? B.ph : B.pb;
     TcMaps mp;
     for (int q = 0; q < 2; ++q) { mp.a[q] = A.map[q]; mp.b[q] = Bp.map[q]; }
-    k_tc_gemm<PREC, BWD><<<grid, TC_THREADS, smem, h->stream>>>(mp, m_tiles, n_tiles, BN, nk, nstage, ep);
+    switch (ep.kind) {
+#define TC_CASE(K) case K: tc_launch_kind<PREC, BWD, K>(h, grid, smem, mp, m_tiles, n_tiles, BN, nk, nstage, ep); break;
+        TC_CASE(TC_FWD_HIDDEN) TC_CASE(TC_FWD_LAST) TC_CASE(TC_BWD_HIDDEN) TC_CASE(TC_BWD_LAST) TC_CASE(TC_JVP_LAST)
+        TC_CASE(TCB_FWD_LAST) TC_CASE(TCB_BWD_HIDDEN) TC_CASE(TCB_BWD_LAST) TC_CASE(TCB_GBAR_HIDDEN)
+        TC_CASE(TCB_GBAR_LAST) TC_CASE(TCB_HBAR_HIDDEN) TC_CASE(TCB_ZBAR)
+#undef TC_CASE
+        default: break;
+    }
     h->launches++;
 }
 
