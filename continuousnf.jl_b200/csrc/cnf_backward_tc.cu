@@ -279,6 +279,7 @@ int tc_vjp_stage(cnf_handle* h, const CnfBufs& bf, const float* src, const float
             if (l > 1) {
                 ep.kind = TCB_BWD_HIDDEN;
                 ep.N = c.dims[l - 1];
+                ep.aux_p = &s->H[l - 1];
                 for (int q = 0; q < 2; ++q) { ep.hp[q] = s->H[l - 1].p[q]; ep.out[q] = s->G[l - 1].p[q]; }
                 ep.ld_h = s->H[l - 1].ld; ep.ld_out = s->G[l - 1].ld;
                 ep.f32a = s->Q[l - 1].p; ep.ld_f = s->Q[l - 1].ld;
@@ -295,6 +296,7 @@ int tc_vjp_stage(cnf_handle* h, const CnfBufs& bf, const float* src, const float
             if (l < L) {
                 ep.kind = TCB_GBAR_HIDDEN;
                 ep.N = c.dims[l];
+                ep.aux_p = &s->H[l]; ep.aux_f = &s->Q[l];
                 for (int q = 0; q < 2; ++q) { ep.hp[q] = s->H[l].p[q]; ep.out[q] = s->QB[l + 1].p[q]; }
                 ep.ld_h = s->H[l].ld; ep.ld_out = s->QB[l + 1].ld;
                 ep.f32a = s->Q[l].p; ep.ld_f = s->Q[l].ld;
@@ -314,6 +316,7 @@ int tc_vjp_stage(cnf_handle* h, const CnfBufs& bf, const float* src, const float
             if (l > 1) {
                 ep.kind = TCB_HBAR_HIDDEN;
                 ep.N = c.dims[l - 1];
+                ep.aux_p = &s->H[l - 1]; ep.aux_f = &s->Q[l - 1];
                 for (int q = 0; q < 2; ++q) { ep.hp[q] = s->H[l - 1].p[q]; ep.out[q] = s->PB[l - 1].p[q]; }
                 ep.ld_h = s->H[l - 1].ld; ep.ld_out = s->PB[l - 1].ld;
                 ep.f32a = s->Q[l - 1].p; ep.ld_f = s->Q[l - 1].ld;

@@ -68,6 +68,9 @@ struct TcEpi {
     int stage;                     // 0..5
     float c_l, c_E, c_n;           // cotangents of the quadrature rows (1/B, lambda1/B, lambda2/B)
     int B;                         // live samples (rows >= B are padding)
+    // ---- host only: whose tiles the TMA producer prefetches into L2 for the epilogue (TcPlane*, TcF32*)
+    const void* aux_p;
+    const void* aux_f;
 };
 
 // two floats -> packed (hi, hi) and (lo, lo) 16-bit pairs; element a in the low half-word
@@ -93,7 +96,11 @@ __device__ __forceinline__ float2 tc_unpack2(uint32_t w) {
     return make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u));
 }
 
-struct TcMaps { CUtensorMap a[2], b[2]; };   // A planes, B planes
+struct TcMaps {
+    CUtensorMap a[2], b[2];   // A planes, B planes
+    CUtensorMap x[3];         // epilogue operands prefetched into L2: hi / lo plane (64-column boxes), fp32 array (32-column boxes)
+    int nxp, nxf;             // 0/1: planes present, fp32 array present
+};
 
 struct TcSmemCtl {
     uint64_t full[8], empty[8], tfull[2], tempty[2];
@@ -482,6 +489,14 @@ k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, i
                     }
                     if (++stage == nstage) { stage = 0; phase ^= 1; }
                 }
+                // what the epilogue of this tile reads from global memory: on its way to L2 while the MMAs run
+                if (mp.nxp)
+                    for (int c = 0; c < BN && nb * BN + c < ep.N; c += 64) {
+                        tc::tma_prefetch_2d(&mp.x[0], nb * BN + c, mb * TC_BM);
+                        tc::tma_prefetch_2d(&mp.x[1], nb * BN + c, mb * TC_BM);
+                    }
+                if (mp.nxf)
+                    for (int c = 0; c < BN && nb * BN + c < ep.N; c += 32) tc::tma_prefetch_2d(&mp.x[2], nb * BN + c, mb * TC_BM);
             }
         }
     } else if (warp == 1) {
@@ -633,6 +648,18 @@ static bool tc_make_map(CUtensorMap* m, const void* base, long long rows, long l
               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+static bool tc_make_map_f32(CUtensorMap* m, const void* base, long long rows, long long ld) {
+    PFN_encodeTiled fn = tc_encode_fn();
+    if (!fn) return false;
+    cuuint64_t dims[2] = {(cuuint64_t)ld, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
+    cuuint32_t box[2] = {32, TC_BM};
+    cuuint32_t estr[2] = {1, 1};
+    return fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims, strides, box, estr,
+              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 static inline int pad_to(int x, int m) { return (x + m - 1) / m * m; }
 
 struct TcPlane {
@@ -648,6 +675,7 @@ struct TcWeight {
 struct TcF32 {
     float* p = nullptr;
     int rows = 0, ld = 0;
+    CUtensorMap map;   // box [128 rows x 32 cols], no swizzle: L2 prefetch only
 };
 struct TcState {
     int L = 0, Mc = 0;
@@ -688,6 +716,7 @@ static int tc_alloc_f32(cnf_handle* h, TcF32& f, int rows, int ld) {
     f.rows = rows; f.ld = ld;
     CNF_CUDA(cudaMalloc(&f.p, (size_t)rows * ld * sizeof(float)));
     CNF_CUDA(cudaMemsetAsync(f.p, 0, (size_t)rows * ld * sizeof(float), h->stream));
+    if (!tc_make_map_f32(&f.map, f.p, rows, ld)) { h->err = "cuTensorMapEncodeTiled failed"; return CNF_ERR_CUDA; }
     return CNF_OK;
 }
 
@@ -824,6 +853,16 @@ static void tc_launch_gemm(cnf_handle* h, TcState* s, const TcPlane& A, const Tc
     const TcPlane& Bp = PREC == 0 ? B.ph : B.pb;
     TcMaps mp;
     for (int q = 0; q < 2; ++q) { mp.a[q] = A.map[q]; mp.b[q] = Bp.map[q]; }
+    mp.nxp = mp.nxf = 0;
+    if (ep.aux_p && !h->tc_noprefetch) {
+        const TcPlane* xp = (const TcPlane*)ep.aux_p;
+        mp.x[0] = xp->map[0]; mp.x[1] = xp->map[1];
+        mp.nxp = 1;
+    }
+    if (ep.aux_f && !h->tc_noprefetch) {
+        mp.x[2] = ((const TcF32*)ep.aux_f)->map;
+        mp.nxf = 1;
+    }
     switch (ep.kind) {
 #define TC_CASE(K) case K: tc_launch_kind<PREC, BWD, K>(h, grid, smem, mp, m_tiles, n_tiles, BN, nk, nstage, ep); break;
         TC_CASE(TC_FWD_HIDDEN) TC_CASE(TC_FWD_LAST) TC_CASE(TC_BWD_HIDDEN) TC_CASE(TC_BWD_LAST) TC_CASE(TC_JVP_LAST)
@@ -896,6 +935,7 @@ int tc_eval(cnf_handle* h, const CnfBufs& bf, const float* src, int kidx, float*
                     ep.kind = TC_BWD_HIDDEN;
                     ep.N = c.dims[l];
                     for (int q = 0; q < 2; ++q) { ep.hp[q] = s->H[l].p[q]; ep.out[q] = s->G[l].p[q]; }
+                    ep.aux_p = &s->H[l];
                     ep.ld_h = s->H[l].ld; ep.ld_out = s->G[l].ld;
                 } else {
                     ep.kind = TC_BWD_LAST;
@@ -916,6 +956,7 @@ int tc_eval(cnf_handle* h, const CnfBufs& bf, const float* src, int kidx, float*
                 if (l < L - 1) {
                     ep.kind = TC_BWD_HIDDEN;
                     for (int q = 0; q < 2; ++q) { ep.hp[q] = s->H[l + 1].p[q]; ep.out[q] = s->G[l + 1].p[q]; }
+                    ep.aux_p = &s->H[l + 1];
                     ep.ld_h = s->H[l + 1].ld; ep.ld_out = s->G[l + 1].ld;
                 } else {
                     ep.kind = TC_JVP_LAST;
