@@ -61,9 +61,11 @@ def test_logdensity(cid, B, trace_mode, mode):
         assert relerr(lp, rlp) < 5e-3
 
 
-@pytest.mark.parametrize("cid,B", [("C0", 64), ("C1", 1024), ("C3", 256), ("C4", 1024)])
+@pytest.mark.parametrize("cid,B", [("C0", 64), ("C1", 1024), ("C3", 256), ("C4", 1024), ("C5", 64)])
 @pytest.mark.parametrize("trace_mode", [0, 1])
 def test_loss_grad(cid, B, trace_mode):
+    if cid == "C5" and trace_mode == 1:
+        pytest.skip("JacVec training at width 1024: the tensor reverse sweep covers VecJac; the generic one does not fit")
     inp = wl.make_inputs(cid, B=B)
     c = wl.CONFIGS[cid]
     icnf = make_icnf(cid, trace_mode=trace_mode)
