@@ -16,7 +16,7 @@ RETCODES = {0: "Success", 1: "MaxIters", 2: "DtLessThanMin", 3: "Unstable"}
 EXPORTS = [
     "cnfb200_version", "cnfb200_create", "cnfb200_destroy", "cnfb200_set_option", "cnfb200_last_error",
     "cnfb200_set_params", "cnfb200_comm_unique_id", "cnfb200_comm_init", "cnfb200_augmented_f",
-    "cnfb200_logdensity", "cnfb200_loss_grad", "cnfb200_generate", "cnfb200_measure_fp32_peak",
+    "cnfb200_logdensity", "cnfb200_loss_grad", "cnfb200_loss_grad_mode", "cnfb200_generate", "cnfb200_measure_fp32_peak",
 ]
 
 
@@ -77,6 +77,9 @@ def load():
                                        C.c_int64, C.c_float, C.c_float, C.c_void_p, C.c_void_p,
                                        C.c_void_p, C.POINTER(CnfStats)]
     lib.cnfb200_loss_grad.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                                      C.c_float, C.c_float, _FP, C.c_void_p, C.c_void_p,
+                                      C.POINTER(CnfStats)]
+    lib.cnfb200_loss_grad_mode.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
                                       C.c_float, C.c_float, _FP, C.c_void_p, C.c_void_p,
                                       C.POINTER(CnfStats)]
     lib.cnfb200_generate.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,

@@ -396,8 +396,6 @@ def loss(icnf, mode, xs, *args, eps=None):
 def loss_and_grad(icnf, mode, xs, *args, eps=None, want_grad=True, want_grad_x=False):
     """loss and its gradient w.r.t. ps (and xs): what Enzyme/SciMLSensitivity provide to the
     reference's `fit` (src/exts/mlj_ext/core_icnf.jl:59-63); here a discrete adjoint."""
-    if not isinstance(mode, TrainMode):
-        raise ValueError("loss_and_grad: TrainMode only")
     ys, ps, st = _split(args, icnf.cond, "loss")
     lib = _cabi.load()
     h = _upload_params(icnf, ps)
@@ -410,9 +408,9 @@ def loss_and_grad(icnf, mode, xs, *args, eps=None, want_grad=True, want_grad_x=F
     g = np.zeros(n, np.float32) if want_grad else None
     gx, gx_ptr = _out(icnf.nvars, x.B, x) if want_grad_x else (None, None)
     st_ = _cabi.CnfStats()
-    rc = lib.cnfb200_loss_grad(h, x.ptr, y.ptr if y else None, e.ptr, x.B, t0, t1, C.byref(val),
-                               g.ctypes.data if want_grad else None, gx_ptr, C.byref(st_))
-    icnf._check(rc, "cnfb200_loss_grad")
+    rc = lib.cnfb200_loss_grad_mode(h, mode.code, x.ptr, y.ptr if y else None, e.ptr if e else None, x.B, t0, t1,
+                                    C.byref(val), g.ctypes.data if want_grad else None, gx_ptr, C.byref(st_))
+    icnf._check(rc, "cnfb200_loss_grad_mode")
     icnf._last_stats = st_.as_dict()
     out = (val.value, g)
     return out + (_rows_view(gx),) if want_grad_x else out

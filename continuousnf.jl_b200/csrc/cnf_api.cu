@@ -610,16 +610,15 @@ static int ensure_bw(cnf_handle* h, long long Bs) {
     return CNF_OK;
 }
 
-extern "C" int32_t cnfb200_loss_grad(cnf_handle* h, const float* xs, const float* ys, const float* eps,
-                                     int64_t B, float t0, float t1, float* loss, float* grad_theta,
-                                     float* grad_x, cnf_stats* stats) {
-    const int mode = CNF_MODE_TRAIN;
+extern "C" int32_t cnfb200_loss_grad_mode(cnf_handle* h, int32_t mode, const float* xs, const float* ys,
+                                          const float* eps, int64_t B, float t0, float t1, float* loss,
+                                          float* grad_theta, float* grad_x, cnf_stats* stats) {
     int rc = check_call(h, mode, B);
     if (rc) return rc;
     if (!xs || !loss) { h->err = "null xs/loss"; return CNF_ERR_BADARG; }
     CNF_CUDA(cudaSetDevice(h->device));
     const cnf_config& c = h->cfg;
-    const int R = c.D + 3;
+    const int R = c.D + (mode == CNF_MODE_TRAIN ? 3 : 1);
     const bool want_grad = grad_theta || grad_x;
     h->cur_R = R;
     h->launches = 0;
@@ -642,8 +641,8 @@ extern "C" int32_t cnfb200_loss_grad(cnf_handle* h, const float* xs, const float
     CNF_CUDA(cudaMemcpyAsync(&lsum, h->d_lossacc, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     if (want_grad) {
         CNF_CUDA(cudaMemsetAsync(h->d_grad, 0, (size_t)h->nparams * sizeof(float), h->stream));
-        launch_init_ubar(h, bf, h->d_bw[11], Bglobal);
-        if ((rc = backward_sweep(h, bf, fin.naccept, Bglobal))) return rc;
+        launch_init_ubar(h, bf, h->d_bw[11], Bglobal, mode);
+        if ((rc = backward_sweep(h, bf, mode, fin.naccept, Bglobal))) return rc;
         if (grad_theta) {
             if (h->nranks > 1 && (rc = cnf_nccl_allreduce_f32(h, h->d_grad, h->nparams))) return rc;
             CNF_CUDA(cudaMemcpyAsync(grad_theta, h->d_grad, (size_t)h->nparams * sizeof(float),
@@ -662,6 +661,12 @@ extern "C" int32_t cnfb200_loss_grad(cnf_handle* h, const float* xs, const float
     *loss = (float)(lsum / (double)Bglobal);
     fill_stats(h, fin, stats);
     return fin.retcode;
+}
+
+extern "C" int32_t cnfb200_loss_grad(cnf_handle* h, const float* xs, const float* ys, const float* eps,
+                                     int64_t B, float t0, float t1, float* loss, float* grad_theta,
+                                     float* grad_x, cnf_stats* stats) {
+    return cnfb200_loss_grad_mode(h, CNF_MODE_TRAIN, xs, ys, eps, B, t0, t1, loss, grad_theta, grad_x, stats);
 }
 
 // ------------------------------------------------------------------ FP32 FFMA peak probe

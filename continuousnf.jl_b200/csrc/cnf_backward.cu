@@ -70,7 +70,7 @@ __global__ void __launch_bounds__(CNF_NT)
 k_vjp_generic(CnfBufs bf, CnfNet net, BwLayout lay, const float* __restrict__ src,
               const float* __restrict__ abar, int stage, const float* __restrict__ dtp, float c_l,
               float c_E, float c_n, float* __restrict__ ubar, float* kb0, float* kb1, float* kb2,
-              float* kb3, float* kb4, float* __restrict__ grad) {
+              float* kb3, float* kb4, float* __restrict__ grad, int unit) {
     extern __shared__ float sm[];
     constexpr int TBP = TB + 1;
     const int D = net.D, L = net.L;
@@ -95,8 +95,10 @@ k_vjp_generic(CnfBufs bf, CnfNet net, BwLayout lay, const float* __restrict__ sr
         long long b = b0 + idx % TB;
         int i = idx / TB;
         bool live = b < bf.B;
-        e[EW_AT] = live ? bf.eps[(long long)i * Bs + b] : 0.0f;
-        ybar[EW_AT] = live ? abar[(long long)i * Bs + b] : 0.0f;
+        // unit >= 0 (TestMode): eps = e_unit, the exact trace is the sum over the D unit vectors of the
+        // Hutchinson term; the zdot cotangent enters once (with unit 0)
+        e[EW_AT] = live ? (unit >= 0 ? (i == unit ? 1.0f : 0.0f) : bf.eps[(long long)i * Bs + b]) : 0.0f;
+        ybar[EW_AT] = (live && unit <= 0) ? abar[(long long)i * Bs + b] : 0.0f;
     }
     __syncthreads();
     const float* hL = sm + lay.hoff[L];
@@ -262,7 +264,7 @@ __global__ void k_kbar_init(const float* __restrict__ ubar, const float* __restr
 template <int TB>
 static void launch_vjp_tb(cnf_handle* h, const CnfBufs& bf, const BwLayout& lay, int smem,
                           const float* src, const float* abar, int stage, const float* dtp,
-                          float c_l, float c_E, float c_n, float* ubar, float** kb, float* grad) {
+                          float c_l, float c_E, float c_n, float* ubar, float** kb, float* grad, int unit) {
     static bool attr_set = false;
     if (!attr_set) {
         cudaFuncSetAttribute(k_vjp_generic<TB>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
@@ -271,29 +273,30 @@ static void launch_vjp_tb(cnf_handle* h, const CnfBufs& bf, const BwLayout& lay,
     unsigned grid = (unsigned)((bf.Bs + TB - 1) / TB);
     k_vjp_generic<TB><<<grid, CNF_NT, smem, h->stream>>>(bf, h->net, lay, src, abar, stage, dtp, c_l,
                                                         c_E, c_n, ubar, kb[0], kb[1], kb[2], kb[3],
-                                                        kb[4], grad);
+                                                        kb[4], grad, unit);
     h->launches++;
 }
 
 static int launch_vjp_generic_stage(cnf_handle* h, const CnfBufs& bf, const float* src,
                                     const float* abar, int stage, const float* dtp, float c_l,
-                                    float c_E, float c_n, float* ubar, float** kb, float* grad) {
+                                    float c_E, float c_n, float* ubar, float** kb, float* grad, int unit = -1) {
     BwLayout l1 = bw_layout(h->cfg, 0);
     int smem = 0;
     int TB = pick_tb(l1.total, &smem);
     if (!TB) { h->err = "generic backward kernel: network too wide for shared memory"; return CNF_ERR_UNSUPPORTED; }
     BwLayout lay = bw_layout(h->cfg, TB);
     switch (TB) {
-        case 32: launch_vjp_tb<32>(h, bf, lay, smem, src, abar, stage, dtp, c_l, c_E, c_n, ubar, kb, grad); break;
-        case 16: launch_vjp_tb<16>(h, bf, lay, smem, src, abar, stage, dtp, c_l, c_E, c_n, ubar, kb, grad); break;
-        case 8: launch_vjp_tb<8>(h, bf, lay, smem, src, abar, stage, dtp, c_l, c_E, c_n, ubar, kb, grad); break;
-        default: launch_vjp_tb<4>(h, bf, lay, smem, src, abar, stage, dtp, c_l, c_E, c_n, ubar, kb, grad); break;
+        case 32: launch_vjp_tb<32>(h, bf, lay, smem, src, abar, stage, dtp, c_l, c_E, c_n, ubar, kb, grad, unit); break;
+        case 16: launch_vjp_tb<16>(h, bf, lay, smem, src, abar, stage, dtp, c_l, c_E, c_n, ubar, kb, grad, unit); break;
+        case 8: launch_vjp_tb<8>(h, bf, lay, smem, src, abar, stage, dtp, c_l, c_E, c_n, ubar, kb, grad, unit); break;
+        default: launch_vjp_tb<4>(h, bf, lay, smem, src, abar, stage, dtp, c_l, c_E, c_n, ubar, kb, grad, unit); break;
     }
     return CNF_OK;
 }
 
 // forward re-evaluation used by the stage checkpointing: tensor path when available
-static int bw_eval(cnf_handle* h, const CnfBufs& bf, const float* src, float* kout) {
+static int bw_eval(cnf_handle* h, const CnfBufs& bf, int mode, const float* src, float* kout) {
+    if (mode == CNF_MODE_TEST) return launch_eval_generic(h, bf, CNF_MODE_TEST, src, kout);
     if (tc_bw_supported(h)) return tc_eval_z(h, bf, src, kout);   // only the zdot rows feed the stage inputs
     if (tc_supported(h->cfg, CNF_MODE_TRAIN) && h->tc_state) return tc_eval(h, bf, src, -1, kout, 0);
     return launch_eval_generic(h, bf, CNF_MODE_TRAIN, src, kout);
@@ -307,32 +310,36 @@ static unsigned bw_grid(long long n) {
 
 // reverse sweep over the accepted steps; d_bw: [0..4] stage inputs s_2..s_6, [5..10] kb_1..kb_6,
 // [11] ubar.  On return ubar holds d loss / d z(t0) and h->d_grad the parameter gradient.
-static int backward_sweep(cnf_handle* h, const CnfBufs& bf, long long naccept, long long Bglobal) {
+static int backward_sweep(cnf_handle* h, const CnfBufs& bf, int mode, long long naccept, long long Bglobal) {
     const cnf_config& c = h->cfg;
     const long long nz = (long long)c.D * bf.Bs;
     float** w = h->d_bw;
     float* ubar = w[11];
     float* kb[6] = {w[5], w[6], w[7], w[8], w[9], w[10]};
     const float invB = 1.0f / (float)Bglobal;
-    const float c_l = invB, c_E = c.lambda1 * invB, c_n = c.lambda2 * invB;
+    const bool train = mode == CNF_MODE_TRAIN;
+    const float c_l = invB, c_E = train ? c.lambda1 * invB : 0.0f, c_n = train ? c.lambda2 * invB : 0.0f;
     int rc;
-    const bool tcb = tc_bw_supported(h);
+    const bool tcb = train && tc_bw_supported(h);
     for (long long n = naccept - 1; n >= 0; --n) {
         const float* un = h->slots[n];
         const float* dtp = h->d_dts + n;
         // stage checkpointing: recompute k_1..k_5 and the stage inputs s_2..s_6 of step n
-        if ((rc = bw_eval(h, bf, un, h->d_K[0]))) return rc;
+        if ((rc = bw_eval(h, bf, mode, un, h->d_K[0]))) return rc;
         for (int i = 1; i <= 5; ++i) {
             k_combine_bw<<<bw_grid(nz), CNF_NT, 0, h->stream>>>(un, bf, i, dtp, w[i - 1], nz);
             h->launches++;
-            if (i < 5 && (rc = bw_eval(h, bf, w[i - 1], h->d_K[i]))) return rc;
+            if (i < 5 && (rc = bw_eval(h, bf, mode, w[i - 1], h->d_K[i]))) return rc;
         }
         k_kbar_init<<<bw_grid(nz), CNF_NT, 0, h->stream>>>(ubar, dtp, kb[0], kb[1], kb[2], kb[3], kb[4], kb[5], nz);
         h->launches++;
         for (int i = 5; i >= 0; --i) {
             const float* src = (i == 0) ? un : w[i - 1];
             if (tcb) rc = tc_vjp_stage(h, bf, src, kb[i], i, dtp, c_l, c_E, c_n, ubar, kb, h->d_grad);
-            else rc = launch_vjp_generic_stage(h, bf, src, kb[i], i, dtp, c_l, c_E, c_n, ubar, kb, h->d_grad);
+            else if (train) rc = launch_vjp_generic_stage(h, bf, src, kb[i], i, dtp, c_l, c_E, c_n, ubar, kb, h->d_grad);
+            else   // exact trace: one Hutchinson-shaped VJP per unit vector (reference src/utils.jl:1-36 seeds)
+                for (int unit = 0; unit < c.D && !rc; ++unit)
+                    rc = launch_vjp_generic_stage(h, bf, src, kb[i], i, dtp, c_l, 0.0f, 0.0f, ubar, kb, h->d_grad, unit);
             if (rc) return rc;
         }
     }

@@ -81,7 +81,7 @@ void launch_initnorm(cnf_handle* h, const CnfBufs& bf, int which);
 void launch_initdt(cnf_handle* h, int phase);  // 0: dt0 from d0,d1; 1: final dt; 2: fixed dt0 begin
 void launch_epilogue(cnf_handle* h, const CnfBufs& bf, int mode, float* logp, float* regs,
                      float* z_out, long long Bglobal);
-void launch_init_ubar(cnf_handle* h, const CnfBufs& bf, float* ubar, long long Bglobal);
+void launch_init_ubar(cnf_handle* h, const CnfBufs& bf, float* ubar, long long Bglobal, int mode);
 
 // ---- cnf_stage_generic.cu
 // du = augmented_f(stage input) ; src: D x Bs z rows ; kout: R x Bs

@@ -291,8 +291,10 @@ __global__ void k_init_ubar(const CnfCtrl* __restrict__ c, CnfBufs bf, int nvars
         ubar[(long long)i * bf.Bs + b] = live ? (v + (i >= nvars ? cA * v : 0.0f)) * invB : 0.0f;
     }
 }
-void launch_init_ubar(cnf_handle* h, const CnfBufs& bf, float* ubar, long long Bglobal) {
+void launch_init_ubar(cnf_handle* h, const CnfBufs& bf, float* ubar, long long Bglobal, int mode) {
+    // the TestMode loss has no regulariser terms (src/base_icnf.jl:489-508)
     k_init_ubar<<<(unsigned)((bf.Bs + CNF_NT - 1) / CNF_NT), CNF_NT, 0, h->stream>>>(
-        h->d_ctrl, bf, h->cfg.nvars, h->cfg.flags, h->cfg.lambda3, 1.0f / (float)Bglobal, ubar);
+        h->d_ctrl, bf, h->cfg.nvars, mode == CNF_MODE_TRAIN ? h->cfg.flags : 0u, h->cfg.lambda3,
+        1.0f / (float)Bglobal, ubar);
     h->launches++;
 }

@@ -130,19 +130,20 @@ CNF.inference(icnf::B200ICNF{<:CNF.MatrixMode}, mode::CNF.Mode, xs::AbstractMatr
     _inference(icnf, mode, xs, ys, ps)
 
 # ---- fused loss + discrete-adjoint gradient; rrule so AutoZygote works, EnzymeRules analogous
-function loss_grad(icnf::B200ICNF, xs, ys, ps; want_gx = false)
+function loss_grad(icnf::B200ICNF, xs, ys, ps; want_gx = false, mode::CNF.Mode = CNF.TrainMode())
     h = handle(icnf); set_params!(icnf, h, ps)
     D = icnf.nvars + icnf.naugmented; B = size(xs, 2)
     x = convert(Matrix{Float32}, xs); y = ys === nothing ? Float32[] : convert(Matrix{Float32}, ys)
     ϵ = Matrix{Float32}(undef, D, B); Random.rand!(icnf.rng, icnf.epsdist, ϵ)
-    t₀, t₁ = CNF.steer_tspan(icnf, CNF.TrainMode())
+    t₀, t₁ = CNF.steer_tspan(icnf, mode)
     ℓ = Ref{Float32}(0); g = zeros(Float32, length(ps)); gx = want_gx ? similar(x) : Float32[]; st = CnfStats()
     GC.@preserve x y ϵ g gx st begin
-        rc = ccall((:cnfb200_loss_grad, icnf.resource.libpath), Int32,
-            (Ptr{Cvoid}, Ptr{Float32}, Ptr{Float32}, Ptr{Float32}, Int64, Float32, Float32, Ref{Float32},
+        rc = ccall((:cnfb200_loss_grad_mode, icnf.resource.libpath), Int32,
+            (Ptr{Cvoid}, Int32, Ptr{Float32}, Ptr{Float32}, Ptr{Float32}, Int64, Float32, Float32, Ref{Float32},
              Ptr{Float32}, Ptr{Float32}, Ref{CnfStats}),
-            h, x, ys === nothing ? C_NULL : pointer(y), ϵ, B, t₀, t₁, ℓ, g, want_gx ? pointer(gx) : C_NULL, st)
-        check(icnf, h, rc, "cnfb200_loss_grad")
+            h, mode isa CNF.TrainMode ? 1 : 0, x, ys === nothing ? C_NULL : pointer(y), ϵ, B, t₀, t₁, ℓ, g,
+            want_gx ? pointer(gx) : C_NULL, st)
+        check(icnf, h, rc, "cnfb200_loss_grad_mode")
     end
     ℓ[], g, gx
 end
@@ -150,8 +151,9 @@ CNF.loss(icnf::B200ICNF{<:CNF.MatrixMode}, ::CNF.TrainMode, xs::AbstractMatrix{<
     first(loss_grad(icnf, xs, nothing, ps))
 CNF.loss(icnf::B200ICNF{<:CNF.MatrixMode}, ::CNF.TrainMode, xs::AbstractMatrix{<:Real}, ys::AbstractMatrix{<:Real}, ps::Any, st::NamedTuple) =
     first(loss_grad(icnf, xs, ys, ps))
-function ChainRulesCore.rrule(::typeof(CNF.loss), icnf::B200ICNF{<:CNF.MatrixMode}, mode::CNF.TrainMode, xs::AbstractMatrix{<:Real}, ps::Any, st::NamedTuple)
-    ℓ, g, gx = loss_grad(icnf, xs, nothing, ps; want_gx = true)
+# (TestMode: loss = -mean(logp̂x), base_icnf.jl:489-508; same entry point, exact-trace reverse sweep)
+function ChainRulesCore.rrule(::typeof(CNF.loss), icnf::B200ICNF{<:CNF.MatrixMode}, mode::CNF.Mode, xs::AbstractMatrix{<:Real}, ps::Any, st::NamedTuple)
+    ℓ, g, gx = loss_grad(icnf, xs, nothing, ps; want_gx = true, mode = mode)
     back(ℓ̄) = (ChainRulesCore.NoTangent(), ChainRulesCore.NoTangent(), ChainRulesCore.NoTangent(), ℓ̄ .* gx, ℓ̄ .* g, ChainRulesCore.NoTangent())
     ℓ, back
 end

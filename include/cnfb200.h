@@ -134,6 +134,13 @@ CNF_API int32_t cnfb200_loss_grad(cnf_handle* h, const float* xs, const float* y
                           int64_t B, float t0, float t1, float* loss, float* grad_theta,
                           float* grad_x, cnf_stats* stats);
 
+/* the same for either mode: mode = CNF_MODE_TEST is loss(icnf, TestMode(), ...) = -mean(logp)
+ * (src/base_icnf.jl:489-508; differentiated w.r.t. ps and xs in test/call_tests.jl:239-251), whose
+ * reverse sweep differentiates the exact trace (eps is ignored and may be NULL). */
+CNF_API int32_t cnfb200_loss_grad_mode(cnf_handle* h, int32_t mode, const float* xs, const float* ys,
+                               const float* eps, int64_t B, float t0, float t1, float* loss,
+                               float* grad_theta, float* grad_x, cnf_stats* stats);
+
 /* replaces generate(...) = generate_prob + generate_sol (src/base_icnf.jl:358-405, 202-211,
  * 447-466): integrates z0 (D x n, drawn by the caller from basedist) from t_from to t_to
  * and returns rows 1:nvars.  xs_out: nvars x n. */

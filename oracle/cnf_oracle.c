@@ -609,16 +609,20 @@ static void outer_acc(double* gW, int dout, int ncols, const float* a, const flo
 /* VJP of the TrainMode augmented_f at stage input s (rows 0:D of u), cotangent
  * (a[D x B], alpha, beta, gamma) on (zdot, ldot, Edot, ndot).  Writes zbar (D x B, stride D)
  * and accumulates parameter gradients into gth (layout of theta). */
-static void rhs_vjp_tile(const omodel* m, oscratch* sc, obscratch* bs, const float* u,
+/* unit >= 0 (TestMode, exact trace): eps is the unit vector e_unit — the trace row is
+ * -sum_i e_i^T J e_i (src/icnf.jl:148-164), so its VJP is the sum over i of the Hutchinson VJP with
+ * eps = e_i; the zdot cotangent abar is applied with unit 0 only and zbar accumulates over units. */
+static void rhs_vjp_tile(const omodel* m, oscratch* sc, obscratch* bs, const float* u, int R, int unit,
                          const float* ys, const float* eps, const float* abar, float alpha,
                          float beta, float gamma, float* zbar, double* gth, int64_t b0, int ns) {
-    const int D = m->D, L = m->L, R = D + 3;
+    const int D = m->D, L = m->L;
     const int jvp = m->cfg.trace_mode == CNF_TRACE_JVP;
     load_h0(m, sc, u, R, ys, b0, ns);
     nn_forward(m, sc);
     float* e = sc->t0;
     for (int i = 0; i < D; ++i)
-        for (int s = 0; s < TS; ++s) e[i * TS + s] = (s < ns) ? eps[(b0 + s) * D + i] : 0.0f;
+        for (int s = 0; s < TS; ++s)
+            e[i * TS + s] = (s < ns) ? (unit >= 0 ? (i == unit ? 1.0f : 0.0f) : eps[(b0 + s) * D + i]) : 0.0f;
     if (jvp) jvp_chain(m, sc, e); else vjp_chain(m, sc, e);
     const float* y = sc->h[L];
     const float* v = jvp ? sc->g[L] : sc->q[1];
@@ -638,7 +642,7 @@ static void rhs_vjp_tile(const omodel* m, oscratch* sc, obscratch* bs, const flo
         float cg = (live && (m->cfg.flags & CNF_FLAG_NORM_J) && nvs > 0.0f) ? gamma / nvs : 0.0f;
         float ca = live ? alpha : 0.0f;
         for (int i = 0; i < D; ++i) {
-            float ab = live ? abar[(b0 + s) * D + i] : 0.0f;
+            float ab = (live && unit <= 0) ? abar[(b0 + s) * D + i] : 0.0f;
             ybar[i * TS + s] = fmaf(cb, y[i * TS + s], ab);
             vbar[i * TS + s] = fmaf(cg, v[i * TS + s], -ca * e[i * TS + s]);
         }
@@ -703,10 +707,13 @@ static void rhs_vjp_tile(const omodel* m, oscratch* sc, obscratch* bs, const flo
         dense_mulT(th + m->w_off[l - 1], dout, used, bs->pb, hb);
     }
     for (int s = 0; s < ns; ++s)
-        for (int i = 0; i < D; ++i) zbar[(b0 + s) * D + i] = hb[i * TS + s];
+        for (int i = 0; i < D; ++i) {
+            if (unit > 0) zbar[(b0 + s) * D + i] += hb[i * TS + s];
+            else zbar[(b0 + s) * D + i] = hb[i * TS + s];
+        }
 }
 
-static void rhs_vjp_all(const omodel* m, const float* u, const float* ys, const float* eps,
+static void rhs_vjp_all(const omodel* m, const float* u, int R, int unit, const float* ys, const float* eps,
                         const float* abar, float alpha, float beta, float gamma, float* zbar,
                         double* gth, int64_t nparams, int64_t B) {
     int64_t ntile = (B + TS - 1) / TS;
@@ -721,7 +728,7 @@ static void rhs_vjp_all(const omodel* m, const float* u, const float* ys, const 
         for (int64_t t = 0; t < ntile; ++t) {
             int64_t b0 = t * TS;
             int ns = (int)((B - b0) < TS ? (B - b0) : TS);
-            rhs_vjp_tile(m, &sc, &bs, u, ys, eps, abar, alpha, beta, gamma, zbar, gl, b0, ns);
+            rhs_vjp_tile(m, &sc, &bs, u, R, unit, ys, eps, abar, alpha, beta, gamma, zbar, gl, b0, ns);
         }
 #pragma omp critical
         for (int64_t p = 0; p < nparams; ++p) gth[p] += gl[p];
@@ -732,33 +739,36 @@ static void rhs_vjp_all(const omodel* m, const float* u, const float* ys, const 
 }
 
 /* loss(icnf, TrainMode(), xs[, ys], ps, st) = mean(-logp + l1 E + l2 n + l3 A)
- * (src/icnf.jl:481-502) and its discrete gradient w.r.t. theta and xs. */
-int32_t cnf_oracle_loss_grad(const cnf_config* cfg, const float* theta, int64_t nparams,
-                             const int64_t* w_off, const int64_t* b_off, const float* xs,
-                             const float* ys, const float* eps, int64_t B, float t0, float t1,
-                             float* loss, float* grad_theta, float* grad_x, cnf_stats* stats) {
+ * (src/icnf.jl:481-502), loss(icnf, TestMode(), ...) = -mean(logp) (src/base_icnf.jl:489-508),
+ * and the discrete gradient w.r.t. theta and xs. */
+int32_t cnf_oracle_loss_grad_mode(const cnf_config* cfg, const float* theta, int64_t nparams,
+                                  const int64_t* w_off, const int64_t* b_off, int32_t mode, const float* xs,
+                                  const float* ys, const float* eps, int64_t B, float t0, float t1,
+                                  float* loss, float* grad_theta, float* grad_x, cnf_stats* stats) {
     omodel m;
     omodel_init(&m, cfg, theta, w_off, b_off);
-    const int D = m.D, R = D + 3, nv = cfg->nvars;
+    const int train = mode == CNF_MODE_TRAIN;
+    const int D = m.D, R = D + (train ? 3 : 1), nv = cfg->nvars;
     const int64_t nel = (int64_t)R * B;
     float* u = assemble_u0(&m, R, xs, B);
     ostats st;
     otape tape;
     memset(&tape, 0, sizeof(tape));
     int want_grad = grad_theta || grad_x;
-    tsit5_solve(&m, CNF_MODE_TRAIN, u, ys, eps, B, t0, t1, &st, want_grad ? &tape : NULL);
+    tsit5_solve(&m, mode, u, ys, eps, B, t0, t1, &st, want_grad ? &tape : NULL);
     float* logp = (float*)malloc(sizeof(float) * (size_t)B);
     float* regs = (float*)malloc(sizeof(float) * 3 * (size_t)B);
-    final_split(&m, CNF_MODE_TRAIN, u, B, logp, regs, NULL);
+    final_split(&m, mode, u, B, logp, regs, NULL);
     double acc = 0.0;
     for (int64_t b = 0; b < B; ++b)
-        acc += (double)(-logp[b] + cfg->lambda1 * regs[b * 3] + cfg->lambda2 * regs[b * 3 + 1] +
-                        cfg->lambda3 * regs[b * 3 + 2]);
+        acc += train ? (double)(-logp[b] + cfg->lambda1 * regs[b * 3] + cfg->lambda2 * regs[b * 3 + 1] +
+                                cfg->lambda3 * regs[b * 3 + 2])
+                     : (double)(-logp[b]);
     *loss = (float)(acc / (double)B);
     copy_stats(stats, &st);
     if (want_grad) {
         const float invB = 1.0f / (float)B;
-        const int useA = (cfg->flags & CNF_FLAG_NORM_Z_AUG) && (cfg->flags & CNF_FLAG_AUGMENTED);
+        const int useA = train && (cfg->flags & CNF_FLAG_NORM_Z_AUG) && (cfg->flags & CNF_FLAG_AUGMENTED);
         float* ubar = (float*)malloc(sizeof(float) * (size_t)D * (size_t)B);
         for (int64_t b = 0; b < B; ++b) {
             const float* ub = u + b * R;
@@ -768,7 +778,7 @@ int32_t cnf_oracle_loss_grad(const cnf_config* cfg, const float* theta, int64_t 
             for (int i = 0; i < D; ++i)
                 ubar[b * D + i] = (ub[i] + (i >= nv ? cA * ub[i] : 0.0f)) * invB;
         }
-        const float c_l = invB, c_E = cfg->lambda1 * invB, c_n = cfg->lambda2 * invB;
+        const float c_l = invB, c_E = train ? cfg->lambda1 * invB : 0.0f, c_n = train ? cfg->lambda2 * invB : 0.0f;
         double* gth = (double*)calloc((size_t)nparams, sizeof(double));
         float* k[6];
         float* s[6];
@@ -783,16 +793,21 @@ int32_t cnf_oracle_loss_grad(const cnf_config* cfg, const float* theta, int64_t 
         for (int64_t n = tape.n - 1; n >= 0; --n) {
             const float dt = tape.dt[n];
             memcpy(s[0], tape.u[n], sizeof(float) * (size_t)nel);
-            rhs_all(&m, CNF_MODE_TRAIN, s[0], ys, eps, k[0], B);
+            rhs_all(&m, mode, s[0], ys, eps, k[0], B);
             for (int i = 1; i < 6; ++i) { /* stage checkpointing: recompute the stage inputs */
                 rk_combine(s[i], s[0], k, A_[i], i, dt, nel);
-                rhs_all(&m, CNF_MODE_TRAIN, s[i], ys, eps, k[i], B);
+                rhs_all(&m, mode, s[i], ys, eps, k[i], B);
             }
             for (int j = 0; j < 6; ++j)
                 for (int64_t e = 0; e < nz; ++e) kb[j][e] = dt * A_[6][j] * ubar[e];
             for (int i = 5; i >= 0; --i) {
                 float w = dt * A_[6][i];
-                rhs_vjp_all(&m, s[i], ys, eps, kb[i], w * c_l, w * c_E, w * c_n, sbar, gth, nparams, B);
+                if (train) {
+                    rhs_vjp_all(&m, s[i], R, -1, ys, eps, kb[i], w * c_l, w * c_E, w * c_n, sbar, gth, nparams, B);
+                } else {
+                    for (int unit = 0; unit < D; ++unit)
+                        rhs_vjp_all(&m, s[i], R, unit, ys, eps, kb[i], w * c_l, 0.0f, 0.0f, sbar, gth, nparams, B);
+                }
                 for (int64_t e = 0; e < nz; ++e) ubar[e] += sbar[e];
                 for (int j = 0; j < i; ++j) {
                     float c = dt * A_[i][j];
@@ -811,6 +826,14 @@ int32_t cnf_oracle_loss_grad(const cnf_config* cfg, const float* theta, int64_t 
     tape_free(&tape);
     free(logp); free(regs); free(u);
     return st.retcode;
+}
+
+int32_t cnf_oracle_loss_grad(const cnf_config* cfg, const float* theta, int64_t nparams,
+                             const int64_t* w_off, const int64_t* b_off, const float* xs,
+                             const float* ys, const float* eps, int64_t B, float t0, float t1,
+                             float* loss, float* grad_theta, float* grad_x, cnf_stats* stats) {
+    return cnf_oracle_loss_grad_mode(cfg, theta, nparams, w_off, b_off, CNF_MODE_TRAIN, xs, ys, eps, B, t0, t1,
+                                     loss, grad_theta, grad_x, stats);
 }
 
 int32_t cnf_oracle_num_threads(void) {

@@ -159,7 +159,7 @@ def generate(cfg, theta, mode, z0, ys=None, eps=None, t_from=1.0, t_to=0.0):
     return xs, st.as_dict()
 
 
-def loss_grad(cfg, theta, xs, ys=None, eps=None, t0=0.0, t1=1.0, want_grad=True):
+def loss_grad(cfg, theta, xs, ys=None, eps=None, t0=0.0, t1=1.0, want_grad=True, mode=1):
     w, b, n = offsets(list(cfg.dims[:cfg.n_layers + 1]))
     xs, ys, eps, theta = _prep(xs), _prep(ys), _prep(eps), _prep(theta)
     B = xs.shape[0]
@@ -167,9 +167,9 @@ def loss_grad(cfg, theta, xs, ys=None, eps=None, t0=0.0, t1=1.0, want_grad=True)
     gth = np.zeros(n, np.float32) if want_grad else None
     gx = np.zeros_like(xs) if want_grad else None
     st = Stats()
-    lib().cnf_oracle_loss_grad(C.byref(cfg), _f(theta), C.c_int64(n), _i64(w), _i64(b), _f(xs),
-                               _f(ys), _f(eps), C.c_int64(B), C.c_float(t0), C.c_float(t1),
-                               C.byref(loss), _f(gth), _f(gx), C.byref(st))
+    lib().cnf_oracle_loss_grad_mode(C.byref(cfg), _f(theta), C.c_int64(n), _i64(w), _i64(b), C.c_int32(mode),
+                                    _f(xs), _f(ys), _f(eps), C.c_int64(B), C.c_float(t0), C.c_float(t1),
+                                    C.byref(loss), _f(gth), _f(gx), C.byref(st))
     return loss.value, gth, gx, st.as_dict()
 
 

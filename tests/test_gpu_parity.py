@@ -88,6 +88,33 @@ def test_loss_grad(cid, B, trace_mode):
     assert relnorm(np.asarray(gx).T, rgx) < tol_g
 
 
+@pytest.mark.parametrize("cid,B,tm", [("C2", 1024, 1), ("C2", 512, 0), ("C1", 256, 0), ("C4", 128, 0)])
+def test_loss_grad_testmode(cid, B, tm):
+    """gradient of loss(icnf, TestMode(), ...) = -mean(logp) w.r.t. ps and xs (reference
+    test/call_tests.jl:239-251 differentiates it): exact-trace reverse sweep vs the oracle's"""
+    inp = wl.make_inputs(cid, B=B)
+    c = wl.CONFIGS[cid]
+    icnf = make_icnf(cid, trace_mode=tm)
+    val, g, gx = cnf.loss_and_grad(icnf, cnf.TestMode(), inp["xs"].T, *args_of(inp), want_grad_x=True)
+    st = cnf.last_stats(icnf)
+    rval, rg, rgx, rst = O.loss_grad(oracle_cfg(cid, trace_mode=tm), inp["theta"], inp["xs"], inp["ys"], None,
+                                     *c["tspan"], mode=0)
+    assert abs(st["naccept"] - rst["naccept"]) <= 1, (st, rst)
+    O.set_perturb(True)
+    pval, pg, _, pst = O.loss_grad(oracle_cfg(cid, trace_mode=tm), inp["theta"], inp["xs"], inp["ys"], None,
+                                   *c["tspan"], mode=0)
+    O.set_perturb(False)
+    same = pst["naccept"] == rst["naccept"]
+    fl_l = 4 * abs(pval - rval) / abs(rval) if same else 0.0
+    fl_g = 4 * relnorm(pg, rg) if same else 0.0
+    tol_l, tol_g = (max(1e-4, fl_l), max(1e-3, fl_g)) if st["naccept"] == rst["naccept"] else (5e-3, 5e-2)
+    assert abs(val - rval) / abs(rval) < tol_l
+    assert relnorm(g, rg) < tol_g
+    assert relnorm(np.asarray(gx).T, rgx) < tol_g
+    # and the loss agrees with the TestMode inference path
+    assert abs(val - cnf.loss(icnf, cnf.TestMode(), inp["xs"].T, *args_of(inp))) < 1e-5 * abs(val)
+
+
 @pytest.mark.parametrize("cid,B", [("C1", 512), ("C2", 2048), ("C4", 512)])
 def test_generate_roundtrip(cid, B):
     """K7: generate from z(t1) returns x within solver tolerance; and parity with the oracle."""

@@ -118,6 +118,21 @@ def test_k6_discrete_gradient_vs_float64_autograd(cid, B, tm):
     assert relnorm(gx, r["grad_x"]) < 1e-4
 
 
+@pytest.mark.parametrize("cid,B,tm", [("C2", 16, 1), ("C2", 16, 0), ("C4", 8, 0)])
+def test_k6c_testmode_loss_gradient_vs_float64_autograd(cid, B, tm):
+    """loss(icnf, TestMode(), ...) = -mean(logp) (reference src/base_icnf.jl:489-508) is differentiated by
+    the reference's tests too (test/call_tests.jl:239-251): exact-trace reverse sweep vs torch autograd"""
+    c = wl.CONFIGS[cid]
+    inp = wl.make_inputs(cid, B=B)
+    cfg = oracle_cfg(cid, trace_mode=tm)
+    val, g, gx, st = O.loss_grad(cfg, inp["theta"], inp["xs"], inp["ys"], None, *c["tspan"], mode=0)
+    dts = [float(d) for d in O.last_dts()]
+    r = F.run(cfg, inp["theta"], 0, inp["xs"], inp["ys"], None, *c["tspan"], frozen_dts=dts, requires_grad=True)
+    assert abs(val - r["loss"]) / abs(r["loss"]) < 1e-5
+    assert relnorm(g, r["grad_theta"]) < 1e-4
+    assert relnorm(gx, r["grad_x"]) < 1e-4
+
+
 def test_k6b_float64_gradient_vs_finite_differences():
     cid, B = "C1", 8
     c = wl.CONFIGS[cid]
