@@ -170,3 +170,34 @@ def test_tensor_path_is_selected_for_wide_train_and_narrow_for_c2():
     icnf = make_icnf("C2")
     cnf.inference(icnf, cnf.TestMode(), inp["xs"].T, inp["theta"], {})
     assert cnf.last_stats(icnf)["kernel_path"] == 2
+
+
+@pytest.mark.parametrize("nvars,naug,C,hidden,B", [(5, 0, 3, (160, 96), 300), (3, 2, 0, (64, 32, 96), 1000), (20, 0, 0, (320,), 130)])
+def test_tensor_path_odd_shapes(nvars, naug, C, hidden, B):
+    """tensor path forced on shapes that exercise every padding rule (widths that are not multiples
+    of 64, D < 16, condition rows, 2- and 4-layer chains, ragged batches) against the generic path"""
+    D = nvars + naug
+    dims = [D + C, *hidden, D]
+    rng = np.random.default_rng(11)
+    theta = wl.glorot_theta(dims, rng)
+    theta[theta == 0] = 0.05 * rng.standard_normal(int((theta == 0).sum())).astype(np.float32)   # non-zero biases
+    xs = rng.normal(0, 1, (B, nvars)).astype(np.float32)
+    ys = rng.normal(0, 1, (B, C)).astype(np.float32) if C else None
+    eps = rng.normal(0, 1, (B, D)).astype(np.float32)
+    nn = cnf.Chain(*[cnf.Dense(dims[i], dims[i + 1], "tanh") for i in range(len(dims) - 1)])
+    tag = cnf.CondRNODE if C else cnf.RNODE
+    out = {}
+    for kp in (1, 3):
+        icnf = cnf.construct(tag, nn, nvars, naug, compute_mode=cnf.DIVecJacMatrixMode(), tspan=(0.0, 1.0),
+                             lambda1=1e-2, lambda2=1e-2, lambda3=(1e-2 if naug else 0.0),
+                             resource=cnf.B200Libs(0, kp), rng=np.random.default_rng(1))
+        tail = ((ys.T,) if C else ()) + (theta, {})
+        val, g, gx = cnf.loss_and_grad(icnf, cnf.TrainMode(), xs.T, *tail, eps=eps.T, want_grad_x=True)
+        st = cnf.last_stats(icnf)
+        assert st["kernel_path"] == kp and st["retcode"] == 0
+        out[kp] = (val, g, np.asarray(gx), st["naccept"])
+    assert abs(out[1][3] - out[3][3]) <= 1
+    if out[1][3] == out[3][3]:
+        assert abs(out[1][0] - out[3][0]) / abs(out[1][0]) < 1e-4
+        assert relnorm(out[3][1], out[1][1]) < 1e-3
+        assert relnorm(out[3][2], out[1][2]) < 1e-3
