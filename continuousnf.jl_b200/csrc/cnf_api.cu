@@ -207,7 +207,8 @@ extern "C" int32_t cnfb200_set_option(cnf_handle* h, const char* key, int64_t va
     if (!h || !key) return CNF_ERR_BADARG;
     if (!strcmp(key, "time_stages")) { h->time_stages = value != 0; return CNF_OK; }
     if (!strcmp(key, "kernel_path")) { h->cfg.kernel_path = (int32_t)value; return CNF_OK; }
-    if (!strcmp(key, "tc_prefetch")) { h->tc_noprefetch = value == 0; return CNF_OK; }
+    if (!strcmp(key, "tc_dbg")) { h->tc_dbg = (int)value; return CNF_OK; }
+    if (!strcmp(key, "tc_ring")) { h->tc_noring = value == 0; return CNF_OK; }
     if (!strcmp(key, "tc_backward")) { h->tc_bw_off = value == 0; return CNF_OK; }
     if (!strcmp(key, "wg_lbo")) { h->wg_lbo = value; return CNF_OK; }
     if (!strcmp(key, "wg_sbo")) { h->wg_sbo = value; return CNF_OK; }

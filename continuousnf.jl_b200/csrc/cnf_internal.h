@@ -51,7 +51,8 @@ struct cnf_handle {
     long long n_stage = 0;
     int path_used = 0;
     void* tc_state = nullptr;   // tensor-core path state (cnf_stage_tc.cu)
-    bool tc_noprefetch = true;  // option "tc_prefetch" = 1: TMA L2 prefetch of the epilogue operands (measured: no gain)
+    int tc_dbg = 0;
+    bool tc_noring = false;     // option "tc_ring" = 0: epilogue operands through registers instead of the shared-memory ring
     bool tc_bw_off = false;     // option "tc_backward" = 0: reverse sweep on the generic SIMT kernels
     long long wg_lbo = 0, wg_sbo = 0;   // debug override of the MN-major descriptor strides (0 = default)
     void* narrow_w = nullptr;   // host copy of the packed kernel-parameter weights (narrow path)

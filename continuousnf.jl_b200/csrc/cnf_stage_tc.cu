@@ -25,7 +25,8 @@
 
 #define TC_BM 128
 #define TC_BK 64            // bf16 elements per 128-byte swizzled row
-#define TC_THREADS 448      // 14 warps: TMA, MMA, 12 epilogue
+#define TC_THREADS 480      // 15 warps: TMA, MMA, 12 epilogue, epilogue-operand producer
+#define TC_AUX_WARP 14
 #define TC_EPI_WARP0 2
 
 enum {
@@ -68,6 +69,7 @@ struct TcEpi {
     int stage;                     // 0..5
     float c_l, c_E, c_n;           // cotangents of the quadrature rows (1/B, lambda1/B, lambda2/B)
     int B;                         // live samples (rows >= B are padding)
+    int dbg;                       // debug switches of the ring kernels
     // ---- host only: whose tiles the TMA producer prefetches into L2 for the epilogue (TcPlane*, TcF32*)
     const void* aux_p;
     const void* aux_f;
@@ -98,12 +100,12 @@ __device__ __forceinline__ float2 tc_unpack2(uint32_t w) {
 
 struct TcMaps {
     CUtensorMap a[2], b[2];   // A planes, B planes
-    CUtensorMap x[3];         // epilogue operands prefetched into L2: hi / lo plane (64-column boxes), fp32 array (32-column boxes)
-    int nxp, nxf;             // 0/1: planes present, fp32 array present
+    CUtensorMap x[3];         // RING kernels: epilogue operands, hi / lo plane and fp32 array, boxes of 128 rows x 16 columns
 };
 
 struct TcSmemCtl {
     uint64_t full[8], empty[8], tfull[2], tempty[2];
+    uint64_t xfull[12], xempty[12];   // rings of epilogue-operand chunks (RING kernels): [sub][depth]
     uint32_t tmem_base;
     float2 red[2][4][3][32];   // [tile parity][lane quadrant][warp of the quadrant][lane]: row reductions
 };
@@ -223,6 +225,62 @@ __device__ __forceinline__ void tc_aux_load(const TcEpi& ep, long long rloc, lon
     }
 }
 
+// Epilogue-operand ring (RING kernels: the kinds whose epilogue reads h planes / an fp32 side array).
+// A dedicated producer thread TMA-loads, chunk by chunk (128 rows x 16 columns), what the epilogue
+// warps need into a ring of shared-memory slots, as far ahead as the ring is deep; the registers of
+// 12 warps can only hold one chunk ahead (~48 KB in flight per SM), which left these kernels at
+// ~3 TB/s waiting on long-scoreboard stalls.
+// Each of the three warp groups (sub = chunk % 3) has its own ring of `d` slots, visited in order by
+// its four warps: a warp that waits for round r of a slot has itself consumed round r-1 of it.  (With
+// one ring shared by all groups a warp could reach a slot two phases early, and a parity wait on an
+// mbarrier cannot tell "two phases behind" from "complete": stale operands in random rows.)
+struct TcRing {
+    const uint8_t* base;
+    uint32_t j;      // chunks this warp has consumed so far
+    int d;           // slots per warp group
+    uint32_t zmask;  // always 0 (from a kernel argument): see tc_ring_read
+};
+template <bool BWD, int KIND> struct TcRingOf {
+    static constexpr bool kind = BWD ? (KIND == TCB_BWD_HIDDEN || KIND == TCB_GBAR_HIDDEN || KIND == TCB_HBAR_HIDDEN)
+                                     : (KIND == TC_BWD_HIDDEN);
+    static constexpr bool f32 = BWD && (KIND == TCB_GBAR_HIDDEN || KIND == TCB_HBAR_HIDDEN);
+    static constexpr uint32_t slot_bytes = f32 ? 16384u : 8192u;
+};
+__device__ __forceinline__ void tc_lds128(uint32_t addr, uint32_t* v) {
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]) : "r"(addr) : "memory");
+}
+template <bool F32>
+__device__ __forceinline__ void tc_ring_read(TcSmemCtl* ctl, TcRing& ring, int sub, int row, int lane, TcAux& a) {
+    const int slot = sub * ring.d + (int)(ring.j % (uint32_t)ring.d);
+    tc::mbar_wait(&ctl->xfull[slot], (ring.j / (uint32_t)ring.d) & 1);
+    ring.j++;
+    const uint32_t sp = tc::smem_u32(ring.base) + (uint32_t)slot * (F32 ? 16384u : 8192u);
+    uint32_t dep = 0;
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+        tc_lds128(sp + q * 4096 + row * 32, a.p[q]);
+        tc_lds128(sp + q * 4096 + row * 32 + 16, a.p[q] + 4);
+        dep ^= a.p[q][0] ^ a.p[q][4];
+    }
+    if (F32) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            uint32_t w[4];
+            tc_lds128(sp + 8192 + row * 64 + j * 16, w);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) a.f[4 * j + i] = __uint_as_float(w[i]);
+            dep ^= w[0];
+        }
+    }
+    // The slot may be overwritten by the async proxy as soon as the fourth warp has arrived, so every
+    // lane's reads must have RETURNED before the arrive is issued: the arrive's address is made to depend
+    // on the loaded words (ptxas does not wait for outstanding loads ahead of a SYNCS.ARRIVE by itself).
+    dep = __reduce_or_sync(0xffffffffu, dep & ring.zmask);   // zmask is 0 at run time, unknown to the compiler
+    if (lane == 0) {
+        asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tc::smem_u32(&ctl->xempty[slot]) + dep) : "memory");
+    }
+}
+
 // sum of (a, b) over the warps of a TMEM lane quadrant (same lane = same sample row);
 // double-buffered by tile parity, so one named barrier per reduction is enough
 __device__ __forceinline__ float2 tc_quad_reduce(TcSmemCtl* ctl, int quad, int sub, int lane, int par, float a, float b) {
@@ -238,9 +296,9 @@ __device__ __forceinline__ float2 tc_quad_reduce(TcSmemCtl* ctl, int quad, int s
 }
 
 // ---- forward-solve epilogue of one 128 x BN tile (kinds TC_*); cur = aux of this warp's first chunk
-template <int PREC, int KIND>
+template <int PREC, int KIND, bool RING>
 __device__ __forceinline__ void tc_epilogue_fwd(const TcEpi& ep, TcSmemCtl* ctl, uint32_t tbase, int mb, int nb, int BN,
-                                                int quad, int sub, int lane, int par, TcAux& cur) {
+                                                int quad, int sub, int lane, int par, TcAux& cur, TcRing& ring) {
     const long long rloc = (long long)mb * TC_BM + quad * 32 + lane;   // row inside the chunk
     const long long grow = ep.row0 + rloc;                               // global sample
     constexpr bool last_kind = (KIND == TC_FWD_LAST || KIND == TC_BWD_LAST || KIND == TC_JVP_LAST);
@@ -251,7 +309,8 @@ __device__ __forceinline__ void tc_epilogue_fwd(const TcEpi& ep, TcSmemCtl* ctl,
         const int c0 = ch * TC_CW, ng = nb * BN + c0;   // global column of v[0]
         if (ng >= nmax) break;
         TcAux nxt;
-        if (ch + TC_NSUB < nchunk && ng + TC_NSUB * TC_CW < nmax)
+        if (RING) tc_ring_read<false>(ctl, ring, sub, quad * 32 + lane, lane, cur);
+        else if (ch + TC_NSUB < nchunk && ng + TC_NSUB * TC_CW < nmax)
             tc_aux_load<PREC, false, KIND>(ep, rloc, grow, ng + TC_NSUB * TC_CW, nxt);
         uint32_t v[TC_CW];
         tc::tmem_ld_32x16(tbase + c0, v);
@@ -292,7 +351,7 @@ __device__ __forceinline__ void tc_epilogue_fwd(const TcEpi& ep, TcSmemCtl* ctl,
                 }
             }
         }
-        cur = nxt;
+        if (!RING) cur = nxt;
     }
     if (!last_kind || (KIND == TC_FWD_LAST && ep.vjp == 2)) return;   // (vjp 2: zdot rows only)
     // per-sample reductions over all D columns: partial sums per warp, combined per quadrant
@@ -307,9 +366,9 @@ __device__ __forceinline__ void tc_epilogue_fwd(const TcEpi& ep, TcSmemCtl* ctl,
 }
 
 // ---- reverse-sweep epilogue of one 128 x BN tile (kinds TCB_*, bfloat16 planes)
-template <int KIND>
+template <int KIND, bool RING>
 __device__ __forceinline__ void tc_epilogue_bwd(const TcEpi& ep, TcSmemCtl* ctl, uint32_t tbase, int mb, int nb, int BN,
-                                                int quad, int sub, int lane, int par, TcAux& cur) {
+                                                int quad, int sub, int lane, int par, TcAux& cur, TcRing& ring) {
     const long long rloc = (long long)mb * TC_BM + quad * 32 + lane;
     const long long grow = ep.row0 + rloc;
     const bool live = grow < (long long)ep.B;
@@ -389,7 +448,8 @@ __device__ __forceinline__ void tc_epilogue_bwd(const TcEpi& ep, TcSmemCtl* ctl,
         const int c0 = ch * TC_CW, ng = nb * BN + c0;
         if (ng >= ep.N) break;
         TcAux nxt;
-        if (ch + TC_NSUB < nchunk && ng + TC_NSUB * TC_CW < ep.N)
+        if (RING) tc_ring_read<TcRingOf<true, KIND>::f32>(ctl, ring, sub, quad * 32 + lane, lane, cur);
+        else if (ch + TC_NSUB < nchunk && ng + TC_NSUB * TC_CW < ep.N)
             tc_aux_load<1, true, KIND>(ep, rloc, grow, ng + TC_NSUB * TC_CW, nxt);
         float y[TC_CW], yb[TC_CW];
         if (KIND == TCB_GBAR_LAST) {
@@ -442,15 +502,15 @@ __device__ __forceinline__ void tc_epilogue_bwd(const TcEpi& ep, TcSmemCtl* ctl,
             }
         }
         tc_store_planes16<1>(x, ep.out, rloc * ep.ld_out + ng);
-        cur = nxt;
+        if (!RING) cur = nxt;
     }
 }
 
 // BM x BN output tile per (m_blk, n_blk); K in blocks of 64 bf16; persistent over tiles.
 // PREC = operand format of the two hi/lo planes (0: IEEE half, forward solve; 1: bfloat16, reverse sweep).
-template <int PREC, bool BWD, int KIND>
+template <int PREC, bool BWD, int KIND, bool RING>
 __global__ void __launch_bounds__(TC_THREADS, 1)
-k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, int nk, int nstage, TcEpi ep) {
+k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, int nk, int nstage, int naux, TcEpi ep) {
     if (ep.ctrl && ep.ctrl->done) return;
     if (ep.kout_ind) ep.kout = *ep.kout_ind;
     extern __shared__ uint8_t smem_raw[];
@@ -458,7 +518,9 @@ k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, i
     const uint32_t a_bytes = TC_BM * 128;          // one plane of A per stage
     const uint32_t b_bytes = (uint32_t)BN * 128;   // one plane of B per stage
     const uint32_t stage_bytes = 2 * (a_bytes + b_bytes);
-    TcSmemCtl* ctl = reinterpret_cast<TcSmemCtl*>(smem + (size_t)nstage * stage_bytes);
+    constexpr uint32_t slot_bytes = TcRingOf<BWD, KIND>::slot_bytes;
+    uint8_t* ring_base = smem + (size_t)nstage * stage_bytes;
+    TcSmemCtl* ctl = reinterpret_cast<TcSmemCtl*>(ring_base + (RING ? (size_t)TC_NSUB * naux * slot_bytes : 0));   // naux = slots per warp group
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int total = m_tiles * n_tiles;
 
@@ -466,6 +528,8 @@ k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, i
         for (int q = 0; q < 2; ++q) { tc::tma_prefetch_desc(&mp.a[q]); tc::tma_prefetch_desc(&mp.b[q]); }
         for (int s = 0; s < nstage; ++s) { tc::mbar_init(&ctl->full[s], 1); tc::mbar_init(&ctl->empty[s], 1); }
         for (int a = 0; a < 2; ++a) { tc::mbar_init(&ctl->tfull[a], 1); tc::mbar_init(&ctl->tempty[a], 4 * TC_NSUB); }
+        if (RING)
+            for (int x = 0; x < TC_NSUB * naux; ++x) { tc::mbar_init(&ctl->xfull[x], 1); tc::mbar_init(&ctl->xempty[x], 4); }
         tc::fence_barrier_init();
     }
     if (warp == 1) tc::tmem_alloc(&ctl->tmem_base, 512);
@@ -489,14 +553,6 @@ k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, i
                     }
                     if (++stage == nstage) { stage = 0; phase ^= 1; }
                 }
-                // what the epilogue of this tile reads from global memory: on its way to L2 while the MMAs run
-                if (mp.nxp)
-                    for (int c = 0; c < BN && nb * BN + c < ep.N; c += 64) {
-                        tc::tma_prefetch_2d(&mp.x[0], nb * BN + c, mb * TC_BM);
-                        tc::tma_prefetch_2d(&mp.x[1], nb * BN + c, mb * TC_BM);
-                    }
-                if (mp.nxf)
-                    for (int c = 0; c < BN && nb * BN + c < ep.N; c += 32) tc::tma_prefetch_2d(&mp.x[2], nb * BN + c, mb * TC_BM);
             }
         }
     } else if (warp == 1) {
@@ -530,7 +586,29 @@ k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, i
                 tc::umma_commit(&ctl->tfull[acc]);
             }
         }
+    } else if (warp == TC_AUX_WARP) {
+        if (RING && lane == 0) {   // ===== epilogue-operand producer: chunk c of a tile goes to the warps with sub = c % 3
+            uint32_t j[TC_NSUB] = {0, 0, 0};
+            for (int t = blockIdx.x; t < total; t += gridDim.x) {
+                const int mb = t / n_tiles, nb = t % n_tiles;
+                const int ncol = min(BN, ep.N - nb * BN);
+                for (int c = 0; c * TC_CW < ncol; ++c) {
+                    const int k = c % TC_NSUB;
+                    const uint32_t jj = (k == 0) ? j[0]++ : (k == 1 ? j[1]++ : j[2]++);
+                    const int slot = k * naux + (int)(jj % (uint32_t)naux);
+                    tc::mbar_wait(&ctl->xempty[slot], ((jj / (uint32_t)naux) & 1) ^ 1);
+                    uint8_t* sp = ring_base + (size_t)slot * slot_bytes;
+                    tc::mbar_arrive_expect_tx(&ctl->xfull[slot], slot_bytes);
+                    tc::tma_load_2d(&mp.x[0], &ctl->xfull[slot], sp, nb * BN + c * TC_CW, mb * TC_BM);
+                    tc::tma_load_2d(&mp.x[1], &ctl->xfull[slot], sp + 4096, nb * BN + c * TC_CW, mb * TC_BM);
+                    if (TcRingOf<BWD, KIND>::f32)
+                        tc::tma_load_2d(&mp.x[2], &ctl->xfull[slot], sp + 8192, nb * BN + c * TC_CW, mb * TC_BM);
+                }
+            }
+        }
     } else {               // ===== epilogue warps
+        TcRing ring;
+        ring.base = ring_base; ring.j = 0; ring.d = naux; ring.zmask = (uint32_t)ep.dbg & 0x80000000u;
         const int quad = warp & 3;                    // TMEM lane quadrant this warp may access
         const int sub = (warp - TC_EPI_WARP0) >> 2;   // 0..2: which chunks of the quadrant's columns
         int it = 0;
@@ -541,13 +619,13 @@ k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, i
             {
                 const long long rloc = (long long)mb * TC_BM + quad * 32 + lane;
                 const int ng0 = nb * BN + sub * TC_CW;
-                if (sub * TC_CW < BN && ng0 < ep.N) tc_aux_load<PREC, BWD, KIND>(ep, rloc, ep.row0 + rloc, ng0, aux);
+                if (!RING && sub * TC_CW < BN && ng0 < ep.N) tc_aux_load<PREC, BWD, KIND>(ep, rloc, ep.row0 + rloc, ng0, aux);
             }
             tc::mbar_wait(&ctl->tfull[acc], (it >> 1) & 1);
             tc::tc_fence_after();
             const uint32_t tbase = tmem + ((uint32_t)(quad * 32) << 16) + (uint32_t)acc * 256;
-            if (BWD) tc_epilogue_bwd<KIND>(ep, ctl, tbase, mb, nb, BN, quad, sub, lane, it & 1, aux);
-            else tc_epilogue_fwd<PREC, KIND>(ep, ctl, tbase, mb, nb, BN, quad, sub, lane, it & 1, aux);
+            if (BWD) tc_epilogue_bwd<KIND, RING>(ep, ctl, tbase, mb, nb, BN, quad, sub, lane, it & 1, aux, ring);
+            else tc_epilogue_fwd<PREC, KIND, RING>(ep, ctl, tbase, mb, nb, BN, quad, sub, lane, it & 1, aux, ring);
             tc::tc_fence_before();
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(&ctl->tempty[acc]);
@@ -636,16 +714,17 @@ static PFN_encodeTiled tc_encode_fn() {
     return fn;
 }
 // 2D bf16 tensor [rows x cols] row-major (ld elements), box = [box_rows x 64 cols], SWIZZLE_128B
-static bool tc_make_map(CUtensorMap* m, const void* base, long long rows, long long cols, long long ld, int box_rows) {
+static bool tc_make_map(CUtensorMap* m, const void* base, long long rows, long long cols, long long ld, int box_rows,
+                        int box_cols = TC_BK) {
     PFN_encodeTiled fn = tc_encode_fn();
     if (!fn) return false;
     cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
     cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
-    cuuint32_t box[2] = {TC_BK, (cuuint32_t)box_rows};
+    cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
     cuuint32_t estr[2] = {1, 1};
     return fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
-              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+              CU_TENSOR_MAP_INTERLEAVE_NONE, box_cols == TC_BK ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+              CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
 static bool tc_make_map_f32(CUtensorMap* m, const void* base, long long rows, long long ld) {
@@ -653,7 +732,7 @@ static bool tc_make_map_f32(CUtensorMap* m, const void* base, long long rows, lo
     if (!fn) return false;
     cuuint64_t dims[2] = {(cuuint64_t)ld, (cuuint64_t)rows};
     cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
-    cuuint32_t box[2] = {32, TC_BM};
+    cuuint32_t box[2] = {TC_CW, TC_BM};
     cuuint32_t estr[2] = {1, 1};
     return fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims, strides, box, estr,
               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -667,15 +746,18 @@ struct TcPlane {
     int rows = 0, ld = 0;
     CUtensorMap map[2];    // box [box_rows x 64 cols]: K-major operand of the layer GEMMs
     CUtensorMap mapk[2];   // box [ 64 rows x 64 cols]: MN-major operand of the weight-gradient GEMMs
+    CUtensorMap mapx[2];   // box [128 rows x 16 cols], no swizzle: epilogue-operand ring
 };
 struct TcWeight {
     TcPlane ph, pb;   // half planes (forward solve), bfloat16 planes (reverse sweep); box rows = BN
     int N = 0, K = 0, BN = 0, n_tiles = 0;
+    int BN128 = 0, n_tiles128 = 0;   // RING kernels: tiles of at most 128 columns
+    CUtensorMap map128[2][2];        // [format][plane], box rows = BN128
 };
 struct TcF32 {
     float* p = nullptr;
     int rows = 0, ld = 0;
-    CUtensorMap map;   // box [128 rows x 32 cols], no swizzle: L2 prefetch only
+    CUtensorMap map;   // box [128 rows x 16 cols], no swizzle: epilogue-operand ring
 };
 struct TcState {
     int L = 0, Mc = 0;
@@ -704,7 +786,8 @@ static int tc_alloc_plane(cnf_handle* h, TcPlane& p, int rows, int ld, int box_r
         CNF_CUDA(cudaMalloc(&p.p[q], bytes));
         CNF_CUDA(cudaMemsetAsync(p.p[q], 0, bytes, h->stream));
         if (!tc_make_map(&p.map[q], p.p[q], rows, ld, ld, box_rows) ||
-            (kmap && !tc_make_map(&p.mapk[q], p.p[q], rows, ld, ld, 64))) {
+            (kmap && (!tc_make_map(&p.mapk[q], p.p[q], rows, ld, ld, 64) ||
+                      !tc_make_map(&p.mapx[q], p.p[q], rows, ld, ld, TC_BM, TC_CW)))) {
             h->err = "cuTensorMapEncodeTiled failed";
             return CNF_ERR_CUDA;
         }
@@ -762,6 +845,14 @@ static int tc_setup_weight(cnf_handle* h, TcWeight& w, const float* W, int dout,
         if ((rc = tc_alloc_plane(h, w.ph, rows, w.K, w.BN, false))) return rc;
         if ((rc = tc_alloc_plane(h, w.pb, rows, w.K, w.BN, false))) return rc;
     }
+    w.BN128 = n16 < 128 ? n16 : 128;
+    w.n_tiles128 = (n16 + w.BN128 - 1) / w.BN128;
+    for (int q = 0; q < 2; ++q)
+        if (!tc_make_map(&w.map128[0][q], w.ph.p[q], rows, w.K, w.K, w.BN128) ||
+            !tc_make_map(&w.map128[1][q], w.pb.p[q], rows, w.K, w.K, w.BN128)) {
+            h->err = "cuTensorMapEncodeTiled failed";
+            return CNF_ERR_CUDA;
+        }
     k_tc_weights<<<296, 256, 0, h->stream>>>(W, dout, din, w.ph.p[0], w.ph.p[1], w.pb.p[0], w.pb.p[1], rows, w.K, transpose);
     h->launches++;
     return CNF_OK;
@@ -823,48 +914,68 @@ static int tc_ensure_acts(cnf_handle* h, TcState* s, long long Bs) {
     return CNF_OK;
 }
 
-// one kernel instantiation per (format, epilogue kind): each carries only its own epilogue path
-template <int PREC, bool BWD, int KIND>
+// one kernel instantiation per (format, epilogue kind[, ring]): each carries only its own epilogue path
+template <int PREC, bool BWD, int KIND, bool RING>
 static void tc_launch_kind(cnf_handle* h, int grid, int smem, const TcMaps& mp, int m_tiles, int n_tiles, int BN, int nk,
-                           int nstage, const TcEpi& ep) {
-    constexpr bool valid = BWD ? (KIND >= TCB_FWD_LAST && PREC == 1) : (KIND <= TC_JVP_LAST && (PREC == 0 || KIND == TC_FWD_HIDDEN));
+                           int nstage, int naux, const TcEpi& ep) {
+    constexpr bool valid = (BWD ? (KIND >= TCB_FWD_LAST && PREC == 1) : (KIND <= TC_JVP_LAST && (PREC == 0 || KIND == TC_FWD_HIDDEN))) &&
+                           (!RING || TcRingOf<BWD, KIND>::kind);
     if constexpr (valid) {
         static bool attr = false;
         if (!attr) {
-            cudaFuncSetAttribute(k_tc_gemm<PREC, BWD, KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+            cudaFuncSetAttribute(k_tc_gemm<PREC, BWD, KIND, RING>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
             attr = true;
         }
-        k_tc_gemm<PREC, BWD, KIND><<<grid, TC_THREADS, smem, h->stream>>>(mp, m_tiles, n_tiles, BN, nk, nstage, ep);
+        k_tc_gemm<PREC, BWD, KIND, RING><<<grid, TC_THREADS, smem, h->stream>>>(mp, m_tiles, n_tiles, BN, nk, nstage, naux, ep);
     }
+}
+
+static bool tc_kind_has_ring(int kind) {
+    return kind == TC_BWD_HIDDEN || kind == TCB_BWD_HIDDEN || kind == TCB_GBAR_HIDDEN || kind == TCB_HBAR_HIDDEN;
 }
 
 template <int PREC, bool BWD>
 static void tc_launch_gemm(cnf_handle* h, TcState* s, const TcPlane& A, const TcWeight& B, int mc, const TcEpi& ep) {
-    const int BN = B.BN, n_tiles = B.n_tiles;
+    // RING kernels trade half of the tile width for a shared-memory ring of epilogue operands
+    bool ring = tc_kind_has_ring(ep.kind) && ep.aux_p && !h->tc_noring;
+    const bool f32kind = ep.kind == TCB_GBAR_HIDDEN || ep.kind == TCB_HBAR_HIDDEN;
+    if ((h->tc_dbg & 8) && f32kind) ring = false;
+    if ((h->tc_dbg & 16) && !f32kind) ring = false;
+    const int BN = ring ? B.BN128 : B.BN, n_tiles = ring ? B.n_tiles128 : B.n_tiles;
     const int m_tiles = mc / TC_BM;
     const int nk = B.K / TC_BK;
     const int stage_bytes = 2 * (TC_BM * 128 + BN * 128);
-    int nstage = (220 * 1024 - 1024) / stage_bytes;
-    if (nstage > 6) nstage = 6;
-    if (nstage < 2) nstage = 2;
-    const int smem = nstage * stage_bytes + 1024 + (int)sizeof(TcSmemCtl) + 64;
+    const int budget = 225 * 1024 - 2048 - (int)sizeof(TcSmemCtl);
+    int nstage, naux = 0, slot = 0;
+    if (ring) {
+        slot = (ep.kind == TCB_GBAR_HIDDEN || ep.kind == TCB_HBAR_HIDDEN) ? 16384 : 8192;
+        nstage = 2;
+        // slots per warp group; the row-reduction scratch at the end of TcSmemCtl is not used by these kinds
+        naux = (227 * 1024 - 1024 - 64 - (int)offsetof(TcSmemCtl, red) - nstage * stage_bytes) / (TC_NSUB * slot);
+        if (naux > 4) naux = 4;
+        if ((h->tc_dbg & 4) && naux > 1) naux = 1;
+    } else {
+        nstage = budget / stage_bytes;
+        if (nstage > 6) nstage = 6;
+        if (nstage < 2) nstage = 2;
+    }
+    const int smem = nstage * stage_bytes + TC_NSUB * naux * slot + 1024 + (ring ? (int)offsetof(TcSmemCtl, red) : (int)sizeof(TcSmemCtl)) + 64;
     int grid = m_tiles * n_tiles;
     if (grid > s->sms) grid = s->sms;
     const TcPlane& Bp = PREC == 0 ? B.ph : B.pb;
     TcMaps mp;
-    for (int q = 0; q < 2; ++q) { mp.a[q] = A.map[q]; mp.b[q] = Bp.map[q]; }
-    mp.nxp = mp.nxf = 0;
-    if (ep.aux_p && !h->tc_noprefetch) {
+    for (int q = 0; q < 2; ++q) { mp.a[q] = A.map[q]; mp.b[q] = ring ? B.map128[PREC][q] : Bp.map[q]; }
+    if (ring) {
         const TcPlane* xp = (const TcPlane*)ep.aux_p;
-        mp.x[0] = xp->map[0]; mp.x[1] = xp->map[1];
-        mp.nxp = 1;
-    }
-    if (ep.aux_f && !h->tc_noprefetch) {
-        mp.x[2] = ((const TcF32*)ep.aux_f)->map;
-        mp.nxf = 1;
+        mp.x[0] = xp->mapx[0]; mp.x[1] = xp->mapx[1];
+        if (ep.aux_f) mp.x[2] = ((const TcF32*)ep.aux_f)->map;
     }
     switch (ep.kind) {
-#define TC_CASE(K) case K: tc_launch_kind<PREC, BWD, K>(h, grid, smem, mp, m_tiles, n_tiles, BN, nk, nstage, ep); break;
+#define TC_CASE(K)                                                                                                  \
+    case K:                                                                                                         \
+        if (ring) tc_launch_kind<PREC, BWD, K, true>(h, grid, smem, mp, m_tiles, n_tiles, BN, nk, nstage, naux, ep);   \
+        else tc_launch_kind<PREC, BWD, K, false>(h, grid, smem, mp, m_tiles, n_tiles, BN, nk, nstage, naux, ep);       \
+        break;
         TC_CASE(TC_FWD_HIDDEN) TC_CASE(TC_FWD_LAST) TC_CASE(TC_BWD_HIDDEN) TC_CASE(TC_BWD_LAST) TC_CASE(TC_JVP_LAST)
         TC_CASE(TCB_FWD_LAST) TC_CASE(TCB_BWD_HIDDEN) TC_CASE(TCB_BWD_LAST) TC_CASE(TCB_GBAR_HIDDEN)
         TC_CASE(TCB_GBAR_LAST) TC_CASE(TCB_HBAR_HIDDEN) TC_CASE(TCB_ZBAR)
@@ -881,6 +992,7 @@ static TcEpi tc_base_epi(cnf_handle* h, TcState* s, const CnfBufs& bf, long long
     base.kout_ind = &s->dyn->kout;
     base.ctrl = check_done ? h->d_ctrl : nullptr;
     base.B = bf.B;
+    base.dbg = h->tc_dbg;
     return base;
 }
 
