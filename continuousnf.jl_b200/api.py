@@ -316,6 +316,8 @@ def _draw_eps(icnf, mode, B, like, eps):
         return _Mat(eps, icnf.D, "eps")
     if not isinstance(mode, TrainMode):
         return None
+    if getattr(icnf, "_device_rng", False):
+        return None   # drawn inside the library (seed_device_rng)
     e = icnf.rng.standard_normal((B, icnf.D), dtype=np.float32)
     m = _Mat.__new__(_Mat)
     m.torch, m.B, m.keep, m.ptr, m.device = False, B, e, e.ctypes.data, None
@@ -324,6 +326,25 @@ def _draw_eps(icnf, mode, B, like, eps):
         t = torch.from_numpy(e).to(like.device)
         m.torch, m.keep, m.ptr, m.device = True, t, t.data_ptr(), t.device
     return m
+
+
+def seed_device_rng(icnf, seed, sample_offset=0):
+    """from now on eps (TrainMode) and, in generate, z0 are drawn on the device
+    by the library's Philox stream instead of on the host from icnf.rng (src/base_icnf.jl:277-278,
+    365-372); `sample_offset` = first global column of this rank's shard."""
+    lib = _cabi.load()
+    rc = lib.cnfb200_seed_rng(icnf.handle(), int(seed), int(sample_offset))
+    icnf._check(rc, "cnfb200_seed_rng")
+    icnf._device_rng = True
+
+
+def last_eps(icnf, B):
+    """the D x B eps of the last TrainMode call (drawn on the device or passed in)"""
+    lib = _cabi.load()
+    out = np.empty((int(B), icnf.D), np.float32)
+    rc = lib.cnfb200_last_eps(icnf.handle(), out.ctypes.data, int(B))
+    icnf._check(rc, "cnfb200_last_eps")
+    return out.T
 
 
 def _split(args, cond, what):
@@ -370,15 +391,19 @@ def generate(icnf, mode, *args, eps=None, z0=None):
     lib = _cabi.load()
     h = _upload_params(icnf, ps)
     y = _Mat(ys, icnf._cfg.C, "ys") if icnf.cond else None
-    if z0 is None:
-        z0 = icnf.rng.standard_normal((n, icnf.D), dtype=np.float32).T
-    z = _Mat(z0, icnf.D, "z0")
-    e = _draw_eps(icnf, mode, z.B, z, eps)
+    if z0 is None and getattr(icnf, "_device_rng", False):
+        z, nB, like = None, int(n), y
+    else:
+        if z0 is None:
+            z0 = icnf.rng.standard_normal((n, icnf.D), dtype=np.float32).T
+        z = _Mat(z0, icnf.D, "z0")
+        nB, like = z.B, z
+    e = _draw_eps(icnf, mode, nB, like, eps)
     t0, t1 = steer_tspan(icnf, mode)
-    xo, xo_ptr = _out(icnf.nvars, z.B, z)
+    xo, xo_ptr = _out(icnf.nvars, nB, like)
     st_ = _cabi.CnfStats()
-    rc = lib.cnfb200_generate(h, mode.code, z.ptr, y.ptr if y else None, e.ptr if e else None,
-                              z.B, t1, t0, xo_ptr, C.byref(st_))
+    rc = lib.cnfb200_generate(h, mode.code, z.ptr if z else None, y.ptr if y else None, e.ptr if e else None,
+                              nB, t1, t0, xo_ptr, C.byref(st_))
     icnf._check(rc, "cnfb200_generate")
     icnf._last_stats = st_.as_dict()
     return _rows_view(xo)

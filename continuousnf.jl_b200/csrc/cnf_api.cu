@@ -467,14 +467,24 @@ static int load_problem(cnf_handle* h, const CnfBufs& bf, const IoPlan& io, int 
     int rc;
     float* slot0 = h->slots[0];
     CNF_CUDA(cudaMemsetAsync(slot0, 0, (size_t)R * bf.Bs * sizeof(float), h->stream));
-    if ((rc = stage_in(h, x, rows_x, B, slot0, bf.Bs, io.off_xs))) return rc;
+    if (x) {
+        if ((rc = stage_in(h, x, rows_x, B, slot0, bf.Bs, io.off_xs))) return rc;
+    } else {   // generate with z0 = NULL: the base sample is drawn here (N1)
+        if (!h->rng_on) { h->err = "null z0 and no device RNG seeded (cnfb200_seed_rng)"; return CNF_ERR_BADARG; }
+        launch_philox_normal(h, slot0, bf.Bs, B, rows_x, h->rng_draws++);
+    }
     if (c.C > 0) {
         if (!ys) { h->err = "conditional flow: ys is required"; return CNF_ERR_BADARG; }
         if ((rc = stage_in(h, ys, c.C, B, h->d_ys, bf.Bs, io.off_ys))) return rc;
     }
     if (mode == CNF_MODE_TRAIN) {
-        if (!eps) { h->err = "TrainMode: eps is required"; return CNF_ERR_BADARG; }
-        if ((rc = stage_in(h, eps, c.D, B, h->d_eps, bf.Bs, io.off_eps))) return rc;
+        if (eps) {
+            if ((rc = stage_in(h, eps, c.D, B, h->d_eps, bf.Bs, io.off_eps))) return rc;
+        } else {
+            if (!h->rng_on) { h->err = "TrainMode: eps is required (or seed the device RNG: cnfb200_seed_rng)"; return CNF_ERR_BADARG; }
+            launch_philox_normal(h, h->d_eps, bf.Bs, B, c.D, h->rng_draws++);
+        }
+        h->eps_B = B;
     }
     return CNF_OK;
 }
@@ -592,9 +602,38 @@ extern "C" int32_t cnfb200_generate(cnf_handle* h, int32_t mode, const float* z0
                                     const float* eps, int64_t n, float t_from, float t_to,
                                     float* xs_out, cnf_stats* stats) {
     if (!h) return CNF_ERR_BADARG;
-    if (!z0 || !xs_out) { h->err = "null z0/xs_out"; return CNF_ERR_BADARG; }
+    if (!xs_out) { h->err = "null xs_out"; return CNF_ERR_BADARG; }
+    if (!z0 && !h->rng_on) { h->err = "null z0 and no device RNG seeded (cnfb200_seed_rng)"; return CNF_ERR_BADARG; }
     return run_flow(h, mode, z0, h->cfg.D, ys, eps, n, t_from, t_to, nullptr, nullptr, xs_out,
                     -h->cfg.nvars, stats);
+}
+
+// ------------------------------------------------------------------ N1: device-side draws
+extern "C" int32_t cnfb200_seed_rng(cnf_handle* h, uint64_t seed, uint64_t sample_offset) {
+    if (!h) return CNF_ERR_BADARG;
+    h->rng_on = true;
+    h->rng_seed = seed;
+    h->rng_offset = sample_offset;
+    h->rng_draws = 0;
+    return CNF_OK;
+}
+
+extern "C" int32_t cnfb200_last_eps(cnf_handle* h, float* eps_out, int64_t B) {
+    if (!h || !eps_out) return CNF_ERR_BADARG;
+    if (B < 1 || B != h->eps_B || !h->d_eps) { h->err = "last_eps: no eps of that batch size on the device"; return CNF_ERR_BADARG; }
+    CNF_CUDA(cudaSetDevice(h->device));
+    const cnf_config& c = h->cfg;
+    const long long Bs = round_up(B, 256);
+    if (is_device_ptr(eps_out)) {
+        launch_unpack_rows(h, h->d_eps, c.D, B, Bs, eps_out);
+    } else {
+        int rc;
+        if ((rc = ensure_io(h, (long long)c.D * B))) return rc;
+        launch_unpack_rows(h, h->d_eps, c.D, B, Bs, h->d_io);
+        CNF_CUDA(cudaMemcpyAsync(eps_out, h->d_io, (size_t)c.D * B * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    }
+    CNF_CUDA(cudaStreamSynchronize(h->stream));
+    return CNF_OK;
 }
 
 // ------------------------------------------------------------------ loss + discrete adjoint

@@ -30,6 +30,11 @@ struct cnf_handle {
     float* d_K[7] = {};
     float* d_S = nullptr;
     float* d_eps = nullptr;
+    // N1: on-device eps / z0 (cnf_rng.cu)
+    bool rng_on = false;
+    unsigned long long rng_seed = 0, rng_offset = 0;
+    uint32_t rng_draws = 0;      // draws made so far (the next draw's index)
+    long long eps_B = 0;         // batch of the eps now in d_eps (cnfb200_last_eps)
     float* d_ys = nullptr;
     float* d_io = nullptr;      // staging for host<->device copies of sample-major I/O
     long long cap_io = 0;
@@ -73,6 +78,7 @@ void stage_timer_end(cnf_handle* h);
 
 // ---- cnf_solver.cu
 void cnf_upload_constants();
+void launch_philox_normal(cnf_handle* h, float* out, long long Bs, long long B, int rows, uint32_t draw);
 void launch_pack_rows(cnf_handle* h, const float* src, int rows, long long B, float* dst, long long Bs);
 void launch_unpack_rows(cnf_handle* h, const float* src, int rows, long long B, long long Bs, float* dst);
 void launch_combine(cnf_handle* h, const CnfBufs& bf, int stage, int also_S = 0);   // stage 1..5 -> S, 6 -> unew, -1 -> init probe

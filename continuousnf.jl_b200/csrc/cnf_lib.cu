@@ -6,5 +6,6 @@
 #include "cnf_stage_tc.cu"
 #include "cnf_backward_tc.cu"
 #include "cnf_backward.cu"
+#include "cnf_rng.cu"
 #include "cnf_nccl.cu"
 #include "cnf_api.cu"

@@ -142,11 +142,24 @@ CNF_API int32_t cnfb200_loss_grad_mode(cnf_handle* h, int32_t mode, const float*
                                float* grad_theta, float* grad_x, cnf_stats* stats);
 
 /* replaces generate(...) = generate_prob + generate_sol (src/base_icnf.jl:358-405, 202-211,
- * 447-466): integrates z0 (D x n, drawn by the caller from basedist) from t_from to t_to
- * and returns rows 1:nvars.  xs_out: nvars x n. */
+ * 447-466): integrates z0 (D x n, drawn by the caller from basedist; NULL = drawn on the device, see
+ * cnfb200_seed_rng) from t_from to t_to and returns rows 1:nvars.  xs_out: nvars x n. */
 CNF_API int32_t cnfb200_generate(cnf_handle* h, int32_t mode, const float* z0, const float* ys,
                          const float* eps, int64_t n, float t_from, float t_to,
                          float* xs_out, cnf_stats* stats);
+
+/* "next" row N1: draw the Hutchinson probe and the base sample on the device.  The reference draws
+ * both on the host once per call (randn!(rng, eps): src/base_icnf.jl:277-278, 367-372;
+ * rand(rng, basedist, n): :365-366) and the caller ships D x B floats.  After cnfb200_seed_rng a NULL
+ * `eps` (TrainMode calls) or NULL `z0` (cnfb200_generate) is drawn here: Philox4x32-10 keyed by
+ * `seed`, counter = (sample_offset + column, row group, draw index), Box-Muller; `sample_offset` is
+ * the first global column of this rank's shard, so a draw does not depend on the sharding.  Opt-in:
+ * the stream is reproducible against oracle/cnf_oracle.c (cnf_oracle_philox_normal), not against
+ * Julia's RNG.  Each drawn matrix consumes one draw index, starting from 0 after seeding. */
+CNF_API int32_t cnfb200_seed_rng(cnf_handle* h, uint64_t seed, uint64_t sample_offset);
+
+/* the eps (D x B, caller's layout) the last TrainMode call of batch B used, drawn or passed */
+CNF_API int32_t cnfb200_last_eps(cnf_handle* h, float* eps_out, int64_t B);
 
 /* measurement helper (bench only): sustained FP32 FFMA rate of this GPU in TFLOP/s,
  * the roofline denominator MEASURED_PEAKS.json does not provide. */

@@ -843,3 +843,46 @@ int32_t cnf_oracle_num_threads(void) {
     return 1;
 #endif
 }
+
+/* ---- "next" row N1: the generator behind cnfb200_seed_rng, restated on the CPU.
+ * Philox4x32-10 (Salmon, Moraes, Dror, Shaw: "Parallel random numbers: as easy as 1, 2, 3", SC'11;
+ * the Random123 known-answer vectors pin it in tests/test_oracle.py), counter =
+ * (lo32(sample), hi32(sample), row group, draw), key = (lo32(seed), hi32(seed)); 23-bit uniforms
+ * u = ((x >> 9) + 1/2) 2^-23 and Box-Muller pairs (x0, x1) -> rows 4g, 4g+1; (x2, x3) -> 4g+2, 4g+3.
+ * Replaces randn!(rng, eps) / rand(rng, basedist, n) of src/base_icnf.jl:277-278, 365-372 when the
+ * caller opts in; it is NOT Julia's stream. */
+void cnf_oracle_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]) {
+    uint32_t c0 = ctr[0], c1 = ctr[1], c2 = ctr[2], c3 = ctr[3], k0 = key[0], k1 = key[1];
+    for (int r = 0; r < 10; ++r) {
+        const uint64_t p0 = (uint64_t)0xD2511F53u * c0, p1 = (uint64_t)0xCD9E8D57u * c2;
+        const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0, n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1;
+        c1 = (uint32_t)p1; c3 = (uint32_t)p0; c0 = n0; c2 = n2;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+static float philox_u01(uint32_t x) { return ((float)(x >> 9) + 0.5f) * 1.1920928955078125e-07f; }
+
+/* out: B x rows, sample-major (the caller's D x B column-major layout) */
+void cnf_oracle_philox_normal(uint64_t seed, uint64_t sample_offset, uint32_t draw, int32_t rows, int64_t B, float* out) {
+    const uint32_t key[2] = {(uint32_t)seed, (uint32_t)(seed >> 32)};
+    const double two_pi = 6.283185307179586476925286766559;
+    for (int64_t b = 0; b < B; ++b) {
+        const uint64_t gs = (uint64_t)b + sample_offset;
+        for (int g = 0; 4 * g < rows; ++g) {
+            const uint32_t ctr[4] = {(uint32_t)gs, (uint32_t)(gs >> 32), (uint32_t)g, draw};
+            uint32_t x[4];
+            cnf_oracle_philox4x32_10(ctr, key, x);
+            float n[4];
+            for (int h = 0; h < 2; ++h) {
+                const float r = sqrtf(-2.0f * logf(philox_u01(x[2 * h])));
+                const double th = two_pi * (double)philox_u01(x[2 * h + 1]);
+                n[2 * h] = r * (float)cos(th);
+                n[2 * h + 1] = r * (float)sin(th);
+            }
+            for (int j = 0; j < 4; ++j)
+                if (4 * g + j < rows) out[b * rows + 4 * g + j] = n[j];
+        }
+    }
+}

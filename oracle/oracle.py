@@ -173,6 +173,23 @@ def loss_grad(cfg, theta, xs, ys=None, eps=None, t0=0.0, t1=1.0, want_grad=True,
     return loss.value, gth, gx, st.as_dict()
 
 
+def philox4x32_10(ctr, key):
+    """one Philox4x32-10 block (known-answer tests)"""
+    c = (C.c_uint32 * 4)(*ctr); k = (C.c_uint32 * 2)(*key); o = (C.c_uint32 * 4)()
+    lib().cnf_oracle_philox4x32_10(c, k, o)
+    return [int(v) for v in o]
+
+
+def philox_normal(seed, sample_offset, draw, rows, B):
+    """the matrix cnfb200_seed_rng's draw number `draw` produces: rows x B (column = sample)"""
+    out = np.empty((B, rows), np.float32)
+    f = lib().cnf_oracle_philox_normal
+    f.argtypes = [C.c_uint64, C.c_uint64, C.c_uint32, C.c_int32, C.c_int64, C.c_void_p]
+    f.restype = None
+    f(seed, sample_offset, draw, rows, B, out.ctypes.data)
+    return out.T
+
+
 def num_threads():
     return int(lib().cnf_oracle_num_threads())
 

@@ -201,3 +201,52 @@ def test_tensor_path_odd_shapes(nvars, naug, C, hidden, B):
         assert abs(out[1][0] - out[3][0]) / abs(out[1][0]) < 1e-4
         assert relnorm(out[3][1], out[1][1]) < 1e-3
         assert relnorm(out[3][2], out[1][2]) < 1e-3
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("cid,B", [("C3", 300), ("C0", 1024)])
+def test_n1_device_eps_matches_oracle_stream_and_host_eps_path(cid, B):
+    """N1: eps drawn on the device (Philox4x32-10 + Box-Muller) = the oracle's restatement of the
+    stream; a call with the drawn eps passed back from the host gives the same bits; the next call
+    uses the next draw; a shard with sample_offset reproduces its columns of the global draw."""
+    inp = wl.make_inputs(cid, B=B)
+    icnf = make_icnf(cid)
+    cnf.seed_device_rng(icnf, 4242)
+    v1, g1 = cnf.loss_and_grad(icnf, cnf.TrainMode(), inp["xs"].T, *args_of(inp))
+    e1 = np.array(cnf.last_eps(icnf, B))
+    ref = O.philox_normal(4242, 0, 0, icnf.D, B)
+    np.testing.assert_allclose(e1, ref, rtol=0, atol=3e-6)
+    v2, g2 = cnf.loss_and_grad(icnf, cnf.TrainMode(), inp["xs"].T, *args_of(inp))
+    e2 = np.array(cnf.last_eps(icnf, B))
+    np.testing.assert_allclose(e2, O.philox_normal(4242, 0, 1, icnf.D, B), rtol=0, atol=3e-6)
+    assert v1 != v2
+    host = make_icnf(cid)
+    v3, g3 = cnf.loss_and_grad(host, cnf.TrainMode(), inp["xs"].T, *args_of(inp), eps=e1)
+    assert v3 == v1
+    assert relnorm(np.asarray(g3), np.asarray(g1)) < 1e-5   # parameter gradients are accumulated with atomics
+    # against the oracle on the same eps
+    ov, og, _, ost = O.loss_grad(oracle_cfg(cid), inp["theta"], inp["xs"], inp["ys"], e1.T.copy(), *wl.CONFIGS[cid]["tspan"])
+    same = cnf.last_stats(host)["naccept"] == ost["naccept"]
+    assert abs(v1 - ov) <= (1e-4 if same else 5e-3) * abs(ov)
+    assert relnorm(np.asarray(g1), og) < (1e-3 if same else 5e-2)
+    # shard invariance
+    sh = make_icnf(cid)
+    cnf.seed_device_rng(sh, 4242, sample_offset=100)
+    cnf.loss_and_grad(sh, cnf.TrainMode(), inp["xs"].T[:, 100:228], *[a[:, 100:228] if getattr(a, "ndim", 0) == 2 and a.shape[1] == B else a for a in args_of(inp)])
+    np.testing.assert_array_equal(np.array(cnf.last_eps(sh, 128)), e1[:, 100:228])
+
+
+@pytest.mark.gpu
+def test_n1_generate_draws_base_sample_on_device():
+    """generate with z0 = None on a seeded handle: z0 is draw 0 of the stream, so passing the
+    oracle's draw as z0 to an unseeded handle must give (nearly) the same samples."""
+    cid, n = "C2", 2000
+    inp = wl.make_inputs(cid, B=n)
+    icnf = make_icnf(cid)
+    cnf.seed_device_rng(icnf, 7)
+    xs = np.array(cnf.generate(icnf, cnf.TestMode(), *args_of(inp), n))
+    z0 = O.philox_normal(7, 0, 0, icnf.D, n)
+    host = make_icnf(cid)
+    xs2 = np.array(cnf.generate(host, cnf.TestMode(), *args_of(inp), n, z0=z0))
+    assert xs.shape == (icnf.nvars, n)
+    np.testing.assert_allclose(xs, xs2, rtol=1e-4, atol=1e-4)   # z0 agrees to 3e-6; the flow amplifies it

@@ -195,3 +195,22 @@ def test_reverse_time_and_maxiters():
     cfg.maxiters = 3
     lp, _, _, st = O.logdensity(cfg, inp["theta"], 0, inp["xs"], None, None, 0.0, 13.0)
     assert st["retcode"] == 1 and st["naccept"] + st["nreject"] == 3
+
+
+def test_n1_philox_known_answers_and_normal_moments():
+    """N1: the generator behind cnfb200_seed_rng.  Known-answer vectors of Philox4x32-10 from the
+    Random123 distribution (kat_vectors: 'philox4x32 10 ...'); then the Box-Muller output is a
+    standard normal matrix whose draws / rows / samples are distinct streams."""
+    assert O.philox4x32_10([0, 0, 0, 0], [0, 0]) == [0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8]
+    assert O.philox4x32_10([0xffffffff] * 4, [0xffffffff] * 2) == [0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd]
+    assert O.philox4x32_10([0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344], [0xa4093822, 0x299f31d0]) == \
+        [0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1]
+    n = O.philox_normal(99, 0, 0, 6, 100000)
+    assert n.shape == (6, 100000) and np.isfinite(n).all()
+    assert abs(n.mean()) < 5e-3 and abs(n.std() - 1) < 5e-3 and abs((n ** 4).mean() - 3) < 5e-2
+    c = np.corrcoef(n)
+    assert np.abs(c - np.eye(6)).max() < 1.5e-2
+    # sharding: columns [b0, b0 + m) of the global draw = the shard's own draw with sample_offset = b0
+    np.testing.assert_array_equal(O.philox_normal(99, 1000, 0, 6, 500), n[:, 1000:1500])
+    assert not np.array_equal(O.philox_normal(99, 0, 1, 6, 500), n[:, :500])      # next draw
+    assert not np.array_equal(O.philox_normal(98, 0, 0, 6, 500), n[:, :500])      # other seed
