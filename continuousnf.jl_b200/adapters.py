@@ -59,7 +59,14 @@ def fit(model, verbosity, X, Y=None):
     bs = model.batch_size if model.use_batch else N
     t0 = time.perf_counter()
     history = []
+    device_loop = getattr(m, "_device_rng", False) and m.steer_rate == 0 and all(isinstance(o, Lion) and o.m is None for o in model.optimizers)
     for opt in model.optimizers:
+        if device_loop:   # N2: the whole epoch loop in one library call (steering is per call there)
+            perm = np.stack([m.rng.permutation(N) for _ in range(model.n_epochs)])
+            ps, hist = api.fit_epochs(m, x.T, y.T if model.cond else None, ps, batch_size=bs, n_epochs=model.n_epochs,
+                                      perm=perm, eta=opt.eta, beta=opt.beta)
+            history.extend(float(v) for v in hist)
+            continue
         for epoch in range(model.n_epochs):
             perm = m.rng.permutation(N)
             tot, cnt = 0.0, 0

@@ -347,6 +347,33 @@ def last_eps(icnf, B):
     return out.T
 
 
+def fit_epochs(icnf, X, Y, ps, *, batch_size, n_epochs, perm=None, eta=1e-3, beta=(0.9, 0.999)):
+    """`n_epochs` of the reference's fit loop (src/exts/mlj_ext/core_icnf.jl:30-90:
+    shuffled DataLoader, loss + gradient, Optimisers.Lion step per mini-batch) in one library call with
+    data, parameters and optimiser state resident on the device.  X: nvars x N (Y: C x N); perm:
+    (n_epochs, N) column indices or None (shuffled inside).  Needs seed_device_rng (eps is drawn on
+    the device).  Returns (ps, loss_history)."""
+    lib = _cabi.load()
+    h = _upload_params(icnf, ps)
+    x = _Mat(X, icnf.nvars, "X")
+    y = _Mat(Y, icnf._cfg.C, "Y") if icnf.cond else None
+    p = None
+    if perm is not None:
+        p = np.ascontiguousarray(perm, dtype=np.int64)
+        if p.shape != (n_epochs, x.B):
+            raise ValueError(f"perm must have shape ({n_epochs}, {x.B})")
+    t0, t1 = steer_tspan(icnf, TrainMode())
+    out = np.empty(param_offsets(icnf.dims)[2], np.float32)
+    hist = np.empty(n_epochs, np.float32)
+    st_ = _cabi.CnfStats()
+    rc = lib.cnfb200_fit_epochs(h, x.ptr, y.ptr if y else None, x.B, int(batch_size), int(n_epochs),
+                                p.ctypes.data if p is not None else None, t0, t1, float(eta), float(beta[0]),
+                                float(beta[1]), out.ctypes.data, hist.ctypes.data, C.byref(st_))
+    icnf._check(rc, "cnfb200_fit_epochs")
+    icnf._last_stats = st_.as_dict()
+    return out, hist
+
+
 def _split(args, cond, what):
     """(xs?, [ys,] ps, st) argument tails, like the Julia method pairs"""
     if cond:

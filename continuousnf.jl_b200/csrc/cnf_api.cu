@@ -121,6 +121,39 @@ __global__ void k_transpose_w(const float* __restrict__ W, int dout, int din, fl
     }
 }
 
+// every derived form of theta (transposed weights, the narrow kernels' packed copy, the tensor path's
+// hi/lo planes) from h->d_theta; `narrow` = also the narrow-path copy (needs a host round trip)
+static int refresh_params(cnf_handle* h, bool narrow) {
+    const cnf_config& c = h->cfg;
+    const long long n = h->nparams;
+    CnfNet& net = h->net;
+    net.L = c.n_layers; net.D = c.D; net.C = c.C;
+    net.flags = c.flags; net.trace_mode = c.trace_mode;
+    for (int l = 0; l <= c.n_layers; ++l) net.dims[l] = c.dims[l];
+    for (int l = 0; l < c.n_layers; ++l) {
+        net.W[l] = h->d_theta + h->w_off[l];
+        net.b[l] = h->d_theta + h->b_off[l];
+        net.Wt[l] = h->d_wt + h->wt_off[l];
+        net.w_off[l] = h->w_off[l];
+        net.b_off[l] = h->b_off[l];
+        long long wsz = (long long)c.dims[l] * c.dims[l + 1];
+        unsigned g = (unsigned)((wsz + 255) / 256);
+        if (g > 1184) g = 1184;
+        k_transpose_w<<<g, 256, 0, h->stream>>>(net.W[l], c.dims[l + 1], c.dims[l], h->d_wt + h->wt_off[l]);
+    }
+    CNF_CUDA(cudaGetLastError());
+    if (narrow && narrow_supported(c, CNF_MODE_TEST)) {
+        std::vector<float> th((size_t)n);
+        CNF_CUDA(cudaMemcpyAsync(th.data(), h->d_theta, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+        CNF_CUDA(cudaStreamSynchronize(h->stream));
+        narrow_set_params(h, th.data());
+    }
+    int rc = tc_set_params(h);
+    if (rc) return rc;
+    if (narrow) CNF_CUDA(cudaStreamSynchronize(h->stream));
+    return CNF_OK;
+}
+
 extern "C" int32_t cnfb200_set_params(cnf_handle* h, const float* theta, int64_t n,
                                       const int64_t* w_off, const int64_t* b_off) {
     if (!h || !theta || !w_off || !b_off || n <= 0) return CNF_ERR_BADARG;
@@ -147,32 +180,10 @@ extern "C" int32_t cnfb200_set_params(cnf_handle* h, const float* theta, int64_t
         h->nparams = n;
     }
     CNF_CUDA(cudaMemcpyAsync(h->d_theta, theta, n * sizeof(float), cudaMemcpyDefault, h->stream));
-    CnfNet& net = h->net;
-    net.L = c.n_layers; net.D = c.D; net.C = c.C;
-    net.flags = c.flags; net.trace_mode = c.trace_mode;
-    for (int l = 0; l <= c.n_layers; ++l) net.dims[l] = c.dims[l];
-    for (int l = 0; l < c.n_layers; ++l) {
-        net.W[l] = h->d_theta + h->w_off[l];
-        net.b[l] = h->d_theta + h->b_off[l];
-        net.Wt[l] = h->d_wt + h->wt_off[l];
-        net.w_off[l] = h->w_off[l];
-        net.b_off[l] = h->b_off[l];
-        long long wsz = (long long)c.dims[l] * c.dims[l + 1];
-        unsigned g = (unsigned)((wsz + 255) / 256);
-        if (g > 1184) g = 1184;
-        k_transpose_w<<<g, 256, 0, h->stream>>>(net.W[l], c.dims[l + 1], c.dims[l], h->d_wt + h->wt_off[l]);
-    }
-    CNF_CUDA(cudaGetLastError());
     CNF_CUDA(cudaStreamSynchronize(h->stream));  // theta may be a pageable host buffer
-    if (narrow_supported(c, CNF_MODE_TEST)) {
-        std::vector<float> th((size_t)n);
-        CNF_CUDA(cudaMemcpy(th.data(), h->d_theta, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost));
-        narrow_set_params(h, th.data());
-    }
     {
-        int rc = tc_set_params(h);
+        int rc = refresh_params(h, true);
         if (rc) return rc;
-        CNF_CUDA(cudaStreamSynchronize(h->stream));
     }
     h->have_params = true;
     return CNF_OK;
@@ -650,6 +661,26 @@ static int ensure_bw(cnf_handle* h, long long Bs) {
     return CNF_OK;
 }
 
+// the problem is loaded (slot 0, d_eps, d_ys): forward solve with the step tape, loss sum into
+// h->d_lossacc (all ranks), and — want_grad — the reverse sweep: grad theta (summed over ranks) in
+// h->d_grad, grad of the initial state in h->d_bw[11]
+static int loss_grad_core(cnf_handle* h, const CnfBufs& bf, int mode, int R, long long Bglobal, float t0, float t1,
+                          bool want_grad, CnfCtrl* fin) {
+    int rc;
+    h->path_used = 1;
+    if ((rc = solve_device(h, bf, mode, R, Bglobal, t0, t1, want_grad, fin))) return rc;
+    CNF_CUDA(cudaMemsetAsync(h->d_lossacc, 0, sizeof(double), h->stream));
+    launch_epilogue(h, bf, mode, nullptr, nullptr, nullptr, Bglobal);
+    if (h->nranks > 1 && (rc = cnf_nccl_allreduce_f64(h, h->d_lossacc, 1))) return rc;
+    if (want_grad) {
+        CNF_CUDA(cudaMemsetAsync(h->d_grad, 0, (size_t)h->nparams * sizeof(float), h->stream));
+        launch_init_ubar(h, bf, h->d_bw[11], Bglobal, mode);
+        if ((rc = backward_sweep(h, bf, mode, fin->naccept, Bglobal))) return rc;
+        if (h->nranks > 1 && (rc = cnf_nccl_allreduce_f32(h, h->d_grad, h->nparams))) return rc;
+    }
+    return CNF_OK;
+}
+
 extern "C" int32_t cnfb200_loss_grad_mode(cnf_handle* h, int32_t mode, const float* xs, const float* ys,
                                           const float* eps, int64_t B, float t0, float t1, float* loss,
                                           float* grad_theta, float* grad_x, cnf_stats* stats) {
@@ -671,20 +702,12 @@ extern "C" int32_t cnfb200_loss_grad_mode(cnf_handle* h, int32_t mode, const flo
     if (rc) return rc;
     CNF_CUDA(cudaEventRecord(h->ev0, h->stream));
     if ((rc = load_problem(h, bf, io, mode, R, xs, c.nvars, ys, eps, B))) return rc;
-    h->path_used = 1;
     CnfCtrl fin;
-    if ((rc = solve_device(h, bf, mode, R, Bglobal, t0, t1, want_grad, &fin))) return rc;
-    CNF_CUDA(cudaMemsetAsync(h->d_lossacc, 0, sizeof(double), h->stream));
-    launch_epilogue(h, bf, mode, nullptr, nullptr, nullptr, Bglobal);
-    if (h->nranks > 1 && (rc = cnf_nccl_allreduce_f64(h, h->d_lossacc, 1))) return rc;
+    if ((rc = loss_grad_core(h, bf, mode, R, Bglobal, t0, t1, want_grad, &fin))) return rc;
     double lsum = 0.0;
     CNF_CUDA(cudaMemcpyAsync(&lsum, h->d_lossacc, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     if (want_grad) {
-        CNF_CUDA(cudaMemsetAsync(h->d_grad, 0, (size_t)h->nparams * sizeof(float), h->stream));
-        launch_init_ubar(h, bf, h->d_bw[11], Bglobal, mode);
-        if ((rc = backward_sweep(h, bf, mode, fin.naccept, Bglobal))) return rc;
         if (grad_theta) {
-            if (h->nranks > 1 && (rc = cnf_nccl_allreduce_f32(h, h->d_grad, h->nparams))) return rc;
             CNF_CUDA(cudaMemcpyAsync(grad_theta, h->d_grad, (size_t)h->nparams * sizeof(float),
                                      cudaMemcpyDefault, h->stream));
         }

@@ -9,3 +9,4 @@
 #include "cnf_rng.cu"
 #include "cnf_nccl.cu"
 #include "cnf_api.cu"
+#include "cnf_fit.cu"

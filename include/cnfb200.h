@@ -161,6 +161,22 @@ CNF_API int32_t cnfb200_seed_rng(cnf_handle* h, uint64_t seed, uint64_t sample_o
 /* the eps (D x B, caller's layout) the last TrainMode call of batch B used, drawn or passed */
 CNF_API int32_t cnfb200_last_eps(cnf_handle* h, float* eps_out, int64_t B);
 
+/* "next" row N2: the caller's training loop (MLJModelInterface.fit, src/exts/mlj_ext/core_icnf.jl:30-90:
+ * DataLoader((x,); batchsize, shuffle = true, partial = true), `epochs = n_epochs` of loss + gradient +
+ * Optimisers.Lion step per mini-batch) as ONE call with data, theta, the Lion momentum and the loss
+ * history resident on the device.  X: nvars x N, Y: C x N (conditional flows, else NULL), column =
+ * sample, host or device.  perm: n_epochs x N 0-based column indices (epoch e visits
+ * perm[e*N .. e*N+N) in mini-batches of batch_size, the last one short), or NULL = shuffled by the
+ * library.  eps is drawn per mini-batch by the device stream (cnfb200_seed_rng is required), draw
+ * index advancing by one per mini-batch.  Starts from the theta of cnfb200_set_params; Lion:
+ * theta -= eta*sign(beta1*m + (1-beta1)*g), m = beta2*m + (1-beta2)*g, m0 = 0.  theta_out: nparams
+ * (may be NULL; the handle keeps the fitted theta either way); loss_history: n_epochs per-epoch means
+ * of the mini-batch losses weighted by their sizes.  With several ranks every rank passes its own
+ * shard (same number of mini-batches per epoch on every rank). */
+CNF_API int32_t cnfb200_fit_epochs(cnf_handle* h, const float* X, const float* Y, int64_t N, int64_t batch_size,
+                           int32_t n_epochs, const int64_t* perm, float t0, float t1, float eta, float beta1,
+                           float beta2, float* theta_out, float* loss_history, cnf_stats* stats);
+
 /* measurement helper (bench only): sustained FP32 FFMA rate of this GPU in TFLOP/s,
  * the roofline denominator MEASURED_PEAKS.json does not provide. */
 CNF_API int32_t cnfb200_measure_fp32_peak(int32_t device, double* tflops_out);

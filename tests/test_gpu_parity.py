@@ -250,3 +250,71 @@ def test_n1_generate_draws_base_sample_on_device():
     xs2 = np.array(cnf.generate(host, cnf.TestMode(), *args_of(inp), n, z0=z0))
     assert xs.shape == (icnf.nvars, n)
     np.testing.assert_allclose(xs, xs2, rtol=1e-4, atol=1e-4)   # z0 agrees to 3e-6; the flow amplifies it
+
+
+def _oracle_fit(cid, inp, N, bs, n_epochs, perm, seed, eta, beta):
+    """the reference's fit loop restated on the host with the oracle's loss gradient, the oracle's
+    Philox eps stream (one draw per mini-batch) and Lion (tests only)"""
+    cfg, c = oracle_cfg(cid), wl.CONFIGS[cid]
+    ps = inp["theta"].copy()
+    m = np.zeros_like(ps)
+    D = c["nvars"] + c["naug"]
+    hist, draw = [], 0
+    for e in range(n_epochs):
+        tot = 0.0
+        for lo in range(0, N, bs):
+            idx = perm[e, lo:lo + bs]
+            eps = O.philox_normal(seed, 0, draw, D, len(idx)).T.copy()
+            draw += 1
+            ys = inp["ys"][idx] if inp["ys"] is not None else None
+            val, g, _, _ = O.loss_grad(cfg, ps, inp["xs"][idx], ys, eps, *c["tspan"])
+            cc = beta[0] * m + (1 - beta[0]) * g
+            ps = (ps - eta * np.sign(cc)).astype(np.float32)
+            m = (beta[1] * m + (1 - beta[1]) * g).astype(np.float32)
+            tot += val * len(idx)
+        hist.append(tot / N)
+    return ps, np.array(hist)
+
+
+@pytest.mark.parametrize("cid,N,bs,n_epochs", [("C1", 300, 128, 2), ("C4", 512, 256, 2), ("C3", 384, 128, 1)])
+def test_n2_fit_epochs_device_loop_vs_oracle_loop(cid, N, bs, n_epochs):
+    """N2: the device-resident epoch loop (gather, device eps, loss+grad, Lion) against the same loop
+    on the host with the oracle's gradients: per-epoch losses to 1e-4; parameters equal except where
+    a Lion sign flips on a near-zero momentum (each flip moves a coordinate by 2 eta)."""
+    inp = wl.make_inputs(cid, B=N)
+    eta, beta, seed = 1e-3, (0.9, 0.999), 31337
+    perm = np.stack([np.random.default_rng(5 + e).permutation(N) for e in range(n_epochs)])
+    icnf = make_icnf(cid)
+    cnf.seed_device_rng(icnf, seed)
+    ys = inp["ys"].T if inp["ys"] is not None else None
+    ps, hist = cnf.fit_epochs(icnf, inp["xs"].T, ys, inp["theta"], batch_size=bs, n_epochs=n_epochs, perm=perm,
+                              eta=eta, beta=beta)
+    rps, rhist = _oracle_fit(cid, inp, N, bs, n_epochs, perm, seed, eta, beta)
+    steps = n_epochs * -(-N // bs)
+    np.testing.assert_allclose(hist, rhist, rtol=2e-4)
+    d = np.abs(ps - rps)
+    assert d.max() <= 2 * eta * steps + 1e-6
+    assert (d > 1e-6).mean() < 0.03, (d > 1e-6).mean()
+    # the fitted parameters stay in the handle: a loss call without re-uploading sees them
+    assert not np.array_equal(ps, inp["theta"])
+
+
+def test_n2_adapter_fit_uses_device_loop_and_matches_per_batch_calls():
+    """fit(ICNFModel) with a seeded device stream runs the one-call loop; the same model fitted
+    through per-mini-batch loss_and_grad calls (same permutations, same device eps draws) agrees."""
+    rng = np.random.default_rng(3)
+    X = rng.beta(2.0, 4.0, size=(256, 1)).astype(np.float32)
+    def mk():
+        nn = cnf.Chain(cnf.Dense(1, 8, "tanh"), cnf.Dense(8, 1, "tanh"))
+        return cnf.construct(cnf.RNODE, nn, 1, 0, tspan=(0.0, 4.0), resource=cnf.B200Libs(0), rng=np.random.default_rng(11))
+    a, b = mk(), mk()
+    cnf.seed_device_rng(a, 77)
+    cnf.seed_device_rng(b, 77)
+    ma = cnf.ICNFModel(a, n_epochs=2, batch_size=64)
+    (psa, _), _, ra = cnf.fit(ma, 0, X)
+    mb = cnf.ICNFModel(b, n_epochs=2, batch_size=64, optimizers=(cnf.Lion(),))
+    mb.optimizers[0].m = np.zeros_like(psa)      # a used optimiser state forces the per-batch path
+    (psb, _), _, rb = cnf.fit(mb, 0, X)
+    np.testing.assert_allclose(ra["loss_history"], rb["loss_history"], rtol=1e-4)
+    d = np.abs(psa - psb)
+    assert d.max() <= 2e-3 * 8 + 1e-6 and (d > 1e-6).mean() < 0.05
