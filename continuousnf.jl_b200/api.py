@@ -45,11 +45,15 @@ class DIJacVecMatrixMode(ComputeMode):
 
 
 class DIVecJacVectorMode(ComputeMode):
-    trace_mode = None  # one-sample path: out of scope, rejected by construct
+    """VectorMode: every sample its own adaptive solve.  Built for TestMode on
+    the narrow 3-layer shapes; anything else raises inside the library."""
+    trace_mode = _cabi.TRACE_VJP
+    vector = True
 
 
 class DIJacVecVectorMode(ComputeMode):
-    trace_mode = None
+    trace_mode = _cabi.TRACE_JVP
+    vector = True
 
 
 class AbstractICNF:
@@ -181,6 +185,8 @@ class ICNF:
                     lib.cnfb200_destroy(self._handle)
                     self._handle = C.c_void_p()
                 raise _cabi.CnfError(f"cnfb200_create: {msg} (rc={rc})")
+            if getattr(self.compute_mode, "vector", False):
+                lib.cnfb200_set_option(self._handle, b"vector_mode", 1)
         return self._handle
 
     def _check(self, rc, what):
@@ -208,7 +214,7 @@ def construct(aicnf, nn, nvars, naugmented=0, *, data_type=np.float32, compute_m
         raise ValueError("B200Libs path is Float32 only")
     compute_mode = DIVecJacMatrixMode() if compute_mode is None else compute_mode
     if getattr(compute_mode, "trace_mode", None) is None:
-        raise ValueError("B200Libs path supports DIVecJacMatrixMode / DIJacVecMatrixMode only")
+        raise ValueError("B200Libs path: compute_mode must be one of the DI*MatrixMode / DI*VectorMode classes")
     if basedist is not None or epsdist is not None:
         raise ValueError("B200Libs path: basedist/epsdist must be the default MvNormal(0, I)")
     resource = B200Libs() if resource is None else resource

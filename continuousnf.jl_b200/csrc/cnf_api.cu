@@ -142,7 +142,7 @@ static int refresh_params(cnf_handle* h, bool narrow) {
         k_transpose_w<<<g, 256, 0, h->stream>>>(net.W[l], c.dims[l + 1], c.dims[l], h->d_wt + h->wt_off[l]);
     }
     CNF_CUDA(cudaGetLastError());
-    if (narrow && narrow_supported(c, CNF_MODE_TEST)) {
+    if (narrow && narrow_shape(c)) {
         std::vector<float> th((size_t)n);
         CNF_CUDA(cudaMemcpyAsync(th.data(), h->d_theta, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
         CNF_CUDA(cudaStreamSynchronize(h->stream));
@@ -218,6 +218,7 @@ extern "C" int32_t cnfb200_set_option(cnf_handle* h, const char* key, int64_t va
     if (!h || !key) return CNF_ERR_BADARG;
     if (!strcmp(key, "time_stages")) { h->time_stages = value != 0; return CNF_OK; }
     if (!strcmp(key, "kernel_path")) { h->cfg.kernel_path = (int32_t)value; return CNF_OK; }
+    if (!strcmp(key, "vector_mode")) { h->vector_mode = value != 0; return CNF_OK; }
     if (!strcmp(key, "tc_dbg")) { h->tc_dbg = (int)value; return CNF_OK; }
     if (!strcmp(key, "tc_ring")) { h->tc_noring = value == 0; return CNF_OK; }
     if (!strcmp(key, "tc_backward")) { h->tc_bw_off = value == 0; return CNF_OK; }
@@ -570,7 +571,10 @@ static int run_flow(cnf_handle* h, int mode, const float* x, int rows_x, const f
     if ((rc = load_problem(h, bf, io, mode, R, x, rows_x, ys, eps, B))) return rc;
     h->path_used = 1;
     CnfCtrl fin;
-    if ((rc = solve_device(h, bf, mode, R, Bglobal, t0, t1, false, &fin))) return rc;
+    if (h->vector_mode) {   // N4: every sample its own adaptive solve (no cross-sample coupling, no allreduce)
+        if (mode != CNF_MODE_TEST) { h->err = "vector mode: TestMode only"; return CNF_ERR_UNSUPPORTED; }
+        if ((rc = vector_solve(h, bf, t0, t1, &fin))) return rc;
+    } else if ((rc = solve_device(h, bf, mode, R, Bglobal, t0, t1, false, &fin))) return rc;
     // epilogue writes in the caller's layout; host destinations go through the staging area
     const int nreg = mode == CNF_MODE_TRAIN ? 3 : 1;
     float* d_logp = logp ? (is_device_ptr(logp) ? logp : h->d_io + io.off_logp) : nullptr;
@@ -597,6 +601,7 @@ static int run_flow(cnf_handle* h, int mode, const float* x, int rows_x, const f
     CNF_CUDA(cudaEventRecord(h->ev3, h->stream));
     CNF_CUDA(cudaStreamSynchronize(h->stream));
     CNF_CUDA(cudaGetLastError());
+    if (h->vector_mode) fin.naccept = fin.iter;   // reported: the maxima over the samples
     fill_stats(h, fin, stats);
     return fin.retcode;
 }

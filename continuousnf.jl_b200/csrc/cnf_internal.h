@@ -31,6 +31,7 @@ struct cnf_handle {
     float* d_S = nullptr;
     float* d_eps = nullptr;
     // N1: on-device eps / z0 (cnf_rng.cu)
+    bool vector_mode = false;    // N4: per-sample step control (cnf_vector.cu)
     bool rng_on = false;
     unsigned long long rng_seed = 0, rng_offset = 0;
     uint32_t rng_draws = 0;      // draws made so far (the next draw's index)
@@ -78,6 +79,8 @@ void stage_timer_end(cnf_handle* h);
 
 // ---- cnf_solver.cu
 void cnf_upload_constants();
+bool narrow_shape(const cnf_config& c);
+int vector_solve(cnf_handle* h, const CnfBufs& bf, float t0, float t1, CnfCtrl* out);
 void launch_philox_normal(cnf_handle* h, float* out, long long Bs, long long B, int rows, uint32_t draw);
 void launch_pack_rows(cnf_handle* h, const float* src, int rows, long long B, float* dst, long long Bs);
 void launch_unpack_rows(cnf_handle* h, const float* src, int rows, long long B, long long Bs, float* dst);

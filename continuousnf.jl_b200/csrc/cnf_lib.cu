@@ -3,6 +3,7 @@
 #include "cnf_solver.cu"
 #include "cnf_stage_generic.cu"
 #include "cnf_stage_narrow.cu"
+#include "cnf_vector.cu"
 #include "cnf_stage_tc.cu"
 #include "cnf_backward_tc.cu"
 #include "cnf_backward.cu"

@@ -40,43 +40,11 @@ struct NarrowLayout {
     static_assert(TOTAL <= NARROW_MAXW, "network too large for the kernel-parameter path");
 };
 
-// stage: 0 k1 = f(u0) [init]; -1 init probe f(u0 + tdir*dt0init*k1) -> K[1]; 1..5 -> K[stage];
-// 6 -> new state, k7 and the error partial sum.
+// f(z) of the 3-layer Dense/tanh chain with its exact Jacobian trace, all in registers:
+// y = zdot, tr = -tr(J) (D one-hot tangents pushed forward with the activations).
 template <int D, int H1, int H2>
-__global__ void __launch_bounds__(256, 1)
-k_stage_narrow_test_jvp(const __grid_constant__ NarrowW p, CnfCtrl* __restrict__ c, CnfBufs bf,
-                        int stage, int check_done) {
+__device__ __forceinline__ void narrow_f(const NarrowW& p, const float (&z)[D], float (&y)[D], float& tr) {
     using LY = NarrowLayout<D, H1, H2>;
-    if (check_done && c->done) return;
-    constexpr int R = D + 1;
-    const long long Bs = bf.Bs;
-    const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    const bool live = b < bf.B;
-    const float* u = bf.slots[cnf_slot(c, stage <= 0 ? (stage == 0 ? 0 : 0) : c->naccept)];
-    const float* k1 = bf.K[c->k1idx];
-    float* kout = (stage == 0) ? bf.K[c->k1idx] : (stage == -1 ? bf.K[1] : (stage == 6 ? bf.K[6 - c->k1idx] : bf.K[stage]));
-    const float dt = c->dt;
-    // ---- stage input
-    float z[D];
-    if (stage == 0) {
-#pragma unroll
-        for (int i = 0; i < D; ++i) z[i] = u[(long long)i * Bs + b];
-    } else if (stage == -1) {
-        const float hh = c->tdir * c->dt0init;
-#pragma unroll
-        for (int i = 0; i < D; ++i) z[i] = fmaf(hh, k1[(long long)i * Bs + b], u[(long long)i * Bs + b]);
-    } else {
-        float* unew = bf.slots[cnf_slot(c, c->naccept + 1)];
-        const int nrow = (stage == 6) ? R : D;
-        for (int r = 0; r < nrow; ++r) {   // rows D.. only at the 7th stage (pure quadrature rows)
-            const long long at = (long long)r * Bs + b;
-            float acc = c_A[stage][0] * k1[at];
-            for (int j = 1; j < stage; ++j) acc = fmaf(c_A[stage][j], bf.K[j][at], acc);
-            float v = fmaf(dt, acc, u[at]);
-            if (stage == 6) unew[at] = v;
-            if (r < D) z[r] = v;
-        }
-    }
     // ---- layer 1 and the D one-hot tangents tau1_v = W1[:,v] .* (1 - h1^2)
     float h1[H1], t1[D][H1];
 #pragma unroll
@@ -133,14 +101,56 @@ k_stage_narrow_test_jvp(const __grid_constant__ NarrowW p, CnfCtrl* __restrict__
             }
         }
     }
-    // ---- outputs: zdot rows and -tr(J)
-    float y[D], tr = 0.0f;
+    tr = 0.0f;
 #pragma unroll
     for (int j = 0; j < D; ++j) {
         y[j] = cnf_tanh_fastpath(p3[j]);
         tr -= fmaf(-y[j], y[j], 1.0f) * r3[j][j];
-        kout[(long long)j * Bs + b] = y[j];
     }
+}
+
+// stage: 0 k1 = f(u0) [init]; -1 init probe f(u0 + tdir*dt0init*k1) -> K[1]; 1..5 -> K[stage];
+// 6 -> new state, k7 and the error partial sum.
+template <int D, int H1, int H2>
+__global__ void __launch_bounds__(256, 1)
+k_stage_narrow_test_jvp(const __grid_constant__ NarrowW p, CnfCtrl* __restrict__ c, CnfBufs bf,
+                        int stage, int check_done) {
+    using LY = NarrowLayout<D, H1, H2>;
+    if (check_done && c->done) return;
+    constexpr int R = D + 1;
+    const long long Bs = bf.Bs;
+    const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool live = b < bf.B;
+    const float* u = bf.slots[cnf_slot(c, stage <= 0 ? (stage == 0 ? 0 : 0) : c->naccept)];
+    const float* k1 = bf.K[c->k1idx];
+    float* kout = (stage == 0) ? bf.K[c->k1idx] : (stage == -1 ? bf.K[1] : (stage == 6 ? bf.K[6 - c->k1idx] : bf.K[stage]));
+    const float dt = c->dt;
+    // ---- stage input
+    float z[D];
+    if (stage == 0) {
+#pragma unroll
+        for (int i = 0; i < D; ++i) z[i] = u[(long long)i * Bs + b];
+    } else if (stage == -1) {
+        const float hh = c->tdir * c->dt0init;
+#pragma unroll
+        for (int i = 0; i < D; ++i) z[i] = fmaf(hh, k1[(long long)i * Bs + b], u[(long long)i * Bs + b]);
+    } else {
+        float* unew = bf.slots[cnf_slot(c, c->naccept + 1)];
+        const int nrow = (stage == 6) ? R : D;
+        for (int r = 0; r < nrow; ++r) {   // rows D.. only at the 7th stage (pure quadrature rows)
+            const long long at = (long long)r * Bs + b;
+            float acc = c_A[stage][0] * k1[at];
+            for (int j = 1; j < stage; ++j) acc = fmaf(c_A[stage][j], bf.K[j][at], acc);
+            float v = fmaf(dt, acc, u[at]);
+            if (stage == 6) unew[at] = v;
+            if (r < D) z[r] = v;
+        }
+    }
+    // ---- zdot and -tr(J) in registers
+    float y[D], tr;
+    narrow_f<D, H1, H2>(p, z, y, tr);
+#pragma unroll
+    for (int j = 0; j < D; ++j) kout[(long long)j * Bs + b] = y[j];
     kout[(long long)D * Bs + b] = tr;
     if (stage != 6) return;
     // ---- 7th stage: embedded error partial sum over this thread's R elements
@@ -217,6 +227,8 @@ static const NarrowEntry* narrow_find(const cnf_config& c) {
 bool narrow_supported(const cnf_config& c, int mode) {
     return mode == CNF_MODE_TEST && c.trace_mode == CNF_TRACE_JVP && narrow_find(c) != nullptr;
 }
+
+bool narrow_shape(const cnf_config& c) { return narrow_find(c) != nullptr; }
 
 // called from set_params with a host copy of theta
 void narrow_set_params(cnf_handle* h, const float* theta_host) {

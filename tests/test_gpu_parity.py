@@ -318,3 +318,57 @@ def test_n2_adapter_fit_uses_device_loop_and_matches_per_batch_calls():
     np.testing.assert_allclose(ra["loss_history"], rb["loss_history"], rtol=1e-4)
     d = np.abs(psa - psb)
     assert d.max() <= 2e-3 * 8 + 1e-6 and (d > 1e-6).mean() < 0.05
+
+
+def _vector_icnf(cid, mode_cls):
+    c = wl.CONFIGS[cid]
+    dims = c["dims"]
+    nn = cnf.Chain(*[cnf.Dense(dims[i], dims[i + 1], "tanh") for i in range(len(dims) - 1)])
+    return cnf.construct(cnf.FFJORD, nn, c["nvars"], c["naug"], compute_mode=mode_cls(), tspan=c["tspan"],
+                         resource=cnf.B200Libs(0), rng=np.random.default_rng(1))
+
+
+@pytest.mark.parametrize("mode_cls", ["DIJacVecVectorMode", "DIVecJacVectorMode"])
+def test_n4_vector_mode_matches_per_sample_oracle_solves(mode_cls):
+    """N4: VectorMode = every column its own adaptive solve (own dt, own error norm over its R
+    entries).  Oracle: the CPU solve called once per column with B = 1.  logp to 1e-4, z to 1e-4,
+    the largest accepted-step count within 1; and the whole batch is one kernel launch."""
+    cid, B = "C2", 333
+    inp = wl.make_inputs(cid, B=B)
+    c = wl.CONFIGS[cid]
+    icnf = _vector_icnf(cid, getattr(cnf, mode_cls))
+    lp, regs, z = cnf.inference(icnf, cnf.TestMode(), inp["xs"].T, *args_of(inp), return_z=True)
+    st = cnf.last_stats(icnf)
+    lp, z = np.asarray(lp), np.asarray(z).T
+    cfg = oracle_cfg(cid)
+    rlp, rz, nacc = np.empty(B, np.float32), np.empty_like(z), []
+    for b in range(B):
+        out = O.logdensity(cfg, inp["theta"], 0, inp["xs"][b:b + 1], None, None, *c["tspan"])
+        rlp[b], rz[b] = out[0][0], out[2][0]
+        nacc.append(out[-1]["naccept"])
+    assert np.max(np.abs(lp - rlp) / np.maximum(1.0, np.abs(rlp))) < 1e-4
+    assert np.max(np.abs(z - rz)) < 1e-4
+    assert abs(st["naccept"] - max(nacc)) <= 1, (st, max(nacc))
+    assert len(set(nacc)) > 1          # the samples really take different numbers of steps
+    assert st["kernel_path"] == 4 and st["gpu_launches"] <= 4
+    # MatrixMode on the same data couples the columns through one error norm: a different answer
+    mat = make_icnf(cid)
+    lpm, _ = cnf.inference(mat, cnf.TestMode(), inp["xs"].T, *args_of(inp))
+    assert np.max(np.abs(np.asarray(lpm) - lp)) > 0
+    assert np.max(np.abs(np.asarray(lpm) - lp)) < 5e-2
+
+
+def test_n4_vector_mode_generate_roundtrip_and_unsupported_shapes():
+    cid, B = "C2", 500
+    inp = wl.make_inputs(cid, B=B)
+    icnf = _vector_icnf(cid, cnf.DIJacVecVectorMode)
+    m = cnf.TestMode()
+    lp, regs, z = cnf.inference(icnf, m, inp["xs"].T, *args_of(inp), return_z=True)
+    xr = np.asarray(cnf.generate(icnf, m, *args_of(inp), B, z0=np.asarray(z))).T
+    assert np.max(np.abs(xr - inp["xs"])) < 2e-2
+    with pytest.raises(cnf._cabi.CnfError):      # TrainMode has no vector kernel
+        cnf.inference(icnf, cnf.TrainMode(), inp["xs"].T, *args_of(inp))
+    wide = _vector_icnf("C3", cnf.DIJacVecVectorMode)
+    i3 = wl.make_inputs("C3", B=8)
+    with pytest.raises(cnf._cabi.CnfError):      # not a narrow shape
+        cnf.inference(wide, m, i3["xs"].T, *args_of(i3))

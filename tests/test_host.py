@@ -35,7 +35,7 @@ def test_unsupported_combinations_raise():
     with pytest.raises(ValueError):
         cnf.construct(cnf.RNODE, chain(2, 2), 2, data_type=np.float64)
     with pytest.raises(ValueError):
-        cnf.construct(cnf.RNODE, chain(2, 2), 2, compute_mode=cnf.DIVecJacVectorMode())
+        cnf.construct(cnf.RNODE, chain(2, 2), 2, compute_mode=object())
     with pytest.raises(ValueError):
         cnf.construct(cnf.RNODE, chain(2, 2), 2, resource=object())
     with pytest.raises(ValueError):
