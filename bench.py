@@ -41,6 +41,8 @@ def parse():
     p.add_argument("--batch", type=int, default=0, help="override the per-GPU batch (debug)")
     p.add_argument("--impl", default="b200", choices=["b200", "reference"])
     p.add_argument("--kernel-path", type=int, default=0)
+    p.add_argument("--compute-mode", default="matrix", choices=["matrix", "vector"],
+                   help="vector = per-sample step control (row N4; TestMode configs on narrow shapes)")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--cpu-sample", type=int, default=0)
     return p.parse_args()
@@ -91,11 +93,13 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-def make_model(cnf, cid, device, kernel_path):
+def make_model(cnf, cid, device, kernel_path, vector=False):
     c = cnf.workloads.CONFIGS[cid]
     dims = c["dims"]
     nn = cnf.Chain(*[cnf.Dense(dims[i], dims[i + 1], "tanh") for i in range(len(dims) - 1)])
     cm = cnf.DIJacVecMatrixMode() if c["trace_mode"] == 1 else cnf.DIVecJacMatrixMode()
+    if vector:
+        cm = cnf.DIJacVecVectorMode() if c["trace_mode"] == 1 else cnf.DIVecJacVectorMode()
     tag = {"RNODE": cnf.RNODE, "ICNF": cnf.FFJORD, "CondRNODE": cnf.CondRNODE}[c["tag"]]
     sk = {k: c[k] for k in ("reltol", "abstol") if c[k]}
     return cnf.construct(tag, nn, c["nvars"], c["naug"], compute_mode=cm, tspan=c["tspan"],
@@ -185,7 +189,7 @@ def main():
     B = args.batch or c["B"]
     D = c["nvars"] + c["naug"]
     inp = wl.make_inputs(cid, B=B, offset=rank)
-    icnf = make_model(cnf, cid, local, args.kernel_path)
+    icnf = make_model(cnf, cid, local, args.kernel_path, args.compute_mode == "vector")
     if world > 1:
         cnf.parallel.init_comm(icnf, rank, world)
     cnf.set_option(icnf, "time_stages", 1)
@@ -221,7 +225,7 @@ def main():
     sampler = ClockSampler(local)
     barrier()
     sampler.start()
-    ms_dev = ms_stage = 0.0
+    ms_dev = ms_stage = ms_solve = 0.0
     n_stage = launches = 0
     t_wall = time.perf_counter()
     for _ in range(args.steps):
@@ -230,6 +234,7 @@ def main():
         _, st = step(xs_d, ys_d, eps_d)
         ms_dev += st["ms_total"]
         ms_stage += st["ms_stage"]
+        ms_solve += st["ms_solve"]
         n_stage += st["n_stage"]
         launches += st["gpu_launches"]
     barrier()
@@ -271,7 +276,20 @@ def main():
         traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(f"{cid}:path{st['kernel_path']}")
     except (OSError, ValueError):
         pass
-    if st["kernel_path"] == 3:
+    if st["kernel_path"] == 4:
+        # vector mode: the whole adaptive solve of every sample is ONE kernel; a warp runs as long as its slowest lane,
+        # so the executed work is nf_max evaluations per lane
+        solve_ms = ms_solve / args.steps
+        achieved = flops_eval * st["nf"] / (solve_ms * 1e-3) / 1e12 if solve_ms > 0 else 0.0
+        roofline = {"bound": "fp32_fma", "achieved": achieved, "peak": pk.value, "unit": "TFLOP/s",
+                    "frac": achieved / pk.value if pk.value else None, "traffic": traffic,
+                    "kernel": "k_solve_vector: one thread = one sample's whole Tsit5 solve in registers",
+                    "peak_source": "measured in this run by cnfb200_measure_fp32_peak",
+                    "note": "achieved counts lane-executed evaluations (nf of the slowest sample for every lane: lanes that "
+                            "finish early idle inside the warp), so it is an upper bound on useful flops",
+                    "stage_ms": solve_ms, "stage_launches": 1, "kernel_path": 4,
+                    "stage_share_of_step": ms_solve / ms_dev if ms_dev else None}
+    elif st["kernel_path"] == 3:
         # tensor path: FP16 hi/lo operand splitting executes 3 f16 MMA flops per algorithmic flop
         peaks = {}
         try:
@@ -279,7 +297,26 @@ def main():
         except (OSError, ValueError):
             pass
         peak = float(peaks.get("bf16_tflops_sustained", 1400.0))
-        roofline = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+        hbm_peak = float(peaks.get("hbm_gbs", 6400.0))
+        bytes_eval = wl.tc_bytes_per_eval(cid) * B
+        t_hbm = bytes_eval / (hbm_peak * 1e9)
+        t_tensor = 3 * flops_eval / (peak * 1e12)
+        if t_hbm > t_tensor:
+            # narrow hidden widths: the layer GEMMs stream hi/lo planes through HBM faster than they fill the tensor pipe
+            gbs = bytes_eval / (stage_ms * 1e-3) / 1e9 if stage_ms > 0 else 0.0
+            roofline = {"bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s", "frac": gbs / hbm_peak,
+                        "traffic": traffic,
+                        "kernel": "one augmented_f evaluation = 2L tcgen05 layer GEMMs (k_tc_gemm) + prep",
+                        "peak_source": "MEASURED_PEAKS.json hbm_gbs (copy bandwidth)" if peaks else "fallback 6.4 TB/s",
+                        "note": "achieved = algorithmic bytes of the evaluation (workloads.tc_bytes_per_eval: operands and "
+                                "results of every layer GEMM as hi/lo 16-bit planes) / mean evaluation time; the tensor-pipe "
+                                "time of the same evaluation at the sustained bf16 peak would be "
+                                f"{1e3 * t_tensor:.3f} ms against {1e3 * t_hbm:.3f} ms of HBM time",
+                        "algorithmic_tflops": achieved, "executed_f16_tflops": 3 * achieved,
+                        "stage_ms": stage_ms, "stage_launches": n_stage, "kernel_path": 3,
+                        "stage_share_of_step": ms_stage / ms_dev if ms_dev else None}
+        else:
+          roofline = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                     "frac": achieved / peak, "traffic": traffic,
                     "kernel": "one augmented_f evaluation = 2L tcgen05 layer GEMMs (k_tc_gemm) + prep",
                     "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (dense bf16, stage timed inside a "

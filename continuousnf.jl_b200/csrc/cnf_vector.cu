@@ -32,57 +32,18 @@ k_solve_vector(const __grid_constant__ NarrowW p, VecParams vp, const float* __r
     const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const bool live = b < vp.B;
     const long long Bs = vp.Bs;
-    float u[R], k[7][R];
+    float u[R], k[7][R];   // k is indexed by the (uniform) stage counter: it lives in local memory, L1-resident
 #pragma unroll
     for (int r = 0; r < R; ++r) u[r] = live ? u0[(long long)r * Bs + b] : 0.0f;
     const double nglobal = (double)R;
-    float z[D], y[D], tr;
-    // k1 = f(u0)
-#pragma unroll
-    for (int i = 0; i < D; ++i) z[i] = u[i];
-    narrow_f<D, H1, H2>(p, z, y, tr);
-#pragma unroll
-    for (int i = 0; i < D; ++i) k[0][i] = y[i];
-    k[0][D] = tr;
     long long nf = 1, iter = 0, naccept = 0, nreject = 0;
     int retcode = 0;
     bool done = !live;
-    float t = vp.t0, dt, dt_last = 0.0f;
-    double qold = CNF_QOLDINIT;
-    if (vp.dt0 > 0.0f) {
-        dt = vp.tdir * vp.dt0;
-    } else {   // Hairer's initial step (k_initnorm / k_initdt with nglobal = R)
-        double a0 = 0.0, a1 = 0.0;
-        float sk[R];
+    float t = vp.t0, dt = 0.0f, hh = 0.0f, dt0init = 0.0f;
+    double qold = CNF_QOLDINIT, d1 = 0.0;
+    float sk[R], un[R];
 #pragma unroll
-        for (int r = 0; r < R; ++r) {
-            sk[r] = fmaf(fabsf(u[r]), vp.reltol, vp.abstol);
-            const float r0 = u[r] / sk[r], r1 = k[0][r] / sk[r];
-            a0 += (double)r0 * (double)r0;
-            a1 += (double)r1 * (double)r1;
-        }
-        const double d0 = sqrt(a0 / nglobal), d1 = sqrt(a1 / nglobal);
-        double dta = (d0 < 1e-5 || d1 < 1e-5) ? 1e-6 : 0.01 * d0 / d1;
-        if (dta > (double)vp.dtmax) dta = (double)vp.dtmax;
-        const float dt0init = (float)dta;
-        const float hh = vp.tdir * dt0init;
-#pragma unroll
-        for (int i = 0; i < D; ++i) z[i] = fmaf(hh, k[0][i], u[i]);
-        narrow_f<D, H1, H2>(p, z, y, tr);
-        double a2 = 0.0;
-#pragma unroll
-        for (int r = 0; r < R; ++r) {
-            const float f1 = r < D ? y[r < D ? r : 0] : tr;
-            const float q = (f1 - k[0][r]) / sk[r];
-            a2 += (double)q * (double)q;
-        }
-        const double d2 = sqrt(a2 / nglobal) / (double)dt0init;
-        const double mx = d1 > d2 ? d1 : d2;
-        const double dt1 = (mx <= 1e-15) ? fmax(1e-6, (double)dt0init * 1e-3) : pow(10.0, -(2.0 + log10(mx)) / 5.0);
-        const double dtb = fmin(fmin(100.0 * (double)dt0init, dt1), (double)vp.dtmax);
-        dt = vp.tdir * (float)dtb;
-        nf += 2;
-    }
+    for (int r = 0; r < R; ++r) { sk[r] = 1.0f; un[r] = 0.0f; }
     // begin_attempt of cnf_solver.cu, per sample
     auto begin_attempt = [&]() {
         if (done) return;
@@ -93,74 +54,129 @@ k_solve_vector(const __grid_constant__ NarrowW p, VecParams vp, const float* __r
         dt = vp.tdir * adt;
         if (t + dt == t || (vp.dtmin > 0.0f && adt < vp.dtmin)) { retcode = CNF_RET_DTLESSTHANMIN; done = true; }
     };
-    begin_attempt();
-    while (__any_sync(0xffffffffu, !done)) {
-        // stages 2..6 and the candidate state (stage 6 = all R rows, the quadrature row included)
-        float un[R];
+    // One call site of narrow_f inside one loop (the function is ~40 KB of straight-line FFMAs: eight
+    // inlined copies would not fit the instruction cache).  phase 0: k1 = f(u0); 1: Hairer probe
+    // f(u0 + tdir*dt0init*k1); 2..7: stage s = phase - 1 of the current attempt (uniform over the grid).
+    int phase = 0;
+#pragma unroll 1
+    for (;;) {
+        float z[D], y[D], tr;
+        const int s = phase - 1;
+        if (phase == 0) {
 #pragma unroll
-        for (int s = 1; s <= 6; ++s) {
+            for (int i = 0; i < D; ++i) z[i] = u[i];
+        } else if (phase == 1) {
+#pragma unroll
+            for (int i = 0; i < D; ++i) z[i] = fmaf(hh, k[0][i], u[i]);
+        } else {
 #pragma unroll
             for (int r = 0; r < R; ++r) {
                 if (s < 6 && r >= D) continue;
                 float acc = c_A[s][0] * k[0][r];
-#pragma unroll
                 for (int j = 1; j < s; ++j) acc = fmaf(c_A[s][j], k[j][r], acc);
                 const float v = fmaf(dt, acc, u[r]);
                 if (s == 6) un[r] = v;
                 if (r < D) z[r < D ? r : 0] = v;
             }
-            narrow_f<D, H1, H2>(p, z, y, tr);
+        }
+        narrow_f<D, H1, H2>(p, z, y, tr);
+        if (phase == 0) {
+#pragma unroll
+            for (int i = 0; i < D; ++i) k[0][i] = y[i];
+            k[0][D] = tr;
+            if (vp.dt0 > 0.0f) {
+                dt = vp.tdir * vp.dt0;
+                begin_attempt();
+                phase = 2;
+            } else {   // Hairer's initial step (k_initnorm / k_initdt with nglobal = R)
+                double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    sk[r] = fmaf(fabsf(u[r]), vp.reltol, vp.abstol);
+                    const float r0 = u[r] / sk[r], r1 = k[0][r] / sk[r];
+                    a0 += (double)r0 * (double)r0;
+                    a1 += (double)r1 * (double)r1;
+                }
+                const double d0 = sqrt(a0 / nglobal);
+                d1 = sqrt(a1 / nglobal);
+                double dta = (d0 < 1e-5 || d1 < 1e-5) ? 1e-6 : 0.01 * d0 / d1;
+                if (dta > (double)vp.dtmax) dta = (double)vp.dtmax;
+                dt0init = (float)dta;
+                hh = vp.tdir * dt0init;
+                phase = 1;
+            }
+        } else if (phase == 1) {
+            double a2 = 0.0;
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const float f1 = r < D ? y[r < D ? r : 0] : tr;
+                const float q = (f1 - k[0][r]) / sk[r];
+                a2 += (double)q * (double)q;
+            }
+            const double d2 = sqrt(a2 / nglobal) / (double)dt0init;
+            const double mx = d1 > d2 ? d1 : d2;
+            const double dt1 = (mx <= 1e-15) ? fmax(1e-6, (double)dt0init * 1e-3) : pow(10.0, -(2.0 + log10(mx)) / 5.0);
+            const double dtb = fmin(fmin(100.0 * (double)dt0init, dt1), (double)vp.dtmax);
+            dt = vp.tdir * (float)dtb;
+            nf += 2;
+            begin_attempt();
+            phase = 2;
+        } else {
 #pragma unroll
             for (int i = 0; i < D; ++i) k[s][i] = y[i];
             k[s][D] = tr;
-        }
-        // embedded error (k_errnorm / the 7th narrow stage)
-        double es = 0.0;
-#pragma unroll
-        for (int r = 0; r < R; ++r) {
-            float a = c_BT[0] * k[0][r];
-#pragma unroll
-            for (int j = 1; j < 7; ++j) a = fmaf(c_BT[j], k[j][r], a);
-            const float ut = dt * a;
-            const float sc = fmaf(fmaxf(fabsf(u[r]), fabsf(un[r])), vp.reltol, vp.abstol);
-            float q = ut / sc;
-            if (un[r] != un[r]) q = un[r];
-            es += (double)q * (double)q;
-        }
-        if (!done) {   // k_controller, per sample
-            nf += 6;
-            const float EEst = (float)sqrt(es / nglobal);
-            if (EEst != EEst) {
-                retcode = CNF_RET_UNSTABLE;
-                done = true;
-            } else {
-                double q11 = 0.0, q;
-                if (EEst == 0.0f) {
-                    q = 1.0 / CNF_QMAX;
-                } else {
-                    q11 = pow((double)EEst, CNF_BETA1);
-                    q = q11 / pow(qold, CNF_BETA2);
-                    q = fmax(1.0 / CNF_QMAX, fmin(1.0 / CNF_QMIN, q / CNF_GAMMA));
-                }
-                if (EEst <= 1.0f) {
-                    float tn = t + dt;
-                    if (fabsf(tn - vp.t1) < 100.0f * 1.1920929e-7f * fmaxf(fabsf(t), fabsf(vp.t1))) tn = vp.t1;
-                    t = tn;
-#pragma unroll
-                    for (int r = 0; r < R; ++r) { u[r] = un[r]; k[0][r] = k[6][r]; }   // FSAL
-                    qold = fmax((double)EEst, CNF_QOLDINIT);
-                    dt_last = dt;
-                    dt = (float)((double)dt / q);
-                    naccept++;
-                } else {
-                    dt = (float)((double)dt / fmin(1.0 / CNF_QMIN, q11 / CNF_GAMMA));
-                    nreject++;
-                }
-                begin_attempt();
+            if (s < 6) {
+                phase++;
+                continue;
             }
+            // embedded error (k_errnorm / the 7th narrow stage)
+            double es = 0.0;
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                float a = c_BT[0] * k[0][r];
+#pragma unroll
+                for (int j = 1; j < 7; ++j) a = fmaf(c_BT[j], k[j][r], a);
+                const float ut = dt * a;
+                const float sc = fmaf(fmaxf(fabsf(u[r]), fabsf(un[r])), vp.reltol, vp.abstol);
+                float q = ut / sc;
+                if (un[r] != un[r]) q = un[r];
+                es += (double)q * (double)q;
+            }
+            if (!done) {   // k_controller, per sample
+                nf += 6;
+                const float EEst = (float)sqrt(es / nglobal);
+                if (EEst != EEst) {
+                    retcode = CNF_RET_UNSTABLE;
+                    done = true;
+                } else {
+                    double q11 = 0.0, q;
+                    if (EEst == 0.0f) {
+                        q = 1.0 / CNF_QMAX;
+                    } else {
+                        q11 = pow((double)EEst, CNF_BETA1);
+                        q = q11 / pow(qold, CNF_BETA2);
+                        q = fmax(1.0 / CNF_QMAX, fmin(1.0 / CNF_QMIN, q / CNF_GAMMA));
+                    }
+                    if (EEst <= 1.0f) {
+                        float tn = t + dt;
+                        if (fabsf(tn - vp.t1) < 100.0f * 1.1920929e-7f * fmaxf(fabsf(t), fabsf(vp.t1))) tn = vp.t1;
+                        t = tn;
+#pragma unroll
+                        for (int r = 0; r < R; ++r) { u[r] = un[r]; k[0][r] = k[6][r]; }   // FSAL
+                        qold = fmax((double)EEst, CNF_QOLDINIT);
+                        dt = (float)((double)dt / q);
+                        naccept++;
+                    } else {
+                        dt = (float)((double)dt / fmin(1.0 / CNF_QMIN, q11 / CNF_GAMMA));
+                        nreject++;
+                    }
+                    begin_attempt();
+                }
+            }
+            phase = 2;
         }
+        if (phase == 2 && !__any_sync(0xffffffffu, !done)) break;
     }
-    (void)dt_last;
     if (live) {
 #pragma unroll
         for (int r = 0; r < R; ++r) uout[(long long)r * Bs + b] = u[r];

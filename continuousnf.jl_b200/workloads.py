@@ -93,6 +93,25 @@ def flops_per_eval(cid, mode=None):
     return 2 * P + 2 * (P - c["C"] * dims[1])
 
 
+def tc_bytes_per_eval(cid):
+    """algorithmic HBM bytes per sample of one TrainMode/VecJac augmented_f evaluation on the tensor
+    path: every layer product is one GEMM launch whose operands and results are
+    hi/lo 16-bit planes (4 bytes per element, widths padded to 64); the epsilon chain re-reads h_l."""
+    c = CONFIGS[cid]
+    dims = c["dims"]
+    L = len(dims) - 1
+    D = c["nvars"] + c["naug"]
+    pad = lambda n: (n + 63) // 64 * 64
+    e = D + pad(dims[0])                                              # prep: z rows -> planes of h_0
+    for l in range(1, L):
+        e += pad(dims[l - 1]) + pad(dims[l])                          # h_l = tanh(W h_{l-1} + b)
+    e += pad(dims[L - 1]) + D + pad(D)                                # last layer: zdot rows + g_L planes
+    for l in range(L - 1, 0, -1):
+        e += pad(dims[l + 1] if l + 1 < L else D) + 2 * pad(dims[l])  # g_l: read g_{l+1}, h_l; write g_l
+    e += pad(dims[1]) + 3 * D                                         # v = W_1^T g_1 against eps; 3 output rows
+    return 4 * e
+
+
 def flops_backward_per_eval(cid):
     dims = CONFIGS[cid]["dims"]
     return 8 * sum(dims[l] * dims[l + 1] for l in range(len(dims) - 1))
