@@ -7,7 +7,7 @@ root) or importlib; the module registers itself as `cnfb200`.
 from . import _cabi, adapters, parallel, workloads  # noqa: F401
 from .adapters import CondICNFDist, CondICNFModel, ICNFDist, ICNFModel, Lion, fit, transform  # noqa: F401
 from .api import (  # noqa: F401
-    B200Libs, Chain, CondFFJORD, CondRNODE, Dense, DIJacVecMatrixMode, DIJacVecVectorMode,
+    B200Libs, Chain, CondFFJORD, CondPlanar, CondRNODE, Dense, Planar, PlanarLayer, DIJacVecMatrixMode, DIJacVecVectorMode,
     DIVecJacMatrixMode, DIVecJacVectorMode, FFJORD, ICNF, RNODE, TestMode, TrainMode, augmented_f,
     construct, generate, inference, last_stats, loss, loss_and_grad, param_offsets, set_option, setup,
     steer_tspan, seed_device_rng, last_eps, fit_epochs,

@@ -10,7 +10,7 @@ LIB_PATH = os.path.join(_HERE, "libcnfb200.so")
 MAX_LAYERS = 8
 MODE_TEST, MODE_TRAIN = 0, 1
 TRACE_VJP, TRACE_JVP = 0, 1
-FLAG_COND, FLAG_AUGMENTED, FLAG_NORM_Z, FLAG_NORM_J, FLAG_NORM_Z_AUG = 1, 2, 4, 8, 16
+FLAG_COND, FLAG_AUGMENTED, FLAG_NORM_Z, FLAG_NORM_J, FLAG_NORM_Z_AUG, FLAG_LAST_LINEAR = 1, 2, 4, 8, 16, 32
 RETCODES = {0: "Success", 1: "MaxIters", 2: "DtLessThanMin", 3: "Unstable"}
 
 EXPORTS = [

@@ -76,6 +76,14 @@ class CondFFJORD(AbstractICNF):
     cond = True
 
 
+class Planar(AbstractICNF):
+    """the tag whose nn is a PlanarLayer (src/icnf.jl:1-18); same augmented_f as FFJORD"""
+
+
+class CondPlanar(AbstractICNF):
+    cond = True
+
+
 class B200Libs:
     """The new resource type (the `resource = ...` keyword of construct selects the path)."""
 
@@ -92,10 +100,29 @@ class Dense:
         self.in_dims, self.out_dims = int(in_dims), int(out_dims)
 
 
+class PlanarLayer:
+    """PlanarLayer(nvars, tanh; n_cond) — src/layers/planar_layer.jl:1-88: z -> u * tanh(w'[z; ys] + b),
+    parameters (u[nvars], w[nvars + n_cond], b[1]).  Row N3: runs as Dense(d0 => 1, tanh) followed
+    by a bias-free linear product (CNF_FLAG_LAST_LINEAR) on the generic kernels."""
+
+    def __init__(self, nvars, activation="tanh", *, n_cond=0, use_bias=True):
+        name = getattr(activation, "__name__", activation)
+        if name != "tanh" or not use_bias:
+            raise ValueError("B200Libs path supports PlanarLayer(nvars, tanh; use_bias = true) only")
+        self.nvars, self.n_cond = int(nvars), int(n_cond)
+        self.in_dims, self.out_dims = self.nvars + self.n_cond, self.nvars
+
+
 class Chain:
+    planar = False
+
     def __init__(self, *layers):
         if len(layers) == 1 and isinstance(layers[0], (list, tuple)):
             layers = tuple(layers[0])
+        if any(isinstance(l, PlanarLayer) for l in layers):
+            if len(layers) != 1:
+                raise ValueError("B200Libs path: a PlanarLayer must be the whole network")
+            self.planar = True
         for a, b in zip(layers[:-1], layers[1:]):
             if a.out_dims != b.in_dims:
                 raise ValueError("Chain: layer widths do not match")
@@ -103,11 +130,17 @@ class Chain:
 
     @property
     def dims(self):
+        if self.planar:
+            return [self.layers[0].in_dims, 1, self.layers[0].out_dims]
         return [self.layers[0].in_dims] + [l.out_dims for l in self.layers]
 
 
-def param_offsets(dims):
-    """Lux/ComponentArray flat layout: layer_k = (weight[d_{k+1} x d_k col-major], bias)."""
+def param_offsets(dims, planar=False):
+    """Lux/ComponentArray flat layout: layer_k = (weight[d_{k+1} x d_k col-major], bias);
+    PlanarLayer: (u, w, b) (src/layers/planar_layer.jl:38-60)."""
+    if planar:
+        d0, D = dims[0], dims[2]
+        return np.array([D, 0], np.int64), np.array([D + d0, 0], np.int64), D + d0 + 1
     w, b, o = [], [], 0
     for l in range(len(dims) - 1):
         w.append(o)
@@ -154,6 +187,8 @@ class ICNF:
             fl |= _cabi.FLAG_NORM_J
         if self.lambda3 != 0:
             fl |= _cabi.FLAG_NORM_Z_AUG
+        if self.nn.planar:
+            fl |= _cabi.FLAG_LAST_LINEAR
         c.flags = fl
         c.lambda1, c.lambda2, c.lambda3 = self.lambda1, self.lambda2, self.lambda3
         sk = dict(self.sol_kwargs)
@@ -242,6 +277,12 @@ def setup(rng, icnf):
     vector in ComponentArray order (src/exts/mlj_ext/core_icnf.jl:37-38)."""
     parts = []
     dims = icnf.dims
+    if icnf.nn.planar:   # glorot_uniform on vectors (nfan = (1, n)), zero bias
+        for n in (dims[2], dims[0]):
+            lim = math.sqrt(6.0 / (1 + n))
+            parts.append(rng.uniform(-lim, lim, n).astype(np.float32))
+        parts.append(np.zeros(1, np.float32))
+        return np.concatenate(parts), {}
     for l in range(len(dims) - 1):
         lim = math.sqrt(6.0 / (dims[l] + dims[l + 1]))
         parts.append(rng.uniform(-lim, lim, dims[l] * dims[l + 1]).astype(np.float32))
@@ -291,7 +332,7 @@ def _rows_view(holder):
 def _upload_params(icnf, ps):
     lib = _cabi.load()
     h = icnf.handle()
-    w, b, n = param_offsets(icnf.dims)
+    w, b, n = param_offsets(icnf.dims, icnf.nn.planar)
     if _is_torch(ps):
         import torch
         p = ps.detach().to(torch.float32).contiguous()
@@ -369,7 +410,7 @@ def fit_epochs(icnf, X, Y, ps, *, batch_size, n_epochs, perm=None, eta=1e-3, bet
         if p.shape != (n_epochs, x.B):
             raise ValueError(f"perm must have shape ({n_epochs}, {x.B})")
     t0, t1 = steer_tspan(icnf, TrainMode())
-    out = np.empty(param_offsets(icnf.dims)[2], np.float32)
+    out = np.empty(param_offsets(icnf.dims, icnf.nn.planar)[2], np.float32)
     hist = np.empty(n_epochs, np.float32)
     st_ = _cabi.CnfStats()
     rc = lib.cnfb200_fit_epochs(h, x.ptr, y.ptr if y else None, x.B, int(batch_size), int(n_epochs),
@@ -461,7 +502,7 @@ def loss_and_grad(icnf, mode, xs, *args, eps=None, want_grad=True, want_grad_x=F
     y = _Mat(ys, icnf._cfg.C, "ys") if icnf.cond else None
     e = _draw_eps(icnf, mode, x.B, x, eps)
     t0, t1 = steer_tspan(icnf, mode)
-    _, _, n = param_offsets(icnf.dims)
+    _, _, n = param_offsets(icnf.dims, icnf.nn.planar)
     val = C.c_float(0.0)
     g = np.zeros(n, np.float32) if want_grad else None
     gx, gx_ptr = _out(icnf.nvars, x.B, x) if want_grad_x else (None, None)

@@ -162,12 +162,13 @@ extern "C" int32_t cnfb200_set_params(cnf_handle* h, const float* theta, int64_t
     long long wt_total = 0;
     for (int l = 0; l < c.n_layers; ++l) {
         long long wsz = (long long)c.dims[l] * c.dims[l + 1];
-        if (w_off[l] < 0 || w_off[l] + wsz > n || b_off[l] < 0 || b_off[l] + c.dims[l + 1] > n) {
+        const bool nobias = (c.flags & CNF_FLAG_LAST_LINEAR) && l == c.n_layers - 1;
+        if (w_off[l] < 0 || w_off[l] + wsz > n || (!nobias && (b_off[l] < 0 || b_off[l] + c.dims[l + 1] > n))) {
             h->err = "set_params: offsets outside theta";
             return CNF_ERR_BADARG;
         }
         h->w_off[l] = w_off[l];
-        h->b_off[l] = b_off[l];
+        h->b_off[l] = nobias ? 0 : b_off[l];
         h->wt_off[l] = wt_total;
         wt_total += wsz;
     }

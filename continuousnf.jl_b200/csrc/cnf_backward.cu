@@ -13,6 +13,7 @@ struct BwLayout {
     int qoff[CNF_MAX_LAYERS + 1];  // l = 1..L, dims[l] rows: q_{l+1} (VecJac) / r_l (JacVec), later db_l
     int w[6];                      // work buffers, maxd rows each
     int e, ybar, vbar, red;
+    int z0;                        // zeros: h_L inside 1 - h^2 when the last layer is linear
     int total;
 };
 static BwLayout bw_layout(const cnf_config& cfg, int TB) {
@@ -30,6 +31,7 @@ static BwLayout bw_layout(const cnf_config& cfg, int TB) {
     L.ybar = o; o += cfg.D * TBP;
     L.vbar = o; o += cfg.D * TBP;
     L.red = o; o += 6 * TBP;
+    L.z0 = o; o += cfg.D * TBP;
     L.total = o;
     return L;
 }
@@ -81,6 +83,10 @@ k_vjp_generic(CnfBufs bf, CnfNet net, BwLayout lay, const float* __restrict__ sr
     const float wgt = dt * c_A[6][stage];
     const float alpha = wgt * c_l, beta = wgt * c_E, gamma = wgt * c_n;
     const bool jvp = net.trace_mode == CNF_TRACE_JVP;
+    const bool lin = (net.flags & CNF_FLAG_LAST_LINEAR) != 0;
+    for (int idx = tid; idx < D * TBP; idx += CNF_NT) sm[lay.z0 + idx] = 0.0f;
+    // h_l as the argument of the activation derivative (and of its derivative -2 h (1 - h^2))
+    auto hder = [&](int l) -> const float* { return (lin && l == L) ? sm + lay.z0 : sm + lay.hoff[l]; };
     // ---- forward activations
     {
         GenLayout gl;
@@ -106,7 +112,8 @@ k_vjp_generic(CnfBufs bf, CnfNet net, BwLayout lay, const float* __restrict__ sr
     // ---- the eps chain (kept per layer: needed by the second-order terms)
     if (!jvp) {
         float* gL = sm + lay.goff[L];
-        EW_LOOP(D) { float hh = hL[EW_AT]; gL[EW_AT] = e[EW_AT] * fmaf(-hh, hh, 1.0f); }
+        const float* hLd = hder(L);
+        EW_LOOP(D) { float hh = hLd[EW_AT]; gL[EW_AT] = e[EW_AT] * fmaf(-hh, hh, 1.0f); }
         __syncthreads();
         for (int l = L; l >= 1; --l) {
             int din = net.dims[l - 1], dout = net.dims[l];
@@ -131,7 +138,7 @@ k_vjp_generic(CnfBufs bf, CnfNet net, BwLayout lay, const float* __restrict__ sr
             dense_tile<TB>(net.Wt[l - 1], din, nullptr, l == 1 ? D : din, dout,
                            l == 1 ? e : sm + lay.goff[l - 1], r, EPI_NONE, nullptr);
             __syncthreads();
-            const float* hm = sm + lay.hoff[l];
+            const float* hm = hder(l);
             float* t = sm + lay.goff[l];
             EW_LOOP(dout) { float hh = hm[EW_AT]; t[EW_AT] = r[EW_AT] * fmaf(-hh, hh, 1.0f); }
             __syncthreads();
@@ -190,7 +197,7 @@ k_vjp_generic(CnfBufs bf, CnfNet net, BwLayout lay, const float* __restrict__ sr
     for (int l = L; l >= 1; --l) {
         int din = net.dims[l - 1], dout = net.dims[l];
         int used = (l == 1) ? D : din;
-        const float* hm = sm + lay.hoff[l];
+        const float* hm = hder(l);
         float* db = sm + lay.qoff[l];
         float* pb = sm + lay.w[1];
         if (jvp) {
@@ -215,7 +222,7 @@ k_vjp_generic(CnfBufs bf, CnfNet net, BwLayout lay, const float* __restrict__ sr
         }
         __syncthreads();
         outer_acc_tile<TB>(grad + net.w_off[l - 1], dout, din, pb, sm + lay.hoff[l - 1]);
-        bias_acc_tile<TB>(grad + net.b_off[l - 1], dout, pb);
+        if (!(lin && l == L)) bias_acc_tile<TB>(grad + net.b_off[l - 1], dout, pb);
         float* hn = sm + lay.w[4 + (l & 1)];
         dense_tile<TB>(net.W[l - 1], dout, nullptr, dout, used, pb, hn, EPI_NONE, nullptr);
         hb = hn;

@@ -50,6 +50,7 @@ __device__ __forceinline__ void dense_tile(const float* __restrict__ Wrow, int l
 struct GenLayout {
     int hoff[CNF_MAX_LAYERS + 1];  // float offsets of h_l
     int gA, gB, e, red;            // ping-pong chain buffers, eps tile, per-sample scalars
+    int z0;                        // zeros: stands in for h_L in 1 - h^2 when the last layer is linear
     int total;                     // floats
 };
 static GenLayout gen_layout(const cnf_config& cfg, int TB) {
@@ -64,6 +65,7 @@ static GenLayout gen_layout(const cnf_config& cfg, int TB) {
     L.gB = o; o += maxd * TBP;
     L.e = o; o += cfg.D * TBP;
     L.red = o; o += 4 * TBP;
+    L.z0 = o; o += cfg.D * TBP;
     L.total = o;
     return L;
 }
@@ -83,10 +85,17 @@ __device__ void gen_forward(const CnfNet& net, const GenLayout& lay, float* sm, 
     }
     __syncthreads();
     for (int l = 0; l < net.L; ++l) {
-        dense_tile<TB>(net.Wt[l], net.dims[l], net.b[l], net.dims[l], net.dims[l + 1],
-                       sm + lay.hoff[l], sm + lay.hoff[l + 1], EPI_TANH, nullptr);
+        // CNF_FLAG_LAST_LINEAR: the last layer is a plain product (PlanarLayer's u * act(.), planar_layer.jl:70-88)
+        const bool lin = (net.flags & CNF_FLAG_LAST_LINEAR) && l == net.L - 1;
+        dense_tile<TB>(net.Wt[l], net.dims[l], lin ? nullptr : net.b[l], net.dims[l], net.dims[l + 1],
+                       sm + lay.hoff[l], sm + lay.hoff[l + 1], lin ? EPI_NONE : EPI_TANH, nullptr);
         __syncthreads();
     }
+}
+
+// h_l as the argument of the activation derivative 1 - h^2 (zeros for a linear last layer: derivative 1)
+__device__ __forceinline__ const float* gen_hder(const CnfNet& net, const GenLayout& lay, const float* sm, int l) {
+    return ((net.flags & CNF_FLAG_LAST_LINEAR) && l == net.L) ? sm + lay.z0 : sm + lay.hoff[l];
 }
 
 // reverse chain from cotangent g_L (already multiplied by 1-h_L^2) in buffer `cur`;
@@ -112,7 +121,7 @@ __device__ float* gen_jvp_chain(const CnfNet& net, const GenLayout& lay, float* 
                                 float* oth) {
     for (int l = 2; l <= net.L; ++l) {
         dense_tile<TB>(net.Wt[l - 1], net.dims[l - 1], nullptr, net.dims[l - 1], net.dims[l], cur,
-                       oth, EPI_MULD, sm + lay.hoff[l]);
+                       oth, EPI_MULD, gen_hder(net, lay, sm, l));
         __syncthreads();
         float* t = cur; cur = oth; oth = t;
     }
@@ -135,8 +144,10 @@ k_eval_generic(const CnfCtrl* __restrict__ c, CnfBufs bf, CnfNet net, GenLayout 
     float* kout = kout_ptr;
     if (!kout) kout = (kidx == 6) ? bf.K[6 - c->k1idx] : (kidx == 0 ? bf.K[c->k1idx] : bf.K[kidx]);
     const long long b0 = (long long)blockIdx.x * TB;
+    for (int idx = threadIdx.x; idx < D * TBP; idx += CNF_NT) sm[lay.z0 + idx] = 0.0f;
     gen_forward<TB>(net, lay, sm, src, bf.ys, Bs, b0, bf.B);
     float* hL = sm + lay.hoff[L];
+    const float* hLd = gen_hder(net, lay, sm, L);   // h_L where 1 - h_L^2 is meant
     float* gA = sm + lay.gA;
     float* gB = sm + lay.gB;
     float* e = sm + lay.e;
@@ -149,14 +160,14 @@ k_eval_generic(const CnfCtrl* __restrict__ c, CnfBufs bf, CnfNet net, GenLayout 
             if (net.trace_mode == CNF_TRACE_VJP) {
                 for (int idx = tid; idx < D * TB; idx += CNF_NT) {
                     int o = idx / TB, s = idx % TB;
-                    float hh = hL[o * TBP + s];
+                    float hh = hLd[o * TBP + s];
                     gA[o * TBP + s] = (o == i) ? fmaf(-hh, hh, 1.0f) : 0.0f;
                 }
                 __syncthreads();
                 res = gen_vjp_chain<TB>(net, lay, sm, gA, gB);
             } else {
                 const int d1 = net.dims[1];
-                const float* h1 = sm + lay.hoff[1];
+                const float* h1 = gen_hder(net, lay, sm, 1);
                 for (int idx = tid; idx < d1 * TB; idx += CNF_NT) {
                     int o = idx / TB, s = idx % TB;
                     float hh = h1[o * TBP + s];
@@ -179,14 +190,14 @@ k_eval_generic(const CnfCtrl* __restrict__ c, CnfBufs bf, CnfNet net, GenLayout 
         if (net.trace_mode == CNF_TRACE_VJP) {
             for (int idx = tid; idx < D * TB; idx += CNF_NT) {
                 int o = idx / TB, s = idx % TB;
-                float hh = hL[o * TBP + s];
+                float hh = hLd[o * TBP + s];
                 gA[o * TBP + s] = e[o * TBP + s] * fmaf(-hh, hh, 1.0f);
             }
             __syncthreads();
             res = gen_vjp_chain<TB>(net, lay, sm, gA, gB);
         } else {
             dense_tile<TB>(net.Wt[0], net.dims[0], nullptr, D, net.dims[1], e, gA, EPI_MULD,
-                           sm + lay.hoff[1]);
+                           gen_hder(net, lay, sm, 1));
             __syncthreads();
             res = gen_jvp_chain<TB>(net, lay, sm, gA, gB);
         }

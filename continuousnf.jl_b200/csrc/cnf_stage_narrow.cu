@@ -217,7 +217,7 @@ static const NarrowEntry g_narrow[] = {
 };
 
 static const NarrowEntry* narrow_find(const cnf_config& c) {
-    if (c.n_layers != 3 || c.C != 0) return nullptr;
+    if (c.n_layers != 3 || c.C != 0 || (c.flags & CNF_FLAG_LAST_LINEAR)) return nullptr;
     for (const NarrowEntry& e : g_narrow)
         if (e.D == c.D && e.H1 == c.dims[1] && e.H2 == c.dims[2]) return &e;
     return nullptr;

@@ -807,6 +807,7 @@ static int tc_alloc_f32(cnf_handle* h, TcF32& f, int rows, int ld) {
 // multiples of 32 and >= 128 (auto) — or any multiple of 32 when forced with kernel_path = 3
 bool tc_supported(const cnf_config& c, int mode) {
     if (mode != CNF_MODE_TRAIN || c.n_layers < 2 || c.D > 256) return false;
+    if (c.flags & CNF_FLAG_LAST_LINEAR) return false;   // generic kernels only
     bool wide = true;
     for (int l = 1; l < c.n_layers; ++l) {
         if (c.dims[l] % 32 != 0) return false;

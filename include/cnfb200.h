@@ -37,6 +37,9 @@ extern "C" {
 #define CNF_FLAG_NORM_Z      (1u << 2) /* lambda1 != 0: integrate ||zdot||_2 (src/icnf.jl:335-341) */
 #define CNF_FLAG_NORM_J      (1u << 3) /* lambda2 != 0: integrate ||eps^T J||_2 (src/icnf.jl:342-348) */
 #define CNF_FLAG_NORM_Z_AUG  (1u << 4) /* lambda3 != 0: ||z_aug(t1)||_2 (src/base_icnf.jl:179-187) */
+#define CNF_FLAG_LAST_LINEAR (1u << 5) /* the last layer has no activation and no bias: with dims = [d0, 1, D] this is
+                                          * PlanarLayer, u * act(w'z + b) (src/layers/planar_layer.jl:70-88; row N3);
+                                          * b_off of that layer is ignored */
 
 /* mode: src/types.jl Mode {TestMode, TrainMode} */
 #define CNF_MODE_TEST  0 /* exact trace, R = D+1 rows (src/icnf.jl:148-184) */

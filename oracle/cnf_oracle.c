@@ -69,12 +69,13 @@ typedef struct {
     float* t0;
     float* t1;
     float* t2;
+    float* zero; /* stands in for h_L where its derivative 1 - h^2 is meant and the last layer is linear */
     float* store;
 } oscratch;
 
 static void oscratch_alloc(oscratch* s, const omodel* m) {
     size_t per = (size_t)m->maxd * TS;
-    size_t n = (size_t)(3 * (CNF_MAX_LAYERS + 1) + 3) * per;
+    size_t n = (size_t)(3 * (CNF_MAX_LAYERS + 1) + 4) * per;
     s->store = (float*)aligned_alloc(64, n * sizeof(float));
     float* p = s->store;
     for (int l = 0; l <= CNF_MAX_LAYERS; ++l) { s->h[l] = p; p += per; }
@@ -82,8 +83,13 @@ static void oscratch_alloc(oscratch* s, const omodel* m) {
     for (int l = 0; l <= CNF_MAX_LAYERS; ++l) { s->q[l] = p; p += per; }
     s->t0 = p; p += per;
     s->t1 = p; p += per;
-    s->t2 = p;
+    s->t2 = p; p += per;
+    s->zero = p;
+    memset(s->zero, 0, per * sizeof(float));
 }
+/* h_l as the argument of the activation derivative: d_l = 1 - h_l^2, or 1 for a linear last layer
+ * (CNF_FLAG_LAST_LINEAR: PlanarLayer's u * act(.), src/layers/planar_layer.jl:70-88) */
+#define H_DER(m, sc, l) ((((m)->cfg.flags & CNF_FLAG_LAST_LINEAR) && (l) == (m)->L) ? (const float*)(sc)->zero : (const float*)(sc)->h[l])
 static void oscratch_free(oscratch* s) { free(s->store); }
 
 /* out[o][:] = (bias ? b[o] : 0) + sum_{i<din_used} W[o,i] * in[i][:]   (W: dout x din col-major) */
@@ -139,9 +145,11 @@ static void dense_mulT(const float* W, int dout, int din_used, const float* in, 
 static void nn_forward(const omodel* m, oscratch* sc) {
     for (int l = 0; l < m->L; ++l) {
         int din = m->cfg.dims[l], dout = m->cfg.dims[l + 1];
-        dense_mul(m->theta + m->w_off[l], m->theta + m->b_off[l], dout, din, sc->h[l], sc->h[l + 1]);
+        const int lin = (m->cfg.flags & CNF_FLAG_LAST_LINEAR) && l == m->L - 1;
+        dense_mul(m->theta + m->w_off[l], lin ? NULL : m->theta + m->b_off[l], dout, din, sc->h[l], sc->h[l + 1]);
         float* y = sc->h[l + 1];
-        for (int k = 0; k < dout * TS; ++k) y[k] = tanh_fast(y[k]);
+        if (!lin)
+            for (int k = 0; k < dout * TS; ++k) y[k] = tanh_fast(y[k]);
     }
 }
 
@@ -151,7 +159,7 @@ static void vjp_chain(const omodel* m, oscratch* sc, const float* seed) {
     int L = m->L;
     {
         int d = m->cfg.dims[L];
-        const float* h = sc->h[L];
+        const float* h = H_DER(m, sc, L);
         float* g = sc->g[L];
         for (int k = 0; k < d * TS; ++k) g[k] = seed[k] * fmaf(-h[k], h[k], 1.0f);
     }
@@ -176,7 +184,7 @@ static void jvp_chain(const omodel* m, oscratch* sc, const float* seed) {
         int din = m->cfg.dims[l - 1], dout = m->cfg.dims[l];
         int used = (l == 1) ? m->D : din;
         dense_mul(m->theta + m->w_off[l - 1], NULL, dout, used, in, sc->q[l]);
-        const float* h = sc->h[l];
+        const float* h = H_DER(m, sc, l);
         const float* r = sc->q[l];
         float* t = sc->g[l];
         for (int k = 0; k < dout * TS; ++k) t[k] = r[k] * fmaf(-h[k], h[k], 1.0f);
@@ -656,7 +664,7 @@ static void rhs_vjp_tile(const omodel* m, oscratch* sc, obscratch* bs, const flo
             int used = (l == 1) ? D : din;
             dense_mul(th + m->w_off[l - 1], NULL, dout, used, qb, bs->gb[l]);
             outer_acc(gth + m->w_off[l - 1], dout, used, sc->g[l], qb);
-            const float* hl = sc->h[l];
+            const float* hl = H_DER(m, sc, l);
             if (l < L) {
                 for (int k = 0; k < dout * TS; ++k) {
                     bs->db[l][k] = bs->gb[l][k] * sc->q[l + 1][k];
@@ -677,7 +685,7 @@ static void rhs_vjp_tile(const omodel* m, oscratch* sc, obscratch* bs, const flo
         for (int l = L; l >= 1; --l) {
             int din = m->cfg.dims[l - 1], dout = m->cfg.dims[l];
             int used = (l == 1) ? D : din;
-            const float* hl = sc->h[l];
+            const float* hl = H_DER(m, sc, l);
             float* rb = bs->gb[l];
             for (int k = 0; k < dout * TS; ++k) {
                 rb[k] = taub[k] * fmaf(-hl[k], hl[k], 1.0f);
@@ -692,17 +700,18 @@ static void rhs_vjp_tile(const omodel* m, oscratch* sc, obscratch* bs, const flo
     for (int k = 0; k < D * TS; ++k) hb[k] = ybar[k];
     for (int l = L; l >= 1; --l) {
         int din = m->cfg.dims[l - 1], dout = m->cfg.dims[l];
-        const float* hl = sc->h[l];
+        const float* hl = H_DER(m, sc, l);
         for (int k = 0; k < dout * TS; ++k) {
             float hbk = fmaf(-2.0f * hl[k], bs->db[l][k], hb[k]);
             bs->pb[k] = hbk * fmaf(-hl[k], hl[k], 1.0f);
         }
         outer_acc(gth + m->w_off[l - 1], dout, din, bs->pb, sc->h[l - 1]);
-        for (int o = 0; o < dout; ++o) {
-            float acc = 0.0f;
-            for (int s = 0; s < TS; ++s) acc += bs->pb[o * TS + s];
-            gth[m->b_off[l - 1] + o] += (double)acc;
-        }
+        if (!((m->cfg.flags & CNF_FLAG_LAST_LINEAR) && l == L))
+            for (int o = 0; o < dout; ++o) {
+                float acc = 0.0f;
+                for (int s = 0; s < TS; ++s) acc += bs->pb[o * TS + s];
+                gth[m->b_off[l - 1] + o] += (double)acc;
+            }
         int used = (l == 1) ? D : din;
         dense_mulT(th + m->w_off[l - 1], dout, used, bs->pb, hb);
     }

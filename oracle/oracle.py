@@ -17,7 +17,7 @@ _LIB = None
 MAX_LAYERS = 8
 MODE_TEST, MODE_TRAIN = 0, 1
 TRACE_VJP, TRACE_JVP = 0, 1
-FLAG_COND, FLAG_AUGMENTED, FLAG_NORM_Z, FLAG_NORM_J, FLAG_NORM_Z_AUG = 1, 2, 4, 8, 16
+FLAG_COND, FLAG_AUGMENTED, FLAG_NORM_Z, FLAG_NORM_J, FLAG_NORM_Z_AUG, FLAG_LAST_LINEAR = 1, 2, 4, 8, 16, 32
 
 
 class Config(C.Structure):
@@ -63,7 +63,7 @@ def lib():
 
 
 def make_config(nvars, naug, dims, *, C_=0, trace_mode=TRACE_VJP, lambda1=0.0, lambda2=0.0,
-                lambda3=0.0, reltol=0.0, abstol=0.0, maxiters=0, dt0=0.0, dtmax=0.0, dtmin=0.0):
+                lambda3=0.0, reltol=0.0, abstol=0.0, maxiters=0, dt0=0.0, dtmax=0.0, dtmin=0.0, planar=False):
     cfg = Config()
     D = nvars + naug
     assert dims[0] == D + C_ and dims[-1] == D, (dims, D, C_)
@@ -82,6 +82,9 @@ def make_config(nvars, naug, dims, *, C_=0, trace_mode=TRACE_VJP, lambda1=0.0, l
         fl |= FLAG_NORM_J
     if lambda3 != 0:
         fl |= FLAG_NORM_Z_AUG
+    if planar:   # PlanarLayer(nvars, tanh; n_cond): u * tanh(w'[z; ys] + b) = Dense(d0 => 1, tanh) then a bias-free product
+        assert len(dims) == 3 and dims[1] == 1
+        fl |= FLAG_LAST_LINEAR
     cfg.flags = fl
     cfg.lambda1, cfg.lambda2, cfg.lambda3 = lambda1, lambda2, lambda3
     cfg.reltol, cfg.abstol, cfg.maxiters = reltol, abstol, maxiters
@@ -89,8 +92,12 @@ def make_config(nvars, naug, dims, *, C_=0, trace_mode=TRACE_VJP, lambda1=0.0, l
     return cfg
 
 
-def offsets(dims):
-    """Lux field order: layer_k = (weight[d_{k+1} x d_k col-major], bias[d_{k+1}])"""
+def offsets(dims, planar=False):
+    """Lux field order: layer_k = (weight[d_{k+1} x d_k col-major], bias[d_{k+1}]); PlanarLayer
+    (src/layers/planar_layer.jl:38-60): (u[nvars], w[nvars + n_cond], b[1])"""
+    if planar:
+        d0, D = dims[0], dims[2]
+        return np.array([D, 0], np.int64), np.array([D + d0, 0], np.int64), D + d0 + 1
     w, b, o = [], [], 0
     for l in range(len(dims) - 1):
         w.append(o)
@@ -118,7 +125,7 @@ def R_of(cfg, mode):
 
 def augmented_f(cfg, theta, mode, u, ys=None, eps=None):
     """u: (B, R) sample-major. returns du (B, R)"""
-    w, b, _ = offsets(list(cfg.dims[:cfg.n_layers + 1]))
+    w, b, _ = offsets(list(cfg.dims[:cfg.n_layers + 1]), bool(cfg.flags & FLAG_LAST_LINEAR))
     u, ys, eps, theta = _prep(u), _prep(ys), _prep(eps), _prep(theta)
     B = u.shape[0]
     du = np.empty_like(u)
@@ -129,7 +136,7 @@ def augmented_f(cfg, theta, mode, u, ys=None, eps=None):
 
 def logdensity(cfg, theta, mode, xs, ys=None, eps=None, t0=0.0, t1=1.0):
     """xs: (B, nvars). returns logp (B,), regs (B, 3|1), z (B, D), stats dict"""
-    w, b, _ = offsets(list(cfg.dims[:cfg.n_layers + 1]))
+    w, b, _ = offsets(list(cfg.dims[:cfg.n_layers + 1]), bool(cfg.flags & FLAG_LAST_LINEAR))
     xs, ys, eps, theta = _prep(xs), _prep(ys), _prep(eps), _prep(theta)
     B = xs.shape[0]
     if eps is None:
@@ -146,7 +153,7 @@ def logdensity(cfg, theta, mode, xs, ys=None, eps=None, t0=0.0, t1=1.0):
 
 
 def generate(cfg, theta, mode, z0, ys=None, eps=None, t_from=1.0, t_to=0.0):
-    w, b, _ = offsets(list(cfg.dims[:cfg.n_layers + 1]))
+    w, b, _ = offsets(list(cfg.dims[:cfg.n_layers + 1]), bool(cfg.flags & FLAG_LAST_LINEAR))
     z0, ys, eps, theta = _prep(z0), _prep(ys), _prep(eps), _prep(theta)
     n = z0.shape[0]
     if eps is None:
@@ -160,7 +167,7 @@ def generate(cfg, theta, mode, z0, ys=None, eps=None, t_from=1.0, t_to=0.0):
 
 
 def loss_grad(cfg, theta, xs, ys=None, eps=None, t0=0.0, t1=1.0, want_grad=True, mode=1):
-    w, b, n = offsets(list(cfg.dims[:cfg.n_layers + 1]))
+    w, b, n = offsets(list(cfg.dims[:cfg.n_layers + 1]), bool(cfg.flags & FLAG_LAST_LINEAR))
     xs, ys, eps, theta = _prep(xs), _prep(ys), _prep(eps), _prep(theta)
     B = xs.shape[0]
     loss = C.c_float(0)

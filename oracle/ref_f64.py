@@ -26,8 +26,12 @@ BT = [-0.00178001105222577714, -0.0008164344596567469, 0.007880878010261995,
       -0.1447110071732629, 0.5823571654525552, -0.45808210592918697, 0.015151515151515152]
 
 
-def unpack(theta, dims):
-    """flat Lux ComponentArray layout -> [(W (dout,din), b (dout,))]"""
+def unpack(theta, dims, planar=False):
+    """flat Lux ComponentArray layout -> [(W (dout,din), b (dout,))]; PlanarLayer (u, w, b) ->
+    [(w' (1,d0), b), (u (D,1), None)] with a linear, bias-free second product"""
+    if planar:
+        d0, D = dims[0], dims[2]
+        return [(theta[D:D + d0].reshape(1, d0), theta[D + d0:D + d0 + 1]), (theta[:D].reshape(D, 1), None)]
     out, o = [], 0
     for l in range(len(dims) - 1):
         din, dout = dims[l], dims[l + 1]
@@ -42,7 +46,7 @@ def unpack(theta, dims):
 def mlp(layers, h):
     """h: (B, d0) -> (B, dL); every Dense layer has tanh (exact tanh here)"""
     for W, b in layers:
-        h = torch.tanh(h @ W.T + b)
+        h = torch.tanh(h @ W.T + b) if b is not None else h @ W.T
     return h
 
 
@@ -142,7 +146,7 @@ def run(cfg, theta, mode, xs, ys=None, eps=None, t0=0.0, t1=1.0, frozen_dts=None
     x = torch.tensor(np.asarray(xs, np.float64), requires_grad=requires_grad)
     y = None if ys is None else torch.tensor(np.asarray(ys, np.float64))
     e = None if eps is None else torch.tensor(np.asarray(eps, np.float64))
-    layers = unpack(th, dims)
+    layers = unpack(th, dims, bool(cfg.flags & 32))
     B = x.shape[0]
     R = D + (3 if mode == 1 else 1)
     u0 = torch.cat([x, torch.zeros(B, R - nv, dtype=torch.float64)], dim=1)

@@ -372,3 +372,48 @@ def test_n4_vector_mode_generate_roundtrip_and_unsupported_shapes():
     i3 = wl.make_inputs("C3", B=8)
     with pytest.raises(cnf._cabi.CnfError):      # not a narrow shape
         cnf.inference(wide, m, i3["xs"].T, *args_of(i3))
+
+
+def _planar_pair(nvars, C, B, trace_mode, seed=7):
+    """(product model, oracle config, inputs) for nn = PlanarLayer(nvars, tanh; n_cond = C)"""
+    rng = np.random.default_rng(seed)
+    d0 = nvars + C
+    cfg = O.make_config(nvars, 0, [d0, 1, nvars], C_=C, planar=True, trace_mode=trace_mode, lambda1=1e-2, lambda2=1e-2)
+    theta = np.concatenate([rng.normal(0, 0.8, nvars), rng.normal(0, 0.8, d0), rng.normal(0, 0.3, 1)]).astype(np.float32)
+    xs = rng.normal(0, 1, (B, nvars)).astype(np.float32)
+    ys = rng.normal(0, 1, (B, C)).astype(np.float32) if C else None
+    eps = rng.normal(0, 1, (B, nvars)).astype(np.float32)
+    cm = cnf.DIVecJacMatrixMode() if trace_mode == 0 else cnf.DIJacVecMatrixMode()
+    tag = cnf.CondPlanar if C else cnf.Planar
+    icnf = cnf.construct(tag, cnf.PlanarLayer(nvars, "tanh", n_cond=C), nvars, 0, compute_mode=cm, tspan=(0.0, 1.0),
+                         lambda1=1e-2, lambda2=1e-2, resource=cnf.B200Libs(0), rng=np.random.default_rng(1))
+    tail = ((ys.T,) if C else ()) + (theta, {})
+    return icnf, cfg, theta, xs, ys, eps, tail
+
+
+@pytest.mark.parametrize("C", [0, 3])
+@pytest.mark.parametrize("trace_mode", [0, 1])
+def test_n3_planar_flow_matches_oracle(C, trace_mode):
+    """N3: the Planar / CondPlanar tags (nn = PlanarLayer) on the new resource: log-density in both
+    modes, loss and gradients (TrainMode Hutchinson and TestMode exact trace), generate round trip."""
+    nv, B = 6, 777
+    icnf, cfg, theta, xs, ys, eps, tail = _planar_pair(nv, C, B, trace_mode)
+    for mode, m in ((0, cnf.TestMode()), (1, cnf.TrainMode())):
+        lp, regs, z = cnf.inference(icnf, m, xs.T, *tail, eps=eps.T if mode else None, return_z=True)
+        st = cnf.last_stats(icnf)
+        rlp, rregs, rz, rst = O.logdensity(cfg, theta, mode, xs, ys, eps if mode else None, 0.0, 1.0)
+        assert abs(st["naccept"] - rst["naccept"]) <= 1
+        tol = 1e-4 if st["naccept"] == rst["naccept"] else 5e-3
+        assert np.max(np.abs(np.asarray(lp) - rlp) / np.maximum(1.0, np.abs(rlp))) < tol
+        assert np.max(np.abs(np.asarray(z).T - rz)) < tol
+        val, g, gx = cnf.loss_and_grad(icnf, m, xs.T, *tail, eps=eps.T if mode else None, want_grad_x=True)
+        st = cnf.last_stats(icnf)
+        rval, rg, rgx, rst = O.loss_grad(cfg, theta, xs, ys, eps if mode else None, 0.0, 1.0, mode=mode)
+        same = st["naccept"] == rst["naccept"]
+        assert np.asarray(g).shape == (2 * nv + C + 1,)
+        assert abs(val - rval) <= (1e-4 if same else 5e-3) * abs(rval)
+        assert relnorm(np.asarray(g), rg) < (1e-3 if same else 5e-2)
+        assert relnorm(np.asarray(gx).T, rgx) < (1e-3 if same else 5e-2)
+    lp, regs, z = cnf.inference(icnf, cnf.TestMode(), xs.T, *tail, return_z=True)
+    xr = np.asarray(cnf.generate(icnf, cnf.TestMode(), *tail, B, z0=np.asarray(z))).T
+    assert np.max(np.abs(xr - xs)) < 2e-2

@@ -214,3 +214,44 @@ def test_n1_philox_known_answers_and_normal_moments():
     np.testing.assert_array_equal(O.philox_normal(99, 1000, 0, 6, 500), n[:, 1000:1500])
     assert not np.array_equal(O.philox_normal(99, 0, 1, 6, 500), n[:, :500])      # next draw
     assert not np.array_equal(O.philox_normal(98, 0, 0, 6, 500), n[:, :500])      # other seed
+
+
+def _planar_case(nvars, C, B, seed=7, **kw):
+    """PlanarLayer(nvars, tanh; n_cond = C) as the vector field (test/call_tests.jl:98-127)"""
+    rng = np.random.default_rng(seed)
+    d0 = nvars + C
+    cfg = O.make_config(nvars, 0, [d0, 1, nvars], C_=C, planar=True, **kw)
+    theta = np.concatenate([rng.normal(0, 0.8, nvars), rng.normal(0, 0.8, d0), rng.normal(0, 0.3, 1)]).astype(np.float32)
+    xs = rng.normal(0, 1, (B, nvars)).astype(np.float32)
+    ys = rng.normal(0, 1, (B, C)).astype(np.float32) if C else None
+    eps = rng.normal(0, 1, (B, nvars)).astype(np.float32)
+    return cfg, theta, xs, ys, eps
+
+
+@pytest.mark.parametrize("C", [0, 3])
+@pytest.mark.parametrize("tm", [0, 1])
+def test_n3_planar_layer_closed_form_trace(C, tm):
+    """N3: with nn = PlanarLayer the field is u * tanh(w'[z; ys] + b) (src/layers/planar_layer.jl:70-88)
+    and the exact trace has the closed form act'(.) * (w[1:D] . u)."""
+    nv, B = 5, 33
+    cfg, theta, xs, ys, eps = _planar_case(nv, C, B, trace_mode=tm)
+    u = np.concatenate([xs, np.zeros((B, 1), np.float32)], axis=1)
+    du = O.augmented_f(cfg, theta, 0, u, ys, None)
+    uu, w, b = theta[:nv].astype(np.float64), theta[nv:nv + nv + C].astype(np.float64), float(theta[-1])
+    inp = xs.astype(np.float64) if C == 0 else np.concatenate([xs, ys], axis=1).astype(np.float64)
+    a = np.tanh(inp @ w + b)
+    np.testing.assert_allclose(du[:, :nv], a[:, None] * uu[None, :], rtol=2e-5, atol=2e-6)
+    np.testing.assert_allclose(du[:, nv], -(1 - a * a) * float(w[:nv] @ uu), rtol=2e-5, atol=2e-6)
+
+
+@pytest.mark.parametrize("C,tm,mode", [(0, 0, 1), (0, 1, 1), (2, 0, 1), (0, 0, 0), (2, 1, 0)])
+def test_n3_planar_loss_gradient_vs_float64_autograd(C, tm, mode):
+    nv, B = 4, 12
+    cfg, theta, xs, ys, eps = _planar_case(nv, C, B, trace_mode=tm, lambda1=1e-2, lambda2=1e-2)
+    val, g, gx, st = O.loss_grad(cfg, theta, xs, ys, eps if mode else None, 0.0, 1.0, mode=mode)
+    dts = [float(d) for d in O.last_dts()]
+    r = F.run(cfg, theta, mode, xs, ys, eps if mode else None, 0.0, 1.0, frozen_dts=dts, requires_grad=True)
+    assert g.shape == (nv + nv + C + 1,)
+    assert abs(val - r["loss"]) / abs(r["loss"]) < 1e-5
+    assert relnorm(g, r["grad_theta"]) < 1e-4
+    assert relnorm(gx, r["grad_x"]) < 1e-4
