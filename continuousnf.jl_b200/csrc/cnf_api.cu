@@ -67,8 +67,43 @@ extern "C" int32_t cnfb200_create(const cnf_config* cfg, cnf_handle** out) {
     CNF_CUDA(cudaMalloc(&h->d_lossacc, sizeof(double)));
     CNF_CUDA(cudaMalloc(&h->d_slots, CNF_MAX_SLOTS * sizeof(float*)));
     CNF_CUDA(cudaMemset(h->d_slots, 0, CNF_MAX_SLOTS * sizeof(float*)));
+    CNF_CUDA(cudaMalloc(&h->d_ktape, CNF_MAX_SLOTS * sizeof(float*)));
+    CNF_CUDA(cudaMemset(h->d_ktape, 0, CNF_MAX_SLOTS * sizeof(float*)));
     cnf_upload_constants();
     CNF_CUDA(cudaGetLastError());
+    return CNF_OK;
+}
+
+static void free_ktape(cnf_handle* h) {
+    for (float* p : h->ktape) cudaFree(p);
+    if (!h->ktape.empty() && h->d_ktape) cudaMemset(h->d_ktape, 0, h->ktape.size() * sizeof(float*));
+    h->ktape.clear();
+    h->ktape_elems = 0;
+}
+
+// stage tape entries for steps [0, want): sized D x Bs x 5; stops growing (the reverse sweep then
+// recomputes the later steps) when less than a quarter of the device memory would stay free
+static int ensure_ktape(cnf_handle* h, size_t want, long long nz) {
+    if (h->ktape_off) return CNF_OK;
+    if (h->ktape_elems != nz) {
+        CNF_CUDA(cudaStreamSynchronize(h->stream));
+        free_ktape(h);
+        h->ktape_elems = nz;
+    }
+    if (want > CNF_MAX_SLOTS) want = CNF_MAX_SLOTS;
+    if (h->ktape.size() >= want) return CNF_OK;
+    const size_t old = h->ktape.size();
+    const size_t bytes = (size_t)5 * (size_t)nz * sizeof(float);
+    while (h->ktape.size() < want) {
+        size_t fr = 0, tot = 0;
+        if (cudaMemGetInfo(&fr, &tot) != cudaSuccess || fr < bytes + tot / 4) break;
+        float* p = nullptr;
+        if (cudaMalloc(&p, bytes) != cudaSuccess) { cudaGetLastError(); break; }
+        h->ktape.push_back(p);
+    }
+    if (h->ktape.size() > old)
+        CNF_CUDA(cudaMemcpyAsync(h->d_ktape + old, h->ktape.data() + old, (h->ktape.size() - old) * sizeof(float*),
+                                 cudaMemcpyHostToDevice, h->stream));
     return CNF_OK;
 }
 
@@ -79,6 +114,7 @@ static void free_workspaces(cnf_handle* h) {
     cudaFree(h->d_ys); h->d_ys = nullptr;
     for (float* p : h->slots) cudaFree(p);
     h->slots.clear();
+    free_ktape(h);
     for (int j = 0; j < 16; ++j) { cudaFree(h->d_bw[j]); h->d_bw[j] = nullptr; }
     h->cap_bw = 0;
     h->cap_B = 0;
@@ -96,7 +132,7 @@ extern "C" int32_t cnfb200_destroy(cnf_handle* h) {
     tc_free(h);
     cudaFree(h->d_io);
     cudaFree(h->d_theta); cudaFree(h->d_wt); cudaFree(h->d_grad);
-    cudaFree(h->d_ctrl); cudaFree(h->d_dts); cudaFree(h->d_lossacc); cudaFree(h->d_slots);
+    cudaFree(h->d_ctrl); cudaFree(h->d_dts); cudaFree(h->d_lossacc); cudaFree(h->d_slots); cudaFree(h->d_ktape);
     if (h->h_ctrl) cudaFreeHost(h->h_ctrl);
     for (cudaEvent_t e : h->stage_ev) cudaEventDestroy(e);
     if (h->ev0) cudaEventDestroy(h->ev0);
@@ -219,6 +255,7 @@ extern "C" int32_t cnfb200_set_option(cnf_handle* h, const char* key, int64_t va
     if (!h || !key) return CNF_ERR_BADARG;
     if (!strcmp(key, "time_stages")) { h->time_stages = value != 0; return CNF_OK; }
     if (!strcmp(key, "kernel_path")) { h->cfg.kernel_path = (int32_t)value; return CNF_OK; }
+    if (!strcmp(key, "stage_tape")) { h->ktape_off = value == 0; return CNF_OK; }
     if (!strcmp(key, "vector_mode")) { h->vector_mode = value != 0; return CNF_OK; }
     if (!strcmp(key, "tc_dbg")) { h->tc_dbg = (int)value; return CNF_OK; }
     if (!strcmp(key, "tc_ring")) { h->tc_noring = value == 0; return CNF_OK; }
@@ -416,7 +453,10 @@ static int solve_device(cnf_handle* h, const CnfBufs& bf, int mode, int R, long 
     int pend = -1;  // index of the pinned snapshot in flight
     for (;;) {
         if (use_tape && (long long)h->slots.size() < launched + 2 && (rc = ensure_slots(h, (size_t)(launched + 10)))) return rc;
+        if (use_tape && (long long)h->ktape.size() < launched + 2 &&
+            (rc = ensure_ktape(h, (size_t)(launched + 10), (long long)c.D * bf.Bs))) return rc;
         if ((rc = enqueue_attempt(h, bf, mode))) return rc;
+        if (use_tape && !h->ktape.empty()) launch_tape_stages(h, bf);
         launched++;
         int cur = (int)(launched & 1);
         CNF_CUDA(cudaMemcpyAsync(&h->h_ctrl[cur], h->d_ctrl, sizeof(CnfCtrl), cudaMemcpyDeviceToHost, h->stream));

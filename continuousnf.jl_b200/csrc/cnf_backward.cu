@@ -331,12 +331,17 @@ static int backward_sweep(cnf_handle* h, const CnfBufs& bf, int mode, long long 
     for (long long n = naccept - 1; n >= 0; --n) {
         const float* un = h->slots[n];
         const float* dtp = h->d_dts + n;
-        // stage checkpointing: recompute k_1..k_5 and the stage inputs s_2..s_6 of step n
-        if ((rc = bw_eval(h, bf, mode, un, h->d_K[0]))) return rc;
+        // the stage inputs s_2..s_6 of step n: from the taped k_1..k_5 of the forward solve when the step
+        // has a tape entry, else stage checkpointing (recompute k_1..k_5 from u_n)
+        const bool taped = !h->ktape_off && h->ktape_elems == nz && n < (long long)h->ktape.size();
+        CnfBufs bk = bf;
+        if (taped)
+            for (int j = 0; j < 5; ++j) bk.K[j] = h->ktape[(size_t)n] + (long long)j * nz;
+        else if ((rc = bw_eval(h, bf, mode, un, h->d_K[0]))) return rc;
         for (int i = 1; i <= 5; ++i) {
-            k_combine_bw<<<bw_grid(nz), CNF_NT, 0, h->stream>>>(un, bf, i, dtp, w[i - 1], nz);
+            k_combine_bw<<<bw_grid(nz), CNF_NT, 0, h->stream>>>(un, bk, i, dtp, w[i - 1], nz);
             h->launches++;
-            if (i < 5 && (rc = bw_eval(h, bf, mode, w[i - 1], h->d_K[i]))) return rc;
+            if (!taped && i < 5 && (rc = bw_eval(h, bf, mode, w[i - 1], h->d_K[i]))) return rc;
         }
         k_kbar_init<<<bw_grid(nz), CNF_NT, 0, h->stream>>>(ubar, dtp, kb[0], kb[1], kb[2], kb[3], kb[4], kb[5], nz);
         h->launches++;

@@ -20,6 +20,7 @@ struct CnfCtrl {
     long long iter, maxiters, naccept, nreject, nf;
     float t, dt, t0, t1, tdir, dtmax, dtmin, reltol, abstol, dt_last, dt0init;
     int done, retcode, k1idx, use_tape, R, D;
+    int accepted;        // the attempt the controller has just judged was accepted (k_tape_stages)
 };
 
 // Network description passed by value to kernels.

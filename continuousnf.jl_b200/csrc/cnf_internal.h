@@ -42,6 +42,10 @@ struct cnf_handle {
     std::vector<float*> slots;  // state slots allocated so far
     long long slot_elems = 0;
     float** d_slots = nullptr;  // device table [CNF_MAX_SLOTS]
+    std::vector<float*> ktape;  // per accepted step: z rows of k_1..k_5 (5 x D x Bs), reverse sweep only
+    float** d_ktape = nullptr;  // device table [CNF_MAX_SLOTS]
+    long long ktape_elems = 0;  // D * Bs the entries were sized for
+    bool ktape_off = false;     // option stage_tape = 0: always recompute
     // backward workspaces
     float* d_bw[16] = {};
     long long cap_bw = 0;
@@ -81,6 +85,7 @@ void stage_timer_end(cnf_handle* h);
 void cnf_upload_constants();
 bool narrow_shape(const cnf_config& c);
 int vector_solve(cnf_handle* h, const CnfBufs& bf, float t0, float t1, CnfCtrl* out);
+void launch_tape_stages(cnf_handle* h, const CnfBufs& bf);
 void launch_philox_normal(cnf_handle* h, float* out, long long Bs, long long B, int rows, uint32_t draw);
 void launch_pack_rows(cnf_handle* h, const float* src, int rows, long long B, float* dst, long long Bs);
 void launch_unpack_rows(cnf_handle* h, const float* src, int rows, long long B, long long Bs, float* dst);

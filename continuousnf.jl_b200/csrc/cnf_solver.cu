@@ -126,6 +126,7 @@ __device__ void begin_attempt(CnfCtrl* c) {
 }
 
 __global__ void k_controller(CnfCtrl* c, float* __restrict__ dts) {
+    c->accepted = 0;
     if (c->done) return;
     const double es = c->errsum;
     c->errsum = 0.0;
@@ -150,6 +151,7 @@ __global__ void k_controller(CnfCtrl* c, float* __restrict__ dts) {
         c->dt_last = c->dt;
         c->dt = (float)((double)c->dt / q);
         c->naccept++;              // the candidate slot becomes the current state
+        c->accepted = 1;
         if (c->use_tape && c->naccept >= CNF_MAX_SLOTS - 1 && c->t != c->t1) {
             c->retcode = CNF_RET_MAXITERS;
             c->done = 1;
@@ -161,6 +163,32 @@ __global__ void k_controller(CnfCtrl* c, float* __restrict__ dts) {
     }
     begin_attempt(c);
 }
+// Stage tape for the reverse sweep: after an accepted step the z rows of k_1..k_5 (all the stage
+// inputs s_2..s_6 of that step are u_n + dt * sum a_ij k_j) are kept, so the sweep does not have to
+// recompute five vector-field evaluations per step.  ktape[n] = 5 x D x Bs floats, or null (then the
+// sweep recomputes that step).
+__global__ void k_tape_stages(const CnfCtrl* __restrict__ c, CnfBufs bf, float* const* __restrict__ ktape, long long nz,
+                              long long cap) {
+    if (!c->accepted) return;
+    const long long n = c->naccept - 1;
+    if (n < 0 || n >= cap) return;
+    float* dst = ktape[n];
+    if (!dst) return;
+    const float* k1 = bf.K[6 - c->k1idx];   // the controller has already swapped k1/k7 for the next step
+    const long long n4 = nz >> 2;            // Bs is a multiple of 256
+    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n4; e += (long long)gridDim.x * blockDim.x) {
+        reinterpret_cast<float4*>(dst)[e] = reinterpret_cast<const float4*>(k1)[e];
+#pragma unroll
+        for (int j = 1; j < 5; ++j)
+            reinterpret_cast<float4*>(dst + j * nz)[e] = reinterpret_cast<const float4*>(bf.K[j])[e];
+    }
+}
+void launch_tape_stages(cnf_handle* h, const CnfBufs& bf) {
+    const long long nz = (long long)h->cfg.D * bf.Bs;
+    k_tape_stages<<<grid_for(nz >> 2), CNF_NT, 0, h->stream>>>(h->d_ctrl, bf, h->d_ktape, nz, (long long)h->ktape.size());
+    h->launches++;
+}
+
 void launch_controller(cnf_handle* h) {
     k_controller<<<1, 1, 0, h->stream>>>(h->d_ctrl, h->d_dts);
     h->launches++;

@@ -417,3 +417,20 @@ def test_n3_planar_flow_matches_oracle(C, trace_mode):
     lp, regs, z = cnf.inference(icnf, cnf.TestMode(), xs.T, *tail, return_z=True)
     xr = np.asarray(cnf.generate(icnf, cnf.TestMode(), *tail, B, z0=np.asarray(z))).T
     assert np.max(np.abs(xr - xs)) < 2e-2
+
+
+@pytest.mark.parametrize("cid,B,tol", [("C1", 700, 1e-5), ("C0", 64, 1e-5), ("C3", 300, 3e-4), ("C4", 1500, 3e-4)])
+def test_stage_tape_matches_stage_recompute(cid, B, tol):
+    """the reverse sweep reads the stage derivatives k_1..k_5 the forward solve taped (default) or
+    recomputes them from u_n (stage_tape = 0): same gradient"""
+    inp = wl.make_inputs(cid, B=B)
+    out = []
+    for tape in (1, 0):
+        icnf = make_icnf(cid)
+        cnf.set_option(icnf, "stage_tape", tape)
+        val, g, gx = cnf.loss_and_grad(icnf, cnf.TrainMode(), inp["xs"].T, *args_of(inp), eps=inp["eps"].T, want_grad_x=True)
+        out.append((val, np.asarray(g), np.asarray(gx), cnf.last_stats(icnf)["gpu_launches"]))
+    assert out[0][0] == out[1][0]
+    assert relnorm(out[0][1], out[1][1]) < tol
+    assert relnorm(out[0][2], out[1][2]) < tol
+    assert out[0][3] < out[1][3]          # fewer launches: no recomputed evaluations
