@@ -26,7 +26,7 @@
 #define TC_BM 128
 #define TC_BK 64            // bf16 elements per 128-byte swizzled row
 #define TC_THREADS 480      // 15 warps: TMA, MMA, 12 epilogue, epilogue-operand producer
-#define TC_AUX_WARP 14
+#define TC_THREADS_WIDE 736 // TC_FWD_HIDDEN: 20 epilogue warps (its tanh + split epilogue is issue-latency-bound, 76 registers)
 #define TC_EPI_WARP0 2
 
 enum {
@@ -298,20 +298,20 @@ __device__ __forceinline__ float2 tc_quad_reduce(TcSmemCtl* ctl, int quad, int s
 // ---- forward-solve epilogue of one 128 x BN tile (kinds TC_*); cur = aux of this warp's first chunk
 template <int PREC, int KIND, bool RING>
 __device__ __forceinline__ void tc_epilogue_fwd(const TcEpi& ep, TcSmemCtl* ctl, uint32_t tbase, int mb, int nb, int BN,
-                                                int quad, int sub, int lane, int par, TcAux& cur, TcRing& ring) {
+                                                int quad, int sub, int nsub, int lane, int par, TcAux& cur, TcRing& ring) {
     const long long rloc = (long long)mb * TC_BM + quad * 32 + lane;   // row inside the chunk
     const long long grow = ep.row0 + rloc;                               // global sample
     constexpr bool last_kind = (KIND == TC_FWD_LAST || KIND == TC_BWD_LAST || KIND == TC_JVP_LAST);
     const int nchunk = (BN + TC_CW - 1) / TC_CW;
     const int nmax = last_kind ? ep.D : ep.N;
     float s0 = 0.0f, s1 = 0.0f;
-    for (int ch = sub; ch < nchunk; ch += TC_NSUB) {
+    for (int ch = sub; ch < nchunk; ch += nsub) {
         const int c0 = ch * TC_CW, ng = nb * BN + c0;   // global column of v[0]
         if (ng >= nmax) break;
         TcAux nxt;
         if (RING) tc_ring_read<false>(ctl, ring, sub, quad * 32 + lane, lane, cur);
-        else if (ch + TC_NSUB < nchunk && ng + TC_NSUB * TC_CW < nmax)
-            tc_aux_load<PREC, false, KIND>(ep, rloc, grow, ng + TC_NSUB * TC_CW, nxt);
+        else if (ch + nsub < nchunk && ng + nsub * TC_CW < nmax)
+            tc_aux_load<PREC, false, KIND>(ep, rloc, grow, ng + nsub * TC_CW, nxt);
         uint32_t v[TC_CW];
         tc::tmem_ld_32x16(tbase + c0, v);
         tc::tmem_ld_wait();
@@ -509,7 +509,7 @@ __device__ __forceinline__ void tc_epilogue_bwd(const TcEpi& ep, TcSmemCtl* ctl,
 // BM x BN output tile per (m_blk, n_blk); K in blocks of 64 bf16; persistent over tiles.
 // PREC = operand format of the two hi/lo planes (0: IEEE half, forward solve; 1: bfloat16, reverse sweep).
 template <int PREC, bool BWD, int KIND, bool RING>
-__global__ void __launch_bounds__(TC_THREADS, 1)
+__global__ void __launch_bounds__((!BWD && KIND == TC_FWD_HIDDEN) ? TC_THREADS_WIDE : TC_THREADS, 1)
 k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, int nk, int nstage, int naux, TcEpi ep) {
     if (ep.ctrl && ep.ctrl->done) return;
     if (ep.kout_ind) ep.kout = *ep.kout_ind;
@@ -523,11 +523,13 @@ k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, i
     TcSmemCtl* ctl = reinterpret_cast<TcSmemCtl*>(ring_base + (RING ? (size_t)TC_NSUB * naux * slot_bytes : 0));   // naux = slots per warp group
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int total = m_tiles * n_tiles;
+    const int nsub = (((int)blockDim.x >> 5) - 3) >> 2;   // epilogue warps per TMEM lane quadrant (3, or 5 for TC_FWD_HIDDEN)
+    const int aux_warp = TC_EPI_WARP0 + 4 * nsub;         // the last warp
 
     if (warp == 0 && lane == 0) {
         for (int q = 0; q < 2; ++q) { tc::tma_prefetch_desc(&mp.a[q]); tc::tma_prefetch_desc(&mp.b[q]); }
         for (int s = 0; s < nstage; ++s) { tc::mbar_init(&ctl->full[s], 1); tc::mbar_init(&ctl->empty[s], 1); }
-        for (int a = 0; a < 2; ++a) { tc::mbar_init(&ctl->tfull[a], 1); tc::mbar_init(&ctl->tempty[a], 4 * TC_NSUB); }
+        for (int a = 0; a < 2; ++a) { tc::mbar_init(&ctl->tfull[a], 1); tc::mbar_init(&ctl->tempty[a], 4 * nsub); }
         if (RING)
             for (int x = 0; x < TC_NSUB * naux; ++x) { tc::mbar_init(&ctl->xfull[x], 1); tc::mbar_init(&ctl->xempty[x], 4); }
         tc::fence_barrier_init();
@@ -586,7 +588,7 @@ k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, i
                 tc::umma_commit(&ctl->tfull[acc]);
             }
         }
-    } else if (warp == TC_AUX_WARP) {
+    } else if (warp == aux_warp) {
         if (RING && lane == 0) {   // ===== epilogue-operand producer: chunk c of a tile goes to the warps with sub = c % 3
             uint32_t j[TC_NSUB] = {0, 0, 0};
             for (int t = blockIdx.x; t < total; t += gridDim.x) {
@@ -625,7 +627,7 @@ k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, i
             tc::tc_fence_after();
             const uint32_t tbase = tmem + ((uint32_t)(quad * 32) << 16) + (uint32_t)acc * 256;
             if (BWD) tc_epilogue_bwd<KIND, RING>(ep, ctl, tbase, mb, nb, BN, quad, sub, lane, it & 1, aux, ring);
-            else tc_epilogue_fwd<PREC, KIND, RING>(ep, ctl, tbase, mb, nb, BN, quad, sub, lane, it & 1, aux, ring);
+            else tc_epilogue_fwd<PREC, KIND, RING>(ep, ctl, tbase, mb, nb, BN, quad, sub, nsub, lane, it & 1, aux, ring);
             tc::tc_fence_before();
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(&ctl->tempty[acc]);
@@ -927,7 +929,8 @@ static void tc_launch_kind(cnf_handle* h, int grid, int smem, const TcMaps& mp, 
             cudaFuncSetAttribute(k_tc_gemm<PREC, BWD, KIND, RING>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
             attr = true;
         }
-        k_tc_gemm<PREC, BWD, KIND, RING><<<grid, TC_THREADS, smem, h->stream>>>(mp, m_tiles, n_tiles, BN, nk, nstage, naux, ep);
+        constexpr int threads = (!BWD && KIND == TC_FWD_HIDDEN) ? TC_THREADS_WIDE : TC_THREADS;
+        k_tc_gemm<PREC, BWD, KIND, RING><<<grid, threads, smem, h->stream>>>(mp, m_tiles, n_tiles, BN, nk, nstage, naux, ep);
     }
 }
 
