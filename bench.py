@@ -163,7 +163,7 @@ def run_reference(args, cnf):
         "e2e": {"value": val, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def main():
@@ -364,10 +364,30 @@ def main():
         dt = (time.perf_counter() - t0) / reps
         line["cpu_baseline"] = {"value": Bs / dt, "unit": unit, "cores": O.num_threads(), "kind": "port",
                                 "sample": f"{Bs} of {B} samples, {reps} repetitions, same synthetic stream"}
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+_REAL_STDOUT = None
+
+
+def _own_stdout():
+    """the contract is ONE JSON line on stdout: everything native libraries print there (e.g. NCCL's
+    version banner under NCCL_DEBUG) is sent to stderr, the line itself goes to the saved descriptor"""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    sys.stdout.flush()
+    data = (json.dumps(line) + "\n").encode()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, data)
+
+
 if __name__ == "__main__":
+    _own_stdout()
     main()
