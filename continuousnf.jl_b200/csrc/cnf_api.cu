@@ -255,6 +255,7 @@ extern "C" int32_t cnfb200_set_option(cnf_handle* h, const char* key, int64_t va
     if (!h || !key) return CNF_ERR_BADARG;
     if (!strcmp(key, "time_stages")) { h->time_stages = value != 0; return CNF_OK; }
     if (!strcmp(key, "kernel_path")) { h->cfg.kernel_path = (int32_t)value; return CNF_OK; }
+    if (!strcmp(key, "tile_solve")) { h->tile_off = value == 0; return CNF_OK; }
     if (!strcmp(key, "stage_tape")) { h->ktape_off = value == 0; return CNF_OK; }
     if (!strcmp(key, "vector_mode")) { h->vector_mode = value != 0; return CNF_OK; }
     if (!strcmp(key, "tc_dbg")) { h->tc_dbg = (int)value; return CNF_OK; }
@@ -448,6 +449,12 @@ static int solve_device(cnf_handle* h, const CnfBufs& bf, int mode, int R, long 
         if (h->nranks > 1 && (rc = cnf_nccl_allreduce_f64(h, h->d_ctrl->initsum + 2, 1))) return rc;
         launch_initdt(h, 1);
     }
+    if (!nar && !tcp && tile_solve_ok(h, mode, bf.B)) {
+        // one-tile batch: the whole attempt loop runs inside one single-CTA kernel (cnf_tile.cu)
+        CnfCtrl tmp;
+        if ((rc = tile_solve(h, bf, mode, use_tape, ic.maxiters, &tmp))) return rc;
+        h->path_used = 5;
+    } else {
     // attempts are enqueued speculatively; kernels of attempts after `done` return immediately
     long long launched = 0;
     int pend = -1;  // index of the pinned snapshot in flight
@@ -467,6 +474,7 @@ static int solve_device(cnf_handle* h, const CnfBufs& bf, int mode, int R, long 
         }
         pend = cur;
         if (launched > ic.maxiters + 2) break;
+    }
     }
     CNF_CUDA(cudaEventRecord(h->ev2, h->stream));
     CNF_CUDA(cudaMemcpyAsync(&h->h_ctrl[0], h->d_ctrl, sizeof(CnfCtrl), cudaMemcpyDeviceToHost, h->stream));

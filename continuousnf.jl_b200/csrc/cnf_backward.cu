@@ -68,11 +68,10 @@ __device__ __forceinline__ void bias_acc_tile(float* __restrict__ gb, int dout, 
 #define EW_AT (((idx / TB) * TBP) + (idx % TB))
 
 template <int TB>
-__global__ void __launch_bounds__(CNF_NT)
-k_vjp_generic(CnfBufs bf, CnfNet net, BwLayout lay, const float* __restrict__ src,
-              const float* __restrict__ abar, int stage, const float* __restrict__ dtp, float c_l,
-              float c_E, float c_n, float* __restrict__ ubar, float* kb0, float* kb1, float* kb2,
-              float* kb3, float* kb4, float* __restrict__ grad, int unit) {
+__device__ __forceinline__ void d_vjp_generic(const CnfBufs& bf, const CnfNet& net, const BwLayout& lay, const float* src,
+                                              const float* abar, int stage, const float* dtp, float c_l,
+                                              float c_E, float c_n, float* ubar, float* kb0, float* kb1, float* kb2,
+                                              float* kb3, float* kb4, float* grad, int unit) {
     extern __shared__ float sm[];
     constexpr int TBP = TB + 1;
     const int D = net.D, L = net.L;
@@ -242,9 +241,16 @@ k_vjp_generic(CnfBufs bf, CnfNet net, BwLayout lay, const float* __restrict__ sr
     }
 }
 
+template <int TB>
+__global__ void __launch_bounds__(CNF_NT)
+k_vjp_generic(CnfBufs bf, CnfNet net, BwLayout lay, const float* src, const float* abar, int stage, const float* dtp, float c_l,
+              float c_E, float c_n, float* ubar, float* kb0, float* kb1, float* kb2, float* kb3, float* kb4, float* grad,
+              int unit) {
+    d_vjp_generic<TB>(bf, net, lay, src, abar, stage, dtp, c_l, c_E, c_n, ubar, kb0, kb1, kb2, kb3, kb4, grad, unit);
+}
+
 // recompute helper: out = u + dt * sum_{j<stage} a[stage][j] K[j]   (D rows)
-__global__ void k_combine_bw(const float* __restrict__ u, CnfBufs bf, int stage,
-                             const float* __restrict__ dtp, float* __restrict__ out, long long n) {
+__device__ __forceinline__ void d_combine_bw(const float* u, const CnfBufs& bf, int stage, const float* dtp, float* out, long long n) {
     const float dt = *dtp;
     for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n;
          e += (long long)gridDim.x * blockDim.x) {
@@ -254,10 +260,13 @@ __global__ void k_combine_bw(const float* __restrict__ u, CnfBufs bf, int stage,
     }
 }
 
+__global__ void k_combine_bw(const float* u, CnfBufs bf, int stage, const float* dtp, float* out, long long n) {
+    d_combine_bw(u, bf, stage, dtp, out, n);
+}
+
 // kb_j = dt * a7j * ubar, j = 0..5
-__global__ void k_kbar_init(const float* __restrict__ ubar, const float* __restrict__ dtp,
-                            float* kb0, float* kb1, float* kb2, float* kb3, float* kb4, float* kb5,
-                            long long n) {
+__device__ __forceinline__ void d_kbar_init(const float* ubar, const float* dtp, float* kb0, float* kb1, float* kb2, float* kb3,
+                                            float* kb4, float* kb5, long long n) {
     const float dt = *dtp;
     float* kb[6] = {kb0, kb1, kb2, kb3, kb4, kb5};
     for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n;
@@ -266,6 +275,11 @@ __global__ void k_kbar_init(const float* __restrict__ ubar, const float* __restr
 #pragma unroll
         for (int j = 0; j < 6; ++j) kb[j][e] = dt * c_A[6][j] * ub;
     }
+}
+
+__global__ void k_kbar_init(const float* ubar, const float* dtp, float* kb0, float* kb1, float* kb2, float* kb3, float* kb4,
+                            float* kb5, long long n) {
+    d_kbar_init(ubar, dtp, kb0, kb1, kb2, kb3, kb4, kb5, n);
 }
 
 template <int TB>
@@ -327,6 +341,7 @@ static int backward_sweep(cnf_handle* h, const CnfBufs& bf, int mode, long long 
     const bool train = mode == CNF_MODE_TRAIN;
     const float c_l = invB, c_E = train ? c.lambda1 * invB : 0.0f, c_n = train ? c.lambda2 * invB : 0.0f;
     int rc;
+    if (tile_sweep(h, bf, mode, naccept, Bglobal)) return CNF_OK;   // one-tile batch: the whole sweep in one launch
     const bool tcb = train && tc_bw_supported(h);
     for (long long n = naccept - 1; n >= 0; --n) {
         const float* un = h->slots[n];

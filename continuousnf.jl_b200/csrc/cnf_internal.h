@@ -31,6 +31,7 @@ struct cnf_handle {
     float* d_S = nullptr;
     float* d_eps = nullptr;
     // N1: on-device eps / z0 (cnf_rng.cu)
+    bool tile_off = false;       // option tile_solve = 0: never use the single-CTA whole-solve kernels (cnf_tile.cu)
     bool vector_mode = false;    // N4: per-sample step control (cnf_vector.cu)
     bool rng_on = false;
     unsigned long long rng_seed = 0, rng_offset = 0;
@@ -84,6 +85,9 @@ void stage_timer_end(cnf_handle* h);
 // ---- cnf_solver.cu
 void cnf_upload_constants();
 bool narrow_shape(const cnf_config& c);
+bool tile_solve_ok(cnf_handle* h, int mode, long long B);
+int tile_solve(cnf_handle* h, const CnfBufs& bf, int mode, bool use_tape, long long maxiters, CnfCtrl* out);
+bool tile_sweep(cnf_handle* h, const CnfBufs& bf, int mode, long long naccept, long long Bglobal);
 int vector_solve(cnf_handle* h, const CnfBufs& bf, float t0, float t1, CnfCtrl* out);
 void launch_tape_stages(cnf_handle* h, const CnfBufs& bf);
 void launch_philox_normal(cnf_handle* h, float* out, long long Bs, long long B, int rows, uint32_t draw);

@@ -10,4 +10,5 @@
 #include "cnf_rng.cu"
 #include "cnf_nccl.cu"
 #include "cnf_api.cu"
+#include "cnf_tile.cu"
 #include "cnf_fit.cu"

@@ -45,7 +45,10 @@ void launch_unpack_rows(cnf_handle* h, const float* src, int rows, long long B, 
 // ---------------------------------------------------------------- RK combination (generic path)
 // stage s in 1..5: S = u + dt*sum_{j<s+... } a[s][j] k_j on the D z rows (f reads only those);
 // stage 6: unew = u + dt*sum a7j k_j on all R rows; stage -1: S = u + tdir*dt0init*k1 (init probe).
-__global__ void k_combine(const CnfCtrl* __restrict__ c, CnfBufs bf, int stage, int also_S) {
+// (device bodies d_*: the same code runs as its own launch and, for batches of one tile, inside the
+// single-CTA whole-solve kernels of cnf_tile.cu, where the control block and the buffers change while
+// the kernel runs — hence no __restrict__/read-only loads on them)
+__device__ __forceinline__ void d_combine(const CnfCtrl* c, const CnfBufs& bf, int stage, int also_S) {
     if (c->done) return;
     const int nrows = (stage == 6) ? c->R : c->D;
     const long long n = (long long)nrows * bf.Bs;
@@ -65,6 +68,7 @@ __global__ void k_combine(const CnfCtrl* __restrict__ c, CnfBufs bf, int stage, 
         }
     }
 }
+__global__ void k_combine(const CnfCtrl* c, CnfBufs bf, int stage, int also_S) { d_combine(c, bf, stage, also_S); }
 static inline unsigned grid_for(long long n) {
     long long g = (n + CNF_NT - 1) / CNF_NT;
     if (g > 148LL * 16) g = 148LL * 16;
@@ -77,7 +81,7 @@ void launch_combine(cnf_handle* h, const CnfBufs& bf, int stage, int also_S) {
 }
 
 // ---------------------------------------------------------------- embedded error norm (A.3)
-__global__ void k_errnorm(CnfCtrl* __restrict__ c, CnfBufs bf) {
+__device__ __forceinline__ void d_errnorm(CnfCtrl* c, const CnfBufs& bf) {
     if (c->done) return;
     __shared__ double sh[32];
     const int R = c->R;
@@ -104,6 +108,7 @@ __global__ void k_errnorm(CnfCtrl* __restrict__ c, CnfBufs bf) {
     acc = cnf_block_sum(acc, sh);
     if (threadIdx.x == 0) atomicAdd(&c->errsum, acc);
 }
+__global__ void k_errnorm(CnfCtrl* c, CnfBufs bf) { d_errnorm(c, bf); }
 void launch_errnorm(cnf_handle* h, const CnfBufs& bf) {
     k_errnorm<<<grid_for((long long)h->cur_R * bf.Bs), CNF_NT, 0, h->stream>>>(h->d_ctrl, bf);
     h->launches++;
@@ -125,7 +130,7 @@ __device__ void begin_attempt(CnfCtrl* c) {
     }
 }
 
-__global__ void k_controller(CnfCtrl* c, float* __restrict__ dts) {
+__device__ __forceinline__ void d_controller(CnfCtrl* c, float* dts) {
     c->accepted = 0;
     if (c->done) return;
     const double es = c->errsum;
@@ -167,8 +172,7 @@ __global__ void k_controller(CnfCtrl* c, float* __restrict__ dts) {
 // inputs s_2..s_6 of that step are u_n + dt * sum a_ij k_j) are kept, so the sweep does not have to
 // recompute five vector-field evaluations per step.  ktape[n] = 5 x D x Bs floats, or null (then the
 // sweep recomputes that step).
-__global__ void k_tape_stages(const CnfCtrl* __restrict__ c, CnfBufs bf, float* const* __restrict__ ktape, long long nz,
-                              long long cap) {
+__device__ __forceinline__ void d_tape_stages(const CnfCtrl* c, const CnfBufs& bf, float* const* ktape, long long nz, long long cap) {
     if (!c->accepted) return;
     const long long n = c->naccept - 1;
     if (n < 0 || n >= cap) return;
@@ -183,12 +187,16 @@ __global__ void k_tape_stages(const CnfCtrl* __restrict__ c, CnfBufs bf, float* 
             reinterpret_cast<float4*>(dst + j * nz)[e] = reinterpret_cast<const float4*>(bf.K[j])[e];
     }
 }
+__global__ void k_tape_stages(const CnfCtrl* c, CnfBufs bf, float* const* ktape, long long nz, long long cap) {
+    d_tape_stages(c, bf, ktape, nz, cap);
+}
 void launch_tape_stages(cnf_handle* h, const CnfBufs& bf) {
     const long long nz = (long long)h->cfg.D * bf.Bs;
     k_tape_stages<<<grid_for(nz >> 2), CNF_NT, 0, h->stream>>>(h->d_ctrl, bf, h->d_ktape, nz, (long long)h->ktape.size());
     h->launches++;
 }
 
+__global__ void k_controller(CnfCtrl* c, float* dts) { d_controller(c, dts); }
 void launch_controller(cnf_handle* h) {
     k_controller<<<1, 1, 0, h->stream>>>(h->d_ctrl, h->d_dts);
     h->launches++;

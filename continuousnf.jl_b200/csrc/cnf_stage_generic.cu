@@ -129,9 +129,8 @@ __device__ float* gen_jvp_chain(const CnfNet& net, const GenLayout& lay, float* 
 }
 
 template <int TB>
-__global__ void __launch_bounds__(CNF_NT)
-k_eval_generic(const CnfCtrl* __restrict__ c, CnfBufs bf, CnfNet net, GenLayout lay, int mode,
-               int src_sel, const float* src_ptr, int kidx, float* kout_ptr, int check_done) {
+__device__ __forceinline__ void d_eval_generic(const CnfCtrl* c, const CnfBufs& bf, const CnfNet& net, const GenLayout& lay, int mode,
+                                               int src_sel, const float* src_ptr, int kidx, float* kout_ptr, int check_done) {
     if (check_done && c->done) return;
     extern __shared__ float sm[];
     constexpr int TBP = TB + 1;
@@ -231,6 +230,13 @@ k_eval_generic(const CnfCtrl* __restrict__ c, CnfBufs bf, CnfNet net, GenLayout 
             }
         }
     }
+}
+
+template <int TB>
+__global__ void __launch_bounds__(CNF_NT)
+k_eval_generic(const CnfCtrl* c, CnfBufs bf, CnfNet net, GenLayout lay, int mode,
+               int src_sel, const float* src_ptr, int kidx, float* kout_ptr, int check_done) {
+    d_eval_generic<TB>(c, bf, net, lay, mode, src_sel, src_ptr, kidx, kout_ptr, check_done);
 }
 
 static int pick_tb(int total_floats_per_tbp /*rows*/, int* smem_bytes) {

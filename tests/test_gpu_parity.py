@@ -434,3 +434,31 @@ def test_stage_tape_matches_stage_recompute(cid, B, tol):
     assert relnorm(out[0][1], out[1][1]) < tol
     assert relnorm(out[0][2], out[1][2]) < tol
     assert out[0][3] < out[1][3]          # fewer launches: no recomputed evaluations
+
+
+@pytest.mark.parametrize("cid,B", [("C1", 32), ("C0", 20), ("C1", 7)])
+def test_one_tile_batches_run_in_whole_solve_kernels_with_identical_results(cid, B):
+    """batches that fit one tile of the generic kernel (the reference's default batch_size = 32) run the
+    attempt loop and the reverse sweep inside single-CTA kernels: same device code, so the results
+    equal the launch-per-stage path, in a handful of launches instead of hundreds"""
+    inp = wl.make_inputs(cid, B=B)
+    res = []
+    for tile in (1, 0):
+        icnf = make_icnf(cid)
+        cnf.set_option(icnf, "tile_solve", tile)
+        lp, regs, z = cnf.inference(icnf, cnf.TrainMode(), inp["xs"].T, *args_of(inp), eps=inp["eps"].T, return_z=True)
+        st_i = cnf.last_stats(icnf)
+        val, g, gx = cnf.loss_and_grad(icnf, cnf.TrainMode(), inp["xs"].T, *args_of(inp), eps=inp["eps"].T, want_grad_x=True)
+        st_g = cnf.last_stats(icnf)
+        lpt, _ = cnf.inference(icnf, cnf.TestMode(), inp["xs"].T, *args_of(inp))
+        vt, gt = cnf.loss_and_grad(icnf, cnf.TestMode(), inp["xs"].T, *args_of(inp))
+        res.append((np.asarray(lp), np.asarray(z), val, np.asarray(g), np.asarray(gx), np.asarray(lpt), vt, np.asarray(gt), st_i, st_g))
+    a, b = res
+    np.testing.assert_array_equal(a[0], b[0])
+    np.testing.assert_array_equal(a[1], b[1])
+    assert a[2] == b[2] and a[6] == b[6]
+    np.testing.assert_array_equal(a[5], b[5])
+    assert relnorm(a[3], b[3]) < 1e-5 and relnorm(a[4], b[4]) < 1e-5 and relnorm(a[7], b[7]) < 1e-5
+    assert a[8]["kernel_path"] == 5 and b[8]["kernel_path"] == 1
+    assert a[8]["naccept"] == b[8]["naccept"] and a[9]["naccept"] == b[9]["naccept"]
+    assert a[9]["gpu_launches"] < 30 < b[9]["gpu_launches"]
