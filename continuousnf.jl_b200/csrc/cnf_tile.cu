@@ -11,7 +11,17 @@
 // identical to the multi-launch path.  Conditions: one rank, generic path, B <= tile width, stage tape.
 #include "cnf_internal.h"
 
-template <int TB>
+#include <cooperative_groups.h>
+
+// launch boundary of the per-stage path: a block barrier for one tile, a grid barrier (cooperative launch,
+// one CTA per tile, all co-resident) for several
+template <bool COOP>
+__device__ __forceinline__ void tile_sync() {
+    if (COOP) cooperative_groups::this_grid().sync();
+    else __syncthreads();
+}
+
+template <int TB, bool COOP>
 __global__ void __launch_bounds__(CNF_NT)
 k_solve_tile(CnfCtrl* c, CnfBufs bf, CnfNet net, GenLayout lay, int mode, float* dts, float* const* ktape, long long nz,
              long long ktape_cap, long long slot_cap, int max_attempts) {
@@ -20,21 +30,21 @@ k_solve_tile(CnfCtrl* c, CnfBufs bf, CnfNet net, GenLayout lay, int mode, float*
         if (c->use_tape && c->naccept + 2 >= slot_cap) break;   // the host grows the tape and relaunches
         for (int i = 1; i <= 5; ++i) {
             d_combine(c, bf, i, 0);
-            __syncthreads();
+            tile_sync<COOP>();
             d_eval_generic<TB>(c, bf, net, lay, mode, SRC_S, nullptr, i, nullptr, 1);
-            __syncthreads();
+            tile_sync<COOP>();
         }
         d_combine(c, bf, 6, 0);
-        __syncthreads();
+        tile_sync<COOP>();
         d_eval_generic<TB>(c, bf, net, lay, mode, SRC_UNEW, nullptr, 6, nullptr, 1);
-        __syncthreads();
+        tile_sync<COOP>();
         d_errnorm(c, bf);
-        __syncthreads();
-        if (threadIdx.x == 0) d_controller(c, dts);
-        __syncthreads();
+        tile_sync<COOP>();
+        if (blockIdx.x == 0 && threadIdx.x == 0) d_controller(c, dts);
+        tile_sync<COOP>();
         if (ktape) {
             d_tape_stages(c, bf, ktape, nz, ktape_cap);
-            __syncthreads();
+            tile_sync<COOP>();
         }
     }
 }
@@ -55,7 +65,7 @@ struct SweepArgs {
     int train, D;
 };
 
-template <int TB>
+template <int TB, bool COOP>
 __global__ void __launch_bounds__(CNF_NT)
 k_sweep_tile(CnfBufs bf, CnfNet net, BwLayout lay, SweepArgs sa) {
     for (long long n = sa.naccept - 1; n >= 0; --n) {
@@ -65,18 +75,18 @@ k_sweep_tile(CnfBufs bf, CnfNet net, BwLayout lay, SweepArgs sa) {
         for (int j = 0; j < 5; ++j) bk.K[j] = sa.ktape[n] + (long long)j * sa.nz;
         for (int i = 1; i <= 5; ++i) d_combine_bw(un, bk, i, dtp, sa.w[i - 1], sa.nz);
         d_kbar_init(sa.ubar, dtp, sa.kb[0], sa.kb[1], sa.kb[2], sa.kb[3], sa.kb[4], sa.kb[5], sa.nz);
-        __syncthreads();
+        tile_sync<COOP>();
         for (int i = 5; i >= 0; --i) {
             const float* src = (i == 0) ? un : sa.w[i - 1];
             if (sa.train) {
                 d_vjp_generic<TB>(bf, net, lay, src, sa.kb[i], i, dtp, sa.c_l, sa.c_E, sa.c_n, sa.ubar, sa.kb[0], sa.kb[1],
                                   sa.kb[2], sa.kb[3], sa.kb[4], sa.grad, -1);
-                __syncthreads();
+                tile_sync<COOP>();
             } else {
                 for (int unit = 0; unit < sa.D; ++unit) {
                     d_vjp_generic<TB>(bf, net, lay, src, sa.kb[i], i, dtp, sa.c_l, 0.0f, 0.0f, sa.ubar, sa.kb[0], sa.kb[1],
                                       sa.kb[2], sa.kb[3], sa.kb[4], sa.grad, unit);
-                    __syncthreads();
+                    tile_sync<COOP>();
                 }
             }
         }
@@ -87,34 +97,75 @@ k_sweep_tile(CnfBufs bf, CnfNet net, BwLayout lay, SweepArgs sa) {
 static int tile_tb_eval(const cnf_config& c, int* smem) { return pick_tb(gen_layout(c, 0).total, smem); }
 static int tile_tb_bw(const cnf_config& c, int* smem) { return pick_tb(bw_layout(c, 0).total, smem); }
 
+// the whole-solve kernels pay for their generality in registers: they only win while a stage kernel is
+// launch-latency-bound, i.e. for small networks (measured: hidden 256 is 20 % slower in one kernel)
+static bool tile_small_net(const cnf_config& c) {
+    long long P = 0;
+    for (int l = 0; l < c.n_layers; ++l) P += (long long)c.dims[l] * c.dims[l + 1];
+    return P <= 8192;
+}
+
+static int tile_sms() {
+    static int sms = 0;
+    if (!sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    return sms;
+}
+
+// launch `kern` on `tiles` CTAs: plain launch for one tile, cooperative launch (grid barriers) for more;
+// false if the CTAs cannot all be resident
+template <typename K>
+static bool tile_launch(cnf_handle* h, K kern, int tiles, int smem, void** args) {
+    if (tiles == 1) return cudaLaunchKernel((const void*)kern, dim3(1), dim3(CNF_NT), args, (size_t)smem, h->stream) == cudaSuccess;
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, CNF_NT, (size_t)smem) != cudaSuccess) return false;
+    if ((long long)per_sm * tile_sms() < tiles) return false;
+    return cudaLaunchCooperativeKernel((const void*)kern, dim3((unsigned)tiles), dim3(CNF_NT), args, (size_t)smem, h->stream) ==
+           cudaSuccess;
+}
+
+template <typename K>
+static long long tile_capacity(K kern, int smem) {
+    int per_sm = 0;
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TILE_SMEM_MAX);
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, CNF_NT, (size_t)smem) != cudaSuccess) return 0;
+    return (long long)per_sm * tile_sms();
+}
+
+#define TILE_DISPATCH(TBV, EXPR1, EXPRN)                         \
+    switch (TBV) {                                               \
+        case 32: { constexpr int TB = 32; if (one) { EXPR1; } else { EXPRN; } } break; \
+        case 16: { constexpr int TB = 16; if (one) { EXPR1; } else { EXPRN; } } break; \
+        case 8: { constexpr int TB = 8; if (one) { EXPR1; } else { EXPRN; } } break;   \
+        default: { constexpr int TB = 4; if (one) { EXPR1; } else { EXPRN; } } break;  \
+    }
+
+// forward: B samples in ceil(B / TB) tiles, all resident at once
 bool tile_solve_ok(cnf_handle* h, int mode, long long B) {
-    if (h->tile_off || h->nranks > 1 || h->time_stages) return false;
+    if (h->tile_off || h->cfg.kernel_path == 1 || h->nranks > 1 || h->time_stages || !tile_small_net(h->cfg)) return false;
     if (use_narrow(h, mode) || use_tc(h, mode)) return false;
     int smem = 0;
     const int tb = tile_tb_eval(h->cfg, &smem);
-    return tb > 0 && B <= tb && smem <= TILE_SMEM_MAX;
+    if (tb <= 0 || smem > TILE_SMEM_MAX) return false;
+    const long long tiles = (B + tb - 1) / tb;
+    if (tiles == 1) return true;
+    const bool one = false;
+    long long cap = 0;
+    TILE_DISPATCH(tb, (void)0, cap = tile_capacity(k_solve_tile<TB, true>, smem));
+    return tiles <= cap;
 }
 
-template <int TB>
-static void tile_launch_solve(cnf_handle* h, const CnfBufs& bf, const GenLayout& lay, int smem, int mode, int use_tape,
-                              int max_attempts) {
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(k_solve_tile<TB>, cudaFuncAttributeMaxDynamicSharedMemorySize, TILE_SMEM_MAX);
-        attr_set = true;
-    }
-    const bool tape = use_tape && !h->ktape.empty();
-    k_solve_tile<TB><<<1, CNF_NT, smem, h->stream>>>(h->d_ctrl, bf, h->net, lay, mode, h->d_dts, tape ? h->d_ktape : nullptr,
-                                                    (long long)h->cfg.D * bf.Bs, (long long)h->ktape.size(),
-                                                    (long long)h->slots.size(), max_attempts);
-    h->launches++;
-}
-
-// the attempt loop of solve_device for a one-tile batch; the initial k1 / dt launches have been enqueued
+// the attempt loop of solve_device in one launch (relaunched only if the tape has to grow); the initial
+// k1 / dt launches have been enqueued
 int tile_solve(cnf_handle* h, const CnfBufs& bf, int mode, bool use_tape, long long maxiters, CnfCtrl* out) {
     int smem = 0;
-    const int TB = tile_tb_eval(h->cfg, &smem);
-    const GenLayout lay = gen_layout(h->cfg, TB);
+    const int tbv = tile_tb_eval(h->cfg, &smem);
+    GenLayout lay = gen_layout(h->cfg, tbv);
+    const int tiles = (int)((bf.B + tbv - 1) / tbv);
+    const bool one = tiles == 1;
     int rc;
     size_t want = 66;   // tape entries for the first launch; grown only when a launch stops at the cap
     for (long long launched = 0;;) {
@@ -122,13 +173,23 @@ int tile_solve(cnf_handle* h, const CnfBufs& bf, int mode, bool use_tape, long l
             if ((rc = ensure_slots(h, want))) return rc;
             if ((rc = ensure_ktape(h, want, (long long)h->cfg.D * bf.Bs))) return rc;
         }
-        const int chunk = 4096;
-        switch (TB) {
-            case 32: tile_launch_solve<32>(h, bf, lay, smem, mode, use_tape, chunk); break;
-            case 16: tile_launch_solve<16>(h, bf, lay, smem, mode, use_tape, chunk); break;
-            case 8: tile_launch_solve<8>(h, bf, lay, smem, mode, use_tape, chunk); break;
-            default: tile_launch_solve<4>(h, bf, lay, smem, mode, use_tape, chunk); break;
-        }
+        int chunk = 4096, md = mode;
+        CnfCtrl* dc = h->d_ctrl;
+        CnfBufs b = bf;
+        CnfNet net = h->net;
+        float* dts = h->d_dts;
+        float* const* kt = (use_tape && !h->ktape.empty()) ? h->d_ktape : nullptr;
+        long long nz = (long long)h->cfg.D * bf.Bs, kcap = (long long)h->ktape.size(), scap = (long long)h->slots.size();
+        void* args[] = {&dc, &b, &net, &lay, &md, &dts, &kt, &nz, &kcap, &scap, &chunk};
+        bool ok = false;
+        static bool attr[2][33] = {};
+        TILE_DISPATCH(tbv,
+            { if (!attr[0][TB]) { cudaFuncSetAttribute(k_solve_tile<TB, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TILE_SMEM_MAX); attr[0][TB] = true; }
+              ok = tile_launch(h, k_solve_tile<TB, false>, 1, smem, args); },
+            { if (!attr[1][TB]) { cudaFuncSetAttribute(k_solve_tile<TB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TILE_SMEM_MAX); attr[1][TB] = true; }
+              ok = tile_launch(h, k_solve_tile<TB, true>, tiles, smem, args); });
+        if (!ok) { h->err = std::string("whole-solve kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()); return CNF_ERR_CUDA; }
+        h->launches++;
         launched += chunk;
         CNF_CUDA(cudaMemcpyAsync(&h->h_ctrl[0], h->d_ctrl, sizeof(CnfCtrl), cudaMemcpyDeviceToHost, h->stream));
         CNF_CUDA(cudaStreamSynchronize(h->stream));
@@ -142,27 +203,19 @@ int tile_solve(cnf_handle* h, const CnfBufs& bf, int mode, bool use_tape, long l
     return CNF_OK;
 }
 
-template <int TB>
-static void tile_launch_sweep(cnf_handle* h, const CnfBufs& bf, const BwLayout& lay, int smem, const SweepArgs& sa) {
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(k_sweep_tile<TB>, cudaFuncAttributeMaxDynamicSharedMemorySize, TILE_SMEM_MAX);
-        attr_set = true;
-    }
-    k_sweep_tile<TB><<<1, CNF_NT, smem, h->stream>>>(bf, h->net, lay, sa);
-    h->launches++;
-}
-
-// reverse sweep of a one-tile batch in one launch; false = conditions not met (caller uses the launch-per-stage sweep)
+// reverse sweep in one launch; false = conditions not met (the caller uses the launch-per-stage sweep)
 bool tile_sweep(cnf_handle* h, const CnfBufs& bf, int mode, long long naccept, long long Bglobal) {
-    if (!tile_solve_ok(h, mode, bf.B)) return false;
+    if (h->tile_off || h->cfg.kernel_path == 1 || h->nranks > 1 || h->time_stages || !tile_small_net(h->cfg)) return false;
+    if (use_narrow(h, mode) || use_tc(h, mode)) return false;
     const cnf_config& c = h->cfg;
     const long long nz = (long long)c.D * bf.Bs;
     if (h->ktape_off || h->ktape_elems != nz || naccept > (long long)h->ktape.size()) return false;
     int smem = 0;
-    const int TB = tile_tb_bw(c, &smem);
-    if (TB <= 0 || bf.B > TB || smem > TILE_SMEM_MAX) return false;
-    const BwLayout lay = bw_layout(c, TB);
+    const int tbv = tile_tb_bw(c, &smem);
+    if (tbv <= 0 || smem > TILE_SMEM_MAX) return false;
+    const int tiles = (int)((bf.B + tbv - 1) / tbv);
+    const bool one = tiles == 1;
+    BwLayout lay = bw_layout(c, tbv);
     const bool train = mode == CNF_MODE_TRAIN;
     const float invB = 1.0f / (float)Bglobal;
     SweepArgs sa;
@@ -179,11 +232,17 @@ bool tile_sweep(cnf_handle* h, const CnfBufs& bf, int mode, long long naccept, l
     sa.c_n = train ? c.lambda2 * invB : 0.0f;
     sa.train = train ? 1 : 0;
     sa.D = c.D;
-    switch (TB) {
-        case 32: tile_launch_sweep<32>(h, bf, lay, smem, sa); break;
-        case 16: tile_launch_sweep<16>(h, bf, lay, smem, sa); break;
-        case 8: tile_launch_sweep<8>(h, bf, lay, smem, sa); break;
-        default: tile_launch_sweep<4>(h, bf, lay, smem, sa); break;
-    }
+    CnfBufs b = bf;
+    CnfNet net = h->net;
+    void* args[] = {&b, &net, &lay, &sa};
+    bool ok = false;
+    static bool attr[2][33] = {};
+    TILE_DISPATCH(tbv,
+        { if (!attr[0][TB]) { cudaFuncSetAttribute(k_sweep_tile<TB, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TILE_SMEM_MAX); attr[0][TB] = true; }
+          ok = tile_launch(h, k_sweep_tile<TB, false>, 1, smem, args); },
+        { if (!attr[1][TB]) { cudaFuncSetAttribute(k_sweep_tile<TB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TILE_SMEM_MAX); attr[1][TB] = true; }
+          ok = tile_launch(h, k_sweep_tile<TB, true>, tiles, smem, args); });
+    if (!ok) { cudaGetLastError(); return false; }   // e.g. more tiles than can be resident: launch-per-stage sweep
+    h->launches++;
     return true;
 }

@@ -436,11 +436,12 @@ def test_stage_tape_matches_stage_recompute(cid, B, tol):
     assert out[0][3] < out[1][3]          # fewer launches: no recomputed evaluations
 
 
-@pytest.mark.parametrize("cid,B", [("C1", 32), ("C0", 20), ("C1", 7)])
-def test_one_tile_batches_run_in_whole_solve_kernels_with_identical_results(cid, B):
-    """batches that fit one tile of the generic kernel (the reference's default batch_size = 32) run the
-    attempt loop and the reverse sweep inside single-CTA kernels: same device code, so the results
-    equal the launch-per-stage path, in a handful of launches instead of hundreds"""
+@pytest.mark.parametrize("cid,B", [("C1", 32), ("C0", 20), ("C1", 7), ("C1", 1000), ("C0", 64), ("C1", 5000)])
+def test_small_batches_run_in_whole_solve_kernels_with_identical_results(cid, B):
+    """batches whose tiles of the generic kernel are all resident at once (one tile = the reference's
+    default batch_size = 32: block barriers; more tiles: a cooperative launch with grid barriers) run the
+    attempt loop and the reverse sweep inside ONE kernel each: same device code, so the results equal
+    the launch-per-stage path, in a handful of launches instead of hundreds"""
     inp = wl.make_inputs(cid, B=B)
     res = []
     for tile in (1, 0):
