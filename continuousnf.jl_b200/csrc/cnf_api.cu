@@ -129,6 +129,7 @@ extern "C" int32_t cnfb200_destroy(cnf_handle* h) {
     }
     free_workspaces(h);
     narrow_free(h);
+    ntc_free(h);
     tc_free(h);
     cudaFree(h->d_io);
     cudaFree(h->d_theta); cudaFree(h->d_wt); cudaFree(h->d_grad);
@@ -183,6 +184,8 @@ static int refresh_params(cnf_handle* h, bool narrow) {
         CNF_CUDA(cudaMemcpyAsync(th.data(), h->d_theta, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
         CNF_CUDA(cudaStreamSynchronize(h->stream));
         narrow_set_params(h, th.data());
+        int rcn = ntc_set_params(h, th.data());
+        if (rcn) return rcn;
     }
     int rc = tc_set_params(h);
     if (rc) return rc;
@@ -351,9 +354,15 @@ static int tc_stage(cnf_handle* h, const CnfBufs& bf, const float* src, int kidx
     return rc;
 }
 
+// kernel_path 2 forces the register-resident SIMT kernel; 0 prefers the tensor-core variant where built
+static bool use_ntc(cnf_handle* h, int mode) {
+    return h->cfg.kernel_path != 2 && ntc_supported(h, mode);
+}
+
 static int narrow_stage(cnf_handle* h, const CnfBufs& bf, int stage, int check_done) {
     stage_timer_begin(h);
-    int rc = launch_stage_narrow(h, bf, stage, check_done);
+    int rc = h->path_used == 6 ? launch_stage_narrow_tc(h, bf, stage, check_done)
+                               : launch_stage_narrow(h, bf, stage, check_done);
     stage_timer_end(h);
     return rc;
 }
@@ -425,7 +434,7 @@ static int solve_device(cnf_handle* h, const CnfBufs& bf, int mode, int R, long 
     int rc;
     const bool nar = use_narrow(h, mode);
     const bool tcp = !nar && use_tc(h, mode);
-    h->path_used = nar ? 2 : (tcp ? 3 : 1);
+    h->path_used = nar ? (use_ntc(h, mode) ? 6 : 2) : (tcp ? 3 : 1);
     if (nar) rc = narrow_stage(h, bf, 0, 0);
     else if (tcp) rc = tc_stage(h, bf, h->slots[0], 0, nullptr, 0);
     else rc = eval_stage(h, bf, mode, 2 /*SRC_SLOT0*/, 0, 0);   // k1 = f(u0)

@@ -67,6 +67,7 @@ struct cnf_handle {
     bool tc_bw_off = false;     // option "tc_backward" = 0: reverse sweep on the generic SIMT kernels
     long long wg_lbo = 0, wg_sbo = 0;   // debug override of the MN-major descriptor strides (0 = default)
     void* narrow_w = nullptr;   // host copy of the packed kernel-parameter weights (narrow path)
+    void* ntc_state = nullptr;  // narrow tensor-core path state (cnf_stage_narrow_tc.cu)
 };
 
 #define CNF_CUDA(call)                                                                   \
@@ -116,6 +117,12 @@ void narrow_set_params(cnf_handle* h, const float* theta_host);
 void narrow_free(cnf_handle* h);
 // fused: stage input from (u, k1..k_i) -> k_{i+1}; stage 6 also writes unew + error partials
 int launch_stage_narrow(cnf_handle* h, const CnfBufs& bf, int stage, int check_done);
+
+// ---- cnf_stage_narrow_tc.cu : narrow exact-trace nets with layer 2 on tcgen05 (D <= 2, hidden 64)
+bool ntc_supported(const cnf_handle* h, int mode);
+int ntc_set_params(cnf_handle* h, const float* theta_host);
+void ntc_free(cnf_handle* h);
+int launch_stage_narrow_tc(cnf_handle* h, const CnfBufs& bf, int stage, int check_done);
 
 // ---- cnf_stage_tc.cu : tcgen05 tensor path (wide nets, TrainMode)
 bool tc_supported(const cnf_config& cfg, int mode);

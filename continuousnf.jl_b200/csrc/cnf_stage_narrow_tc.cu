@@ -1,0 +1,314 @@
+// cnf_stage_narrow_tc.cu — RK stage kernel for narrow exact-trace nets (D -> 64 -> 64 -> D, TestMode,
+// JacVec; reference src/icnf.jl:148-164 through src/utils.jl:19-36) with the one product that holds
+// 94 % of the flops — layer 2 applied to the activation h1 AND to the D tangents tau1_v — on the
+// tensor cores.  The register-resident kernel (cnf_stage_narrow.cu) is bound by the FP32-FMA pipe
+// (13 k FFMA per sample); here a group of 128 threads owns a tile of 128 samples:
+//   1. SIMT: stage input u + dt*sum a_ij k_j, layer 1 and the D one-hot tangents in registers,
+//      written as IEEE-half hi/lo planes straight into shared memory in the canonical K-major
+//      SWIZZLE_128B operand layout (no TMA: the operand never exists in global memory);
+//   2. one thread issues (1+D) x 3 x 4 tcgen05.mma (hi*hi + lo*hi + hi*lo = FP32-level products,
+//      as in cnf_stage_tc.cu) against the resident W2 planes; accumulators in TMEM;
+//   3. SIMT epilogue from TMEM: bias + tanh, tangent scaling, layer 3 (only the diagonal of the
+//      D x D Jacobian product is needed for the trace), output rows; at the 7th stage also the
+//      new state and the embedded-error partial sum.
+// Two such groups per CTA (one persistent CTA per SM) alternate, so the tensor pipe works on one
+// tile while the other group's SIMT phases run.  ~2.6 k instructions per sample instead of 17.7 k.
+#include "cnf_internal.h"
+#include "cnf_tc_ptx.cuh"
+
+#define NTC_H 64            // hidden width (one 128-byte swizzle row of halves)
+#define NTC_GROUPS 2
+#define NTC_THREADS (128 * NTC_GROUPS)
+#define NTC_PLANE_A (128 * NTC_H * 2)   // 16 KB: one plane of one operand vector
+#define NTC_PLANE_B (NTC_H * NTC_H * 2) // 8 KB: one plane of W2
+
+template <int D>
+struct alignas(16) NtcW {   // kernel-parameter weights of layers 1 and 3 (uniform-register operands)
+    float w1[NTC_H * D];    // [o][i]
+    float b1[NTC_H];
+    float b2[NTC_H];
+    float w3[NTC_H * D];    // [o][j]
+    float b3[4];
+};
+
+struct NtcState {
+    void* w_host = nullptr;            // NtcW<D>
+    __half* d_w2 = nullptr;            // hi plane then lo plane, pre-swizzled K-major SWIZZLE_128B
+    int D = 0;
+    int sms = 148;
+};
+
+template <int D>
+constexpr int ntc_smem_bytes() { return 1024 + 2 * NTC_PLANE_B + NTC_GROUPS * (1 + D) * 2 * NTC_PLANE_A + 64; }
+
+// byte offset of the 16-byte chunk `ch` (8 halves along K) of row `r` inside a SWIZZLE_128B K-major tile
+__device__ __forceinline__ uint32_t ntc_swz(int r, int ch) {
+    return (uint32_t)((r >> 3) * 1024 + (r & 7) * 128 + ((ch ^ (r & 7)) << 4));
+}
+__device__ __forceinline__ void ntc_sts128(uint32_t addr, const uint32_t (&v)[4]) {
+    asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]) : "memory");
+}
+__device__ __forceinline__ void ntc_group_sync(int g) {
+    asm volatile("bar.sync %0, 128;" ::"r"(g + 1) : "memory");
+}
+
+// stage numbering as in k_stage_narrow_test_jvp: 0 k1 = f(u0); -1 initial-dt probe -> K[1];
+// 1..5 -> K[stage]; 6 -> new state, k7 and the error partial sum
+template <int D>
+__global__ void __launch_bounds__(NTC_THREADS, 1)
+k_stage_narrow_tc(const __grid_constant__ NtcW<D> p, const __half* __restrict__ w2planes, CnfCtrl* __restrict__ c,
+                  CnfBufs bf, int stage, int check_done, int ntiles) {
+    if (check_done && c->done) return;
+    constexpr int R = D + 1;
+    constexpr int NV = 1 + D;                       // operand vectors: h1, tau1_1..tau1_D
+    extern __shared__ uint8_t ntc_raw[];
+    const uint32_t sbase = (tc::smem_u32(ntc_raw) + 1023u) & ~1023u;
+    uint8_t* sgen = ntc_raw + (sbase - tc::smem_u32(ntc_raw));
+    const uint32_t sB = sbase;                                       // W2 hi, lo planes
+    const uint32_t sA = sbase + 2 * NTC_PLANE_B;                     // [group][vector][plane]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sgen + 2 * NTC_PLANE_B + NTC_GROUPS * NV * 2 * NTC_PLANE_A);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + NTC_GROUPS);
+    __shared__ double sh_red[32];
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int g = tid >> 7;              // group
+    const int r = tid & 127;             // row of the tile = TMEM lane
+    // ---- one-time setup: W2 planes into shared memory, barriers, TMEM
+    {
+        const uint4* src = reinterpret_cast<const uint4*>(w2planes);
+        uint4* dst = reinterpret_cast<uint4*>(sgen);
+        for (int i = tid; i < 2 * NTC_PLANE_B / 16; i += NTC_THREADS) dst[i] = src[i];
+    }
+    if (tid == 0) {
+        for (int i = 0; i < NTC_GROUPS; ++i) tc::mbar_init(&bars[i], 1);
+        tc::fence_barrier_init();
+    }
+    if (warp == 0) tc::tmem_alloc(tmem_slot, 512);
+    tc::fence_proxy_async();
+    tc::tc_fence_before();
+    __syncthreads();
+    tc::tc_fence_after();
+    const uint32_t tmem = *tmem_slot + (uint32_t)g * 256u;          // this group's accumulators: NV x 64 columns
+    const uint32_t tlane = tmem + ((uint32_t)((warp & 3) * 32) << 16);
+    const uint32_t idesc = tc::umma_idesc_f16(128, NTC_H, 0);
+    const uint32_t myA = sA + (uint32_t)g * (NV * 2 * NTC_PLANE_A);
+
+    const long long Bs = bf.Bs;
+    const float* u = bf.slots[cnf_slot(c, stage <= 0 ? 0 : c->naccept)];
+    const float* k1 = bf.K[c->k1idx];
+    float* kout = (stage == 0) ? bf.K[c->k1idx] : (stage == -1 ? bf.K[1] : (stage == 6 ? bf.K[6 - c->k1idx] : bf.K[stage]));
+    float* unew = bf.slots[cnf_slot(c, c->naccept + 1)];
+    const float dt = c->dt;
+    const float reltol = c->reltol, abstol = c->abstol;
+    double acc = 0.0;
+
+    uint32_t it = 0;
+    for (int tile = blockIdx.x * NTC_GROUPS + g; tile < ntiles; tile += gridDim.x * NTC_GROUPS, ++it) {
+        const long long b = (long long)tile * 128 + r;
+        // ---- stage input
+        float z[D];
+        if (stage == 0) {
+#pragma unroll
+            for (int i = 0; i < D; ++i) z[i] = u[(long long)i * Bs + b];
+        } else if (stage == -1) {
+            const float hh = c->tdir * c->dt0init;
+#pragma unroll
+            for (int i = 0; i < D; ++i) z[i] = fmaf(hh, k1[(long long)i * Bs + b], u[(long long)i * Bs + b]);
+        } else {
+            const int nrow = (stage == 6) ? R : D;
+            for (int rr = 0; rr < nrow; ++rr) {   // rows D.. only at the 7th stage (pure quadrature rows)
+                const long long at = (long long)rr * Bs + b;
+                float a = c_A[stage][0] * k1[at];
+                for (int j = 1; j < stage; ++j) a = fmaf(c_A[stage][j], bf.K[j][at], a);
+                float v = fmaf(dt, a, u[at]);
+                if (stage == 6) unew[at] = v;
+                if (rr < D) z[rr] = v;
+            }
+        }
+        // ---- layer 1 and the D one-hot tangents -> hi/lo operand planes in shared memory
+#pragma unroll
+        for (int cb = 0; cb < NTC_H / 8; ++cb) {
+            float x[NV][8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                const int o = cb * 8 + q;
+                float a = p.b1[o];
+#pragma unroll
+                for (int i = 0; i < D; ++i) a = fmaf(p.w1[o * D + i], z[i], a);
+                const float h = tc_tanh(a);
+                const float d = fmaf(-h, h, 1.0f);
+                x[0][q] = h;
+#pragma unroll
+                for (int v = 0; v < D; ++v) x[1 + v][q] = p.w1[o * D + v] * d;
+            }
+            const uint32_t off = ntc_swz(r, cb);
+#pragma unroll
+            for (int v = 0; v < NV; ++v) {
+                uint32_t hi[4], lo[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) tc_split2<0>(x[v][2 * q], x[v][2 * q + 1], hi[q], lo[q]);
+                ntc_sts128(myA + (uint32_t)(v * 2) * NTC_PLANE_A + off, hi);
+                ntc_sts128(myA + (uint32_t)(v * 2 + 1) * NTC_PLANE_A + off, lo);
+            }
+        }
+        tc::fence_proxy_async();     // generic-proxy writes -> visible to the tensor core's async proxy
+        tc::tc_fence_before();       // the previous tile's tcgen05.ld of this thread are ordered before the barrier
+        ntc_group_sync(g);
+        // ---- layer 2 for all operand vectors: (1+D) x 4 k-steps x 3 MMAs, one issuing thread
+        if (r == 0) {
+            tc::tc_fence_after();
+#pragma unroll
+            for (int v = 0; v < NV; ++v) {
+#pragma unroll
+                for (int kk = 0; kk < NTC_H / 16; ++kk) {
+                    const uint64_t ahi = tc::umma_desc_sw128(myA + (uint32_t)(v * 2) * NTC_PLANE_A + kk * 32);
+                    const uint64_t alo = tc::umma_desc_sw128(myA + (uint32_t)(v * 2 + 1) * NTC_PLANE_A + kk * 32);
+                    const uint64_t bhi = tc::umma_desc_sw128(sB + kk * 32);
+                    const uint64_t blo = tc::umma_desc_sw128(sB + NTC_PLANE_B + kk * 32);
+                    tc::umma_bf16(tmem + v * NTC_H, ahi, bhi, idesc, kk != 0);
+                    tc::umma_bf16(tmem + v * NTC_H, alo, bhi, idesc, 1);
+                    tc::umma_bf16(tmem + v * NTC_H, ahi, blo, idesc, 1);
+                }
+            }
+            tc::umma_commit(&bars[g]);
+        }
+        tc::mbar_wait(&bars[g], it & 1);
+        __syncwarp();
+        tc::tc_fence_after();
+        // ---- epilogue: tanh, tangent scaling, layer 3 (diagonal of the Jacobian product only)
+        float p3[D], r3[D];
+#pragma unroll
+        for (int j = 0; j < D; ++j) { p3[j] = p.b3[j]; r3[j] = 0.0f; }
+#pragma unroll
+        for (int ch = 0; ch < NTC_H / 16; ++ch) {
+            uint32_t va[NV][16];
+#pragma unroll
+            for (int v = 0; v < NV; ++v) tc::tmem_ld_32x16(tlane + v * NTC_H + ch * 16, va[v]);
+            tc::tmem_ld_wait();
+#pragma unroll
+            for (int q = 0; q < 16; ++q) {
+                const int o = ch * 16 + q;
+                const float h = tc_tanh(__uint_as_float(va[0][q]) + p.b2[o]);
+                const float d = fmaf(-h, h, 1.0f);
+#pragma unroll
+                for (int j = 0; j < D; ++j) {
+                    const float w3 = p.w3[o * D + j];
+                    p3[j] = fmaf(w3, h, p3[j]);
+                    r3[j] = fmaf(w3, __uint_as_float(va[1 + j][q]) * d, r3[j]);
+                }
+            }
+        }
+        float y[D], tr = 0.0f;
+#pragma unroll
+        for (int j = 0; j < D; ++j) {
+            y[j] = cnf_tanh_fastpath(p3[j]);
+            tr -= fmaf(-y[j], y[j], 1.0f) * r3[j];
+        }
+#pragma unroll
+        for (int j = 0; j < D; ++j) kout[(long long)j * Bs + b] = y[j];
+        kout[(long long)D * Bs + b] = tr;
+        // ---- 7th stage: embedded error partial sum over this thread's R elements
+        if (stage == 6 && b < bf.B) {
+#pragma unroll
+            for (int rr = 0; rr < R; ++rr) {
+                const long long at = (long long)rr * Bs + b;
+                float a = c_BT[0] * k1[at];
+                for (int j = 1; j < 6; ++j) a = fmaf(c_BT[j], bf.K[j][at], a);
+                a = fmaf(c_BT[6], rr < D ? y[rr < D ? rr : 0] : tr, a);
+                float ut = dt * a;
+                float unv = unew[at];
+                float sc = fmaf(fmaxf(fabsf(u[at]), fabsf(unv)), reltol, abstol);
+                float q = ut / sc;
+                if (unv != unv) q = unv;
+                acc += (double)q * (double)q;
+            }
+        }
+    }
+    tc::tc_fence_before();
+    if (stage == 6) {
+        acc = cnf_block_sum(acc, sh_red);
+        if (tid == 0) atomicAdd(&c->errsum, acc);
+    }
+    __syncthreads();
+    if (warp == 0) tc::tmem_dealloc(*tmem_slot, 512);
+}
+
+// ------------------------------------------------------------------ host side
+template <int D>
+static void ntc_pack(const cnf_handle* h, const float* theta, NtcW<D>* out, __half* planes) {
+    memset(out, 0, sizeof(*out));
+    const float* W1 = theta + h->w_off[0];   // col-major H x D
+    const float* W2 = theta + h->w_off[1];   // col-major H x H: W2[i * H + o]
+    const float* W3 = theta + h->w_off[2];   // col-major D x H
+    for (int o = 0; o < NTC_H; ++o) {
+        for (int i = 0; i < D; ++i) out->w1[o * D + i] = W1[i * NTC_H + o];
+        out->b1[o] = theta[h->b_off[0] + o];
+        out->b2[o] = theta[h->b_off[1] + o];
+        for (int j = 0; j < D; ++j) out->w3[o * D + j] = W3[o * D + j];
+    }
+    for (int j = 0; j < D; ++j) out->b3[j] = theta[h->b_off[2] + j];
+    // B operand: row n = output unit, K = input unit; K-major SWIZZLE_128B (same layout as ntc_swz)
+    for (int n = 0; n < NTC_H; ++n)
+        for (int k = 0; k < NTC_H; ++k) {
+            const float w = W2[k * NTC_H + n];
+            const __half hi = __float2half_rn(w);
+            const __half lo = __float2half_rn(w - __half2float(hi));
+            const size_t off = (size_t)(n >> 3) * 512 + (n & 7) * 64 + (((k >> 3) ^ (n & 7)) << 3) + (k & 7);   // in halves
+            planes[off] = hi;
+            planes[NTC_PLANE_B / 2 + off] = lo;
+        }
+}
+
+static bool ntc_shape(const cnf_config& c) {
+    return c.n_layers == 3 && c.C == 0 && !(c.flags & CNF_FLAG_LAST_LINEAR) && (c.D == 1 || c.D == 2) &&
+           c.dims[1] == NTC_H && c.dims[2] == NTC_H;
+}
+bool ntc_supported(const cnf_handle* h, int mode) {
+    return mode == CNF_MODE_TEST && h->cfg.trace_mode == CNF_TRACE_JVP && ntc_shape(h->cfg) && h->ntc_state != nullptr;
+}
+
+// called from set_params with a host copy of theta
+int ntc_set_params(cnf_handle* h, const float* theta_host) {
+    if (!ntc_shape(h->cfg)) return CNF_OK;
+    NtcState* s = (NtcState*)h->ntc_state;
+    if (!s) {
+        s = new NtcState();
+        s->D = h->cfg.D;
+        cudaDeviceProp prop;
+        if (cudaGetDeviceProperties(&prop, h->device) == cudaSuccess) s->sms = prop.multiProcessorCount;
+        s->w_host = (s->D == 1) ? (void*)new NtcW<1>() : (void*)new NtcW<2>();
+        CNF_CUDA(cudaMalloc(&s->d_w2, 2 * NTC_PLANE_B));
+        CNF_CUDA(cudaFuncSetAttribute(k_stage_narrow_tc<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ntc_smem_bytes<1>()));
+        CNF_CUDA(cudaFuncSetAttribute(k_stage_narrow_tc<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, ntc_smem_bytes<2>()));
+        h->ntc_state = s;
+    }
+    std::vector<__half> planes(NTC_PLANE_B);   // 2 planes x NTC_PLANE_B / 2 halves
+    if (s->D == 1) ntc_pack<1>(h, theta_host, (NtcW<1>*)s->w_host, planes.data());
+    else ntc_pack<2>(h, theta_host, (NtcW<2>*)s->w_host, planes.data());
+    CNF_CUDA(cudaMemcpyAsync(s->d_w2, planes.data(), 2 * NTC_PLANE_B, cudaMemcpyHostToDevice, h->stream));
+    CNF_CUDA(cudaStreamSynchronize(h->stream));
+    return CNF_OK;
+}
+void ntc_free(cnf_handle* h) {
+    NtcState* s = (NtcState*)h->ntc_state;
+    if (!s) return;
+    if (s->D == 1) delete (NtcW<1>*)s->w_host; else delete (NtcW<2>*)s->w_host;
+    cudaFree(s->d_w2);
+    delete s;
+    h->ntc_state = nullptr;
+}
+int launch_stage_narrow_tc(cnf_handle* h, const CnfBufs& bf, int stage, int check_done) {
+    NtcState* s = (NtcState*)h->ntc_state;
+    if (!s) { h->err = "narrow tensor path: no parameters"; return CNF_ERR_UNSUPPORTED; }
+    const int ntiles = (int)(bf.Bs / 128);
+    int grid = (ntiles + NTC_GROUPS - 1) / NTC_GROUPS;
+    if (grid > s->sms) grid = s->sms;
+    if (s->D == 1)
+        k_stage_narrow_tc<1><<<grid, NTC_THREADS, ntc_smem_bytes<1>(), h->stream>>>(*(const NtcW<1>*)s->w_host, s->d_w2, h->d_ctrl,
+                                                                                   bf, stage, check_done, ntiles);
+    else
+        k_stage_narrow_tc<2><<<grid, NTC_THREADS, ntc_smem_bytes<2>(), h->stream>>>(*(const NtcW<2>*)s->w_host, s->d_w2, h->d_ctrl,
+                                                                                   bf, stage, check_done, ntiles);
+    h->launches++;
+    return CNF_OK;
+}
