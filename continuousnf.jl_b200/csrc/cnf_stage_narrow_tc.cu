@@ -67,10 +67,10 @@ k_stage_narrow_tc(const __grid_constant__ NtcW<D> p, const __half* __restrict__ 
     const uint32_t sB = sbase;                                       // W2 hi, lo planes
     const uint32_t sA = sbase + 2 * NTC_PLANE_B;                     // [group][vector][plane]
     uint64_t* bars = reinterpret_cast<uint64_t*>(sgen + 2 * NTC_PLANE_B + NTC_GROUPS * NV * 2 * NTC_PLANE_A);
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + NTC_GROUPS);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * NTC_GROUPS);
     __shared__ double sh_red[32];
 
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tid = threadIdx.x, warp = tid >> 5;
     const int g = tid >> 7;              // group
     const int r = tid & 127;             // row of the tile = TMEM lane
     // ---- one-time setup: W2 planes into shared memory, barriers, TMEM
@@ -80,7 +80,7 @@ k_stage_narrow_tc(const __grid_constant__ NtcW<D> p, const __half* __restrict__ 
         for (int i = tid; i < 2 * NTC_PLANE_B / 16; i += NTC_THREADS) dst[i] = src[i];
     }
     if (tid == 0) {
-        for (int i = 0; i < NTC_GROUPS; ++i) tc::mbar_init(&bars[i], 1);
+        for (int i = 0; i < 2 * NTC_GROUPS; ++i) tc::mbar_init(&bars[i], 1);
         tc::fence_barrier_init();
     }
     if (warp == 0) tc::tmem_alloc(tmem_slot, 512);
@@ -90,7 +90,7 @@ k_stage_narrow_tc(const __grid_constant__ NtcW<D> p, const __half* __restrict__ 
     tc::tc_fence_after();
     const uint32_t tmem = *tmem_slot + (uint32_t)g * 256u;          // this group's accumulators: NV x 64 columns
     const uint32_t tlane = tmem + ((uint32_t)((warp & 3) * 32) << 16);
-    const uint32_t idesc = tc::umma_idesc_f16(128, NTC_H, 0);
+    const uint32_t idesc64 = tc::umma_idesc_f16(128, NTC_H, 0), idesc32 = tc::umma_idesc_f16(128, NTC_H / 2, 0);
     const uint32_t myA = sA + (uint32_t)g * (NV * 2 * NTC_PLANE_A);
 
     const long long Bs = bf.Bs;
@@ -99,88 +99,131 @@ k_stage_narrow_tc(const __grid_constant__ NtcW<D> p, const __half* __restrict__ 
     float* kout = (stage == 0) ? bf.K[c->k1idx] : (stage == -1 ? bf.K[1] : (stage == 6 ? bf.K[6 - c->k1idx] : bf.K[stage]));
     float* unew = bf.slots[cnf_slot(c, c->naccept + 1)];
     const float dt = c->dt;
+    const float hh = c->tdir * c->dt0init;
     const float reltol = c->reltol, abstol = c->abstol;
+    const int nrow = (stage == 6) ? R : D;   // rows D.. only at the 7th stage (pure quadrature rows)
     double acc = 0.0;
 
-    uint32_t it = 0;
-    for (int tile = blockIdx.x * NTC_GROUPS + g; tile < ntiles; tile += gridDim.x * NTC_GROUPS, ++it) {
+    // raw stage-input operands of one tile: issued as independent loads one tile ahead (an in-order
+    // warp that loads at the point of use pays one DRAM latency per k_j)
+    float ru[R], rk[R][6];
+    auto load_raw = [&](int tile) {
         const long long b = (long long)tile * 128 + r;
-        // ---- stage input
-        float z[D];
-        if (stage == 0) {
 #pragma unroll
-            for (int i = 0; i < D; ++i) z[i] = u[(long long)i * Bs + b];
-        } else if (stage == -1) {
-            const float hh = c->tdir * c->dt0init;
-#pragma unroll
-            for (int i = 0; i < D; ++i) z[i] = fmaf(hh, k1[(long long)i * Bs + b], u[(long long)i * Bs + b]);
-        } else {
-            const int nrow = (stage == 6) ? R : D;
-            for (int rr = 0; rr < nrow; ++rr) {   // rows D.. only at the 7th stage (pure quadrature rows)
+        for (int rr = 0; rr < R; ++rr) {
+            if (rr < nrow) {
                 const long long at = (long long)rr * Bs + b;
-                float a = c_A[stage][0] * k1[at];
-                for (int j = 1; j < stage; ++j) a = fmaf(c_A[stage][j], bf.K[j][at], a);
-                float v = fmaf(dt, a, u[at]);
-                if (stage == 6) unew[at] = v;
-                if (rr < D) z[rr] = v;
+                ru[rr] = u[at];
+                if (stage != 0) rk[rr][0] = k1[at];
+#pragma unroll
+                for (int j = 1; j < 6; ++j)
+                    if (j < stage) rk[rr][j] = bf.K[j][at];
             }
         }
-        // ---- layer 1 and the D one-hot tangents -> hi/lo operand planes in shared memory
+    };
+
+    const int tile0 = blockIdx.x * NTC_GROUPS + g, tstride = gridDim.x * NTC_GROUPS;
+    if (tile0 < ntiles) load_raw(tile0);
+    uint32_t it = 0;
+    for (int tile = tile0; tile < ntiles; tile += tstride, ++it) {
+        const long long b = (long long)tile * 128 + r;
+        // ---- stage input (and, at the 7th stage, the new state and the k1..k6 part of the error estimate)
+        float z[D], ep[R] = {}, uo[R] = {}, un[R] = {};
 #pragma unroll
-        for (int cb = 0; cb < NTC_H / 8; ++cb) {
-            float x[NV][8];
+        for (int rr = 0; rr < R; ++rr) {
+            if (rr < nrow) {
+                float v;
+                if (stage == 0) v = ru[rr];
+                else if (stage == -1) v = fmaf(hh, rk[rr][0], ru[rr]);
+                else {
+                    float a = c_A[stage][0] * rk[rr][0];
 #pragma unroll
-            for (int q = 0; q < 8; ++q) {
-                const int o = cb * 8 + q;
-                float a = p.b1[o];
+                    for (int j = 1; j < 6; ++j)
+                        if (j < stage) a = fmaf(c_A[stage][j], rk[rr][j], a);
+                    v = fmaf(dt, a, ru[rr]);
+                    if (stage == 6) {
+                        unew[(long long)rr * Bs + b] = v;
+                        float e = c_BT[0] * rk[rr][0];
 #pragma unroll
-                for (int i = 0; i < D; ++i) a = fmaf(p.w1[o * D + i], z[i], a);
-                const float h = tc_tanh(a);
-                const float d = fmaf(-h, h, 1.0f);
-                x[0][q] = h;
-#pragma unroll
-                for (int v = 0; v < D; ++v) x[1 + v][q] = p.w1[o * D + v] * d;
-            }
-            const uint32_t off = ntc_swz(r, cb);
-#pragma unroll
-            for (int v = 0; v < NV; ++v) {
-                uint32_t hi[4], lo[4];
-#pragma unroll
-                for (int q = 0; q < 4; ++q) tc_split2<0>(x[v][2 * q], x[v][2 * q + 1], hi[q], lo[q]);
-                ntc_sts128(myA + (uint32_t)(v * 2) * NTC_PLANE_A + off, hi);
-                ntc_sts128(myA + (uint32_t)(v * 2 + 1) * NTC_PLANE_A + off, lo);
+                        for (int j = 1; j < 6; ++j) e = fmaf(c_BT[j], rk[rr][j], e);
+                        ep[rr] = e; uo[rr] = ru[rr]; un[rr] = v;
+                    }
+                }
+                if (rr < D) z[rr < D ? rr : 0] = v;
             }
         }
-        tc::fence_proxy_async();     // generic-proxy writes -> visible to the tensor core's async proxy
-        tc::tc_fence_before();       // the previous tile's tcgen05.ld of this thread are ordered before the barrier
-        ntc_group_sync(g);
-        // ---- layer 2 for all operand vectors: (1+D) x 4 k-steps x 3 MMAs, one issuing thread
-        if (r == 0) {
-            tc::tc_fence_after();
+        // ---- layer 1 and the D one-hot tangents -> hi/lo operand planes in shared memory, in two K halves:
+        // the MMAs of the first 32 hidden units run while the second half is computed
 #pragma unroll
-            for (int v = 0; v < NV; ++v) {
+        for (int kh = 0; kh < 2; ++kh) {
 #pragma unroll
-                for (int kk = 0; kk < NTC_H / 16; ++kk) {
-                    const uint64_t ahi = tc::umma_desc_sw128(myA + (uint32_t)(v * 2) * NTC_PLANE_A + kk * 32);
-                    const uint64_t alo = tc::umma_desc_sw128(myA + (uint32_t)(v * 2 + 1) * NTC_PLANE_A + kk * 32);
-                    const uint64_t bhi = tc::umma_desc_sw128(sB + kk * 32);
-                    const uint64_t blo = tc::umma_desc_sw128(sB + NTC_PLANE_B + kk * 32);
-                    tc::umma_bf16(tmem + v * NTC_H, ahi, bhi, idesc, kk != 0);
-                    tc::umma_bf16(tmem + v * NTC_H, alo, bhi, idesc, 1);
-                    tc::umma_bf16(tmem + v * NTC_H, ahi, blo, idesc, 1);
+            for (int cb = kh * 4; cb < kh * 4 + 4; ++cb) {
+                float x[NV][8];
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    const int o = cb * 8 + q;
+                    float a = p.b1[o];
+#pragma unroll
+                    for (int i = 0; i < D; ++i) a = fmaf(p.w1[o * D + i], z[i], a);
+                    const float h = tc_tanh(a);
+                    const float d = fmaf(-h, h, 1.0f);
+                    x[0][q] = h;
+#pragma unroll
+                    for (int v = 0; v < D; ++v) x[1 + v][q] = p.w1[o * D + v] * d;
+                }
+                const uint32_t off = ntc_swz(r, cb);
+#pragma unroll
+                for (int v = 0; v < NV; ++v) {
+                    uint32_t hi[4], lo[4];
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) tc_split2<0>(x[v][2 * q], x[v][2 * q + 1], hi[q], lo[q]);
+                    ntc_sts128(myA + (uint32_t)(v * 2) * NTC_PLANE_A + off, hi);
+                    ntc_sts128(myA + (uint32_t)(v * 2 + 1) * NTC_PLANE_A + off, lo);
                 }
             }
-            tc::umma_commit(&bars[g]);
+            tc::fence_proxy_async();     // generic-proxy writes -> visible to the tensor core's async proxy
+            if (kh == 0) tc::tc_fence_before();   // the previous tile's tcgen05.ld are ordered before the barrier
+            ntc_group_sync(g);
+            // ---- layer 2 for all operand vectors, one issuing thread: 3 MMAs per k-step (hi*hi + lo*hi + hi*lo)
+            if (r == 0) {
+                tc::tc_fence_after();
+                // second K half: the two N halves commit separately so the epilogue starts on columns 0..31
+#pragma unroll
+                for (int nh = 0; nh < 2; ++nh) {
+                    if (kh == 0 && nh == 1) break;
+                    const uint32_t idesc = kh == 0 ? idesc64 : idesc32;
+                    const uint32_t boff = (uint32_t)nh * (32 * 128);     // B rows 32.. = output units 32..
+#pragma unroll
+                    for (int v = 0; v < NV; ++v) {
+#pragma unroll
+                        for (int kk = kh * 2; kk < kh * 2 + 2; ++kk) {
+                            const uint64_t ahi = tc::umma_desc_sw128(myA + (uint32_t)(v * 2) * NTC_PLANE_A + kk * 32);
+                            const uint64_t alo = tc::umma_desc_sw128(myA + (uint32_t)(v * 2 + 1) * NTC_PLANE_A + kk * 32);
+                            const uint64_t bhi = tc::umma_desc_sw128(sB + boff + kk * 32);
+                            const uint64_t blo = tc::umma_desc_sw128(sB + NTC_PLANE_B + boff + kk * 32);
+                            const uint32_t dcol = tmem + v * NTC_H + nh * 32;
+                            tc::umma_bf16(dcol, ahi, bhi, idesc, kk != 0);
+                            tc::umma_bf16(dcol, alo, bhi, idesc, 1);
+                            tc::umma_bf16(dcol, ahi, blo, idesc, 1);
+                        }
+                    }
+                    if (kh == 1) tc::umma_commit(&bars[g * 2 + nh]);
+                }
+            }
         }
-        tc::mbar_wait(&bars[g], it & 1);
-        __syncwarp();
-        tc::tc_fence_after();
+        // ---- next tile's operands: in flight during the MMA wait and the epilogue
+        if (tile + tstride < ntiles) load_raw(tile + tstride);
         // ---- epilogue: tanh, tangent scaling, layer 3 (diagonal of the Jacobian product only)
         float p3[D], r3[D];
 #pragma unroll
         for (int j = 0; j < D; ++j) { p3[j] = p.b3[j]; r3[j] = 0.0f; }
 #pragma unroll
         for (int ch = 0; ch < NTC_H / 16; ++ch) {
+            if ((ch & 1) == 0) {
+                tc::mbar_wait(&bars[g * 2 + (ch >> 1)], it & 1);
+                __syncwarp();
+                tc::tc_fence_after();
+            }
             uint32_t va[NV][16];
 #pragma unroll
             for (int v = 0; v < NV; ++v) tc::tmem_ld_32x16(tlane + v * NTC_H + ch * 16, va[v]);
@@ -211,15 +254,11 @@ k_stage_narrow_tc(const __grid_constant__ NtcW<D> p, const __half* __restrict__ 
         if (stage == 6 && b < bf.B) {
 #pragma unroll
             for (int rr = 0; rr < R; ++rr) {
-                const long long at = (long long)rr * Bs + b;
-                float a = c_BT[0] * k1[at];
-                for (int j = 1; j < 6; ++j) a = fmaf(c_BT[j], bf.K[j][at], a);
-                a = fmaf(c_BT[6], rr < D ? y[rr < D ? rr : 0] : tr, a);
-                float ut = dt * a;
-                float unv = unew[at];
-                float sc = fmaf(fmaxf(fabsf(u[at]), fabsf(unv)), reltol, abstol);
+                const float a = fmaf(c_BT[6], rr < D ? y[rr < D ? rr : 0] : tr, ep[rr]);
+                const float ut = dt * a;
+                const float sc = fmaf(fmaxf(fabsf(uo[rr]), fabsf(un[rr])), reltol, abstol);
                 float q = ut / sc;
-                if (unv != unv) q = unv;
+                if (un[rr] != un[rr]) q = un[rr];
                 acc += (double)q * (double)q;
             }
         }

@@ -21,7 +21,8 @@ def run(cid, B, kp):
     return inp, np.asarray(lp), st, time.time() - t
 
 
-for cid, B in (("C2", 128), ("C2", 4096), ("C2", 1000), ("C2", 1 << 17)):
+SMALL = () if os.environ.get("NTC_BIG_ONLY") else (("C2", 128), ("C2", 4096), ("C2", 1000), ("C2", 1 << 17))
+for cid, B in SMALL:
     inp, lp6, st6, _ = run(cid, B, 0)
     _, lp2, st2, _ = run(cid, B, 2)
     print(f"{cid} B={B}: path {st6['kernel_path']} vs {st2['kernel_path']}: naccept {st6['naccept']}/{st2['naccept']} "
@@ -32,7 +33,7 @@ for cid, B in (("C2", 128), ("C2", 4096), ("C2", 1000), ("C2", 1 << 17)):
         print(f"   oracle naccept {rst['naccept']}: path6 err {relerr(lp6, rlp):.3e}  path2 err {relerr(lp2, rlp):.3e}", flush=True)
 
 Bbig = int(sys.argv[1]) if len(sys.argv) > 1 else 1 << 20
-for kp in (0, 2):
+for kp in ((0,) if os.environ.get("NTC_BIG_ONLY") else (0, 2)):
     inp = wl.make_inputs("C2", B=Bbig)
     icnf = make_icnf("C2", kernel_path=kp)
     cnf.set_option(icnf, "time_stages", 1)
