@@ -2,44 +2,52 @@
 // JacVec; reference src/icnf.jl:148-164 through src/utils.jl:19-36) with the one product that holds
 // 94 % of the flops — layer 2 applied to the activation h1 AND to the D tangents tau1_v — on the
 // tensor cores.  The register-resident kernel (cnf_stage_narrow.cu) is bound by the FP32-FMA pipe
-// (13 k FFMA per sample); here a group of 128 threads owns a tile of 128 samples:
+// (13 k FFMA per sample); here a group of 256 threads owns a tile of 128 samples, two threads per
+// sample (each takes one half of the hidden units / accumulator columns):
 //   1. SIMT: stage input u + dt*sum a_ij k_j, layer 1 and the D one-hot tangents in registers,
 //      written as IEEE-half hi/lo planes straight into shared memory in the canonical K-major
 //      SWIZZLE_128B operand layout (no TMA: the operand never exists in global memory);
-//   2. one thread issues (1+D) x 3 x 4 tcgen05.mma (hi*hi + lo*hi + hi*lo = FP32-level products,
-//      as in cnf_stage_tc.cu) against the resident W2 planes; accumulators in TMEM;
+//   2. one thread issues (1+D) x 2 x 4 x 3 tcgen05.mma (hi*hi + lo*hi + hi*lo = FP32-level products,
+//      as in cnf_stage_tc.cu; N = 32 column halves committed separately) against the resident W2
+//      planes; accumulators in TMEM;
 //   3. SIMT epilogue from TMEM: bias + tanh, tangent scaling, layer 3 (only the diagonal of the
-//      D x D Jacobian product is needed for the trace), output rows; at the 7th stage also the
-//      new state and the embedded-error partial sum.
-// Two such groups per CTA (one persistent CTA per SM) alternate, so the tensor pipe works on one
-// tile while the other group's SIMT phases run.  ~2.6 k instructions per sample instead of 17.7 k.
+//      D x D Jacobian product is needed for the trace); the two halves of a sample meet through
+//      shared memory; output rows; at the 7th stage also the new state and the embedded-error
+//      partial sum.
+// Two such groups per CTA (one persistent CTA per SM, 16 warps) alternate, so the tensor pipe works
+// on one tile while the other group's SIMT phases run.  ~2.7 k instructions per sample instead of 17.7 k.
 #include "cnf_internal.h"
 #include "cnf_tc_ptx.cuh"
 
 #define NTC_H 64            // hidden width (one 128-byte swizzle row of halves)
 #define NTC_GROUPS 2
-#define NTC_THREADS (128 * NTC_GROUPS)
+#define NTC_GT 256          // threads per group: 128 sample rows x 2 halves
+#define NTC_WORKERS (NTC_GT * NTC_GROUPS)
+#define NTC_THREADS (NTC_WORKERS + 32)   // + one warp that issues the MMAs of both groups
 #define NTC_PLANE_A (128 * NTC_H * 2)   // 16 KB: one plane of one operand vector
 #define NTC_PLANE_B (NTC_H * NTC_H * 2) // 8 KB: one plane of W2
+#define NTC_C 2.8853900817779268f       // 2 log2(e): tanh(x) = 1 - 2 / (exp2(C x) + 1)
 
-template <int D>
-struct alignas(16) NtcW {   // kernel-parameter weights of layers 1 and 3 (uniform-register operands)
-    float w1[NTC_H * D];    // [o][i]
-    float b1[NTC_H];
-    float b2[NTC_H];
-    float w3[NTC_H * D];    // [o][j]
+// small weights, one float4 per hidden unit (broadcast LDS.128 in the kernel):
+// l1[o] = C * {W1[o][0], W1[o][1], b1[o], 0}; l3[o] = {C * b2[o], W3[0][o], W3[1][o], 0}
+struct alignas(16) NtcW {
+    float4 l1[NTC_H];
+    float4 l3[NTC_H];
     float b3[4];
 };
 
 struct NtcState {
-    void* w_host = nullptr;            // NtcW<D>
+    NtcW* w_host = nullptr;
+    NtcW* d_w = nullptr;
     __half* d_w2 = nullptr;            // hi plane then lo plane, pre-swizzled K-major SWIZZLE_128B
     int D = 0;
     int sms = 148;
 };
 
 template <int D>
-constexpr int ntc_smem_bytes() { return 1024 + 2 * NTC_PLANE_B + NTC_GROUPS * (1 + D) * 2 * NTC_PLANE_A + 64; }
+constexpr int ntc_smem_bytes() {
+    return 1024 + 2 * NTC_PLANE_B + NTC_GROUPS * (1 + D) * 2 * NTC_PLANE_A + (int)sizeof(NtcW) + NTC_GROUPS * 128 * 16 + 64;
+}
 
 // byte offset of the 16-byte chunk `ch` (8 halves along K) of row `r` inside a SWIZZLE_128B K-major tile
 __device__ __forceinline__ uint32_t ntc_swz(int r, int ch) {
@@ -48,15 +56,21 @@ __device__ __forceinline__ uint32_t ntc_swz(int r, int ch) {
 __device__ __forceinline__ void ntc_sts128(uint32_t addr, const uint32_t (&v)[4]) {
     asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]) : "memory");
 }
-__device__ __forceinline__ void ntc_group_sync(int g) {
-    asm volatile("bar.sync %0, 128;" ::"r"(g + 1) : "memory");
+__device__ __forceinline__ void ntc_bar_sync(int id) { asm volatile("bar.sync %0, 256;" ::"r"(id) : "memory"); }
+__device__ __forceinline__ void ntc_bar_arrive(int id) { asm volatile("bar.arrive %0, 256;" ::"r"(id) : "memory"); }
+// tanh of x given cx = C * x
+__device__ __forceinline__ float ntc_tanh_scaled(float cx) {
+    float t, r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(cx));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(t + 1.0f));
+    return fmaf(-2.0f, r, 1.0f);
 }
 
 // stage numbering as in k_stage_narrow_test_jvp: 0 k1 = f(u0); -1 initial-dt probe -> K[1];
 // 1..5 -> K[stage]; 6 -> new state, k7 and the error partial sum
 template <int D>
-__global__ void __launch_bounds__(NTC_THREADS, 1)
-k_stage_narrow_tc(const __grid_constant__ NtcW<D> p, const __half* __restrict__ w2planes, CnfCtrl* __restrict__ c,
+__global__ void __maxnreg__(96)
+k_stage_narrow_tc(const NtcW* __restrict__ wsmall, const __half* __restrict__ w2planes, CnfCtrl* __restrict__ c,
                   CnfBufs bf, int stage, int check_done, int ntiles) {
     if (check_done && c->done) return;
     constexpr int R = D + 1;
@@ -66,21 +80,30 @@ k_stage_narrow_tc(const __grid_constant__ NtcW<D> p, const __half* __restrict__ 
     uint8_t* sgen = ntc_raw + (sbase - tc::smem_u32(ntc_raw));
     const uint32_t sB = sbase;                                       // W2 hi, lo planes
     const uint32_t sA = sbase + 2 * NTC_PLANE_B;                     // [group][vector][plane]
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sgen + 2 * NTC_PLANE_B + NTC_GROUPS * NV * 2 * NTC_PLANE_A);
+    uint8_t* after = sgen + 2 * NTC_PLANE_B + NTC_GROUPS * NV * 2 * NTC_PLANE_A;
+    const NtcW* sw = reinterpret_cast<const NtcW*>(after);
+    float4* xch = reinterpret_cast<float4*>(after + sizeof(NtcW));   // [group][row]: partial sums of the upper half
+    uint64_t* bars = reinterpret_cast<uint64_t*>(after + sizeof(NtcW) + NTC_GROUPS * 128 * 16);
+    uint64_t* full = bars + NTC_GROUPS;   // operand planes of a tile written (256 arrivals)
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * NTC_GROUPS);
     __shared__ double sh_red[32];
 
     const int tid = threadIdx.x, warp = tid >> 5;
-    const int g = tid >> 7;              // group
-    const int r = tid & 127;             // row of the tile = TMEM lane
-    // ---- one-time setup: W2 planes into shared memory, barriers, TMEM
+    const int g = tid >> 8;              // group
+    const int gt = tid & (NTC_GT - 1);
+    const int hw = gt >> 7;              // which half of the hidden units / accumulator columns
+    const int r = gt & 127;              // row of the tile = TMEM lane
+    // ---- one-time setup: W2 planes and the small weights into shared memory, barriers, TMEM
     {
         const uint4* src = reinterpret_cast<const uint4*>(w2planes);
         uint4* dst = reinterpret_cast<uint4*>(sgen);
         for (int i = tid; i < 2 * NTC_PLANE_B / 16; i += NTC_THREADS) dst[i] = src[i];
+        const uint4* src2 = reinterpret_cast<const uint4*>(wsmall);
+        uint4* dst2 = reinterpret_cast<uint4*>(after);
+        for (int i = tid; i < (int)sizeof(NtcW) / 16; i += NTC_THREADS) dst2[i] = src2[i];
     }
     if (tid == 0) {
-        for (int i = 0; i < 2 * NTC_GROUPS; ++i) tc::mbar_init(&bars[i], 1);
+        for (int i = 0; i < NTC_GROUPS; ++i) { tc::mbar_init(&bars[i], 1); tc::mbar_init(&full[i], NTC_GT); }
         tc::fence_barrier_init();
     }
     if (warp == 0) tc::tmem_alloc(tmem_slot, 512);
@@ -89,10 +112,58 @@ k_stage_narrow_tc(const __grid_constant__ NtcW<D> p, const __half* __restrict__ 
     __syncthreads();
     tc::tc_fence_after();
     const uint32_t tmem = *tmem_slot + (uint32_t)g * 256u;          // this group's accumulators: NV x 64 columns
-    const uint32_t tlane = tmem + ((uint32_t)((warp & 3) * 32) << 16);
-    const uint32_t idesc64 = tc::umma_idesc_f16(128, NTC_H, 0), idesc32 = tc::umma_idesc_f16(128, NTC_H / 2, 0);
+    const uint32_t tlane = tmem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)hw * 32u;
     const uint32_t myA = sA + (uint32_t)g * (NV * 2 * NTC_PLANE_A);
+    const int barB = 1 + g;
 
+    double acc = 0.0;
+    const int tile0 = blockIdx.x * NTC_GROUPS + g, tstride = gridDim.x * NTC_GROUPS;
+    if (warp == NTC_WORKERS / 32) {
+        // ---- MMA issuer: layer 2 for all operand vectors of a tile as soon as its planes are written;
+        // 3 MMAs per k-step (hi*hi + lo*hi + hi*lo), one commit per tile
+        if ((tid & 31) == 0) {
+            const uint32_t idesc = tc::umma_idesc_f16(128, NTC_H, 0);
+            const uint64_t dhi = (uint64_t)(tc::umma_desc_sw128(0) >> 32) << 32;
+            const uint32_t blo0 = (uint32_t)tc::umma_desc_sw128(sB);
+            int left[NTC_GROUPS];
+            uint32_t ph[NTC_GROUPS];
+#pragma unroll
+            for (int q = 0; q < NTC_GROUPS; ++q) {
+                const int t0 = blockIdx.x * NTC_GROUPS + q;
+                left[q] = t0 < ntiles ? (ntiles - 1 - t0) / tstride + 1 : 0;
+                ph[q] = 0;
+            }
+            uint32_t spins = 0;
+            while (left[0] > 0 || left[1] > 0) {
+#pragma unroll
+                for (int q = 0; q < NTC_GROUPS; ++q) {
+                    if (left[q] > 0 && tc::mbar_try_wait(&full[q], ph[q])) {
+                        tc::tc_fence_after();
+                        const uint32_t alo0 = (uint32_t)tc::umma_desc_sw128(sA + (uint32_t)q * (NV * 2 * NTC_PLANE_A));
+                        const uint32_t tq = *tmem_slot + (uint32_t)q * 256u;
+#pragma unroll
+                        for (int v = 0; v < NV; ++v) {
+#pragma unroll
+                            for (int kk = 0; kk < NTC_H / 16; ++kk) {
+                                const uint64_t ahi = dhi | (alo0 + (uint32_t)(((v * 2) * NTC_PLANE_A + kk * 32) >> 4));
+                                const uint64_t alo = dhi | (alo0 + (uint32_t)(((v * 2 + 1) * NTC_PLANE_A + kk * 32) >> 4));
+                                const uint64_t bhi = dhi | (blo0 + (uint32_t)((kk * 32) >> 4));
+                                const uint64_t blo = dhi | (blo0 + (uint32_t)((NTC_PLANE_B + kk * 32) >> 4));
+                                tc::umma_bf16(tq + v * NTC_H, ahi, bhi, idesc, kk != 0);
+                                tc::umma_bf16(tq + v * NTC_H, alo, bhi, idesc, 1);
+                                tc::umma_bf16(tq + v * NTC_H, ahi, blo, idesc, 1);
+                            }
+                        }
+                        tc::umma_commit(&bars[q]);
+                        ph[q] ^= 1;
+                        left[q]--;
+                        spins = 0;
+                    }
+                }
+                if (++spins > (1u << 26)) { asm volatile("trap;"); }
+            }
+        }
+    } else {
     const long long Bs = bf.Bs;
     const float* u = bf.slots[cnf_slot(c, stage <= 0 ? 0 : c->naccept)];
     const float* k1 = bf.K[c->k1idx];
@@ -101,8 +172,8 @@ k_stage_narrow_tc(const __grid_constant__ NtcW<D> p, const __half* __restrict__ 
     const float dt = c->dt;
     const float hh = c->tdir * c->dt0init;
     const float reltol = c->reltol, abstol = c->abstol;
-    const int nrow = (stage == 6) ? R : D;   // rows D.. only at the 7th stage (pure quadrature rows)
-    double acc = 0.0;
+    // rows D.. only at the 7th stage (pure quadrature rows), and only in the thread that finishes the sample
+    const int nrow = (stage == 6 && hw == 0) ? R : D;
 
     // raw stage-input operands of one tile: issued as independent loads one tile ahead (an in-order
     // warp that loads at the point of use pays one DRAM latency per k_j)
@@ -122,7 +193,6 @@ k_stage_narrow_tc(const __grid_constant__ NtcW<D> p, const __half* __restrict__ 
         }
     };
 
-    const int tile0 = blockIdx.x * NTC_GROUPS + g, tstride = gridDim.x * NTC_GROUPS;
     if (tile0 < ntiles) load_raw(tile0);
     uint32_t it = 0;
     for (int tile = tile0; tile < ntiles; tile += tstride, ++it) {
@@ -141,7 +211,7 @@ k_stage_narrow_tc(const __grid_constant__ NtcW<D> p, const __half* __restrict__ 
                     for (int j = 1; j < 6; ++j)
                         if (j < stage) a = fmaf(c_A[stage][j], rk[rr][j], a);
                     v = fmaf(dt, a, ru[rr]);
-                    if (stage == 6) {
+                    if (stage == 6 && hw == 0) {
                         unew[(long long)rr * Bs + b] = v;
                         float e = c_BT[0] * rk[rr][0];
 #pragma unroll
@@ -152,100 +222,81 @@ k_stage_narrow_tc(const __grid_constant__ NtcW<D> p, const __half* __restrict__ 
                 if (rr < D) z[rr < D ? rr : 0] = v;
             }
         }
-        // ---- layer 1 and the D one-hot tangents -> hi/lo operand planes in shared memory, in two K halves:
-        // the MMAs of the first 32 hidden units run while the second half is computed
+        // ---- layer 1 and the D one-hot tangents (scaled by C) of this thread's 32 hidden units -> hi/lo
+        // operand planes in shared memory
 #pragma unroll
-        for (int kh = 0; kh < 2; ++kh) {
+        for (int cq = 0; cq < 4; ++cq) {
+            const int cb = hw * 4 + cq;
+            float x[NV][8];
 #pragma unroll
-            for (int cb = kh * 4; cb < kh * 4 + 4; ++cb) {
-                float x[NV][8];
-#pragma unroll
-                for (int q = 0; q < 8; ++q) {
-                    const int o = cb * 8 + q;
-                    float a = p.b1[o];
-#pragma unroll
-                    for (int i = 0; i < D; ++i) a = fmaf(p.w1[o * D + i], z[i], a);
-                    const float h = tc_tanh(a);
-                    const float d = fmaf(-h, h, 1.0f);
-                    x[0][q] = h;
-#pragma unroll
-                    for (int v = 0; v < D; ++v) x[1 + v][q] = p.w1[o * D + v] * d;
-                }
-                const uint32_t off = ntc_swz(r, cb);
-#pragma unroll
-                for (int v = 0; v < NV; ++v) {
-                    uint32_t hi[4], lo[4];
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) tc_split2<0>(x[v][2 * q], x[v][2 * q + 1], hi[q], lo[q]);
-                    ntc_sts128(myA + (uint32_t)(v * 2) * NTC_PLANE_A + off, hi);
-                    ntc_sts128(myA + (uint32_t)(v * 2 + 1) * NTC_PLANE_A + off, lo);
-                }
+            for (int q = 0; q < 8; ++q) {
+                const float4 w = sw->l1[cb * 8 + q];
+                float a = fmaf(w.x, z[0], w.z);
+                if (D > 1) a = fmaf(w.y, z[D > 1 ? 1 : 0], a);
+                const float h = ntc_tanh_scaled(a);
+                const float d = fmaf(-h, h, 1.0f);
+                x[0][q] = h;
+                x[1][q] = w.x * d;
+                if (D > 1) x[D > 1 ? 2 : 1][q] = w.y * d;
             }
-            tc::fence_proxy_async();     // generic-proxy writes -> visible to the tensor core's async proxy
-            if (kh == 0) tc::tc_fence_before();   // the previous tile's tcgen05.ld are ordered before the barrier
-            ntc_group_sync(g);
-            // ---- layer 2 for all operand vectors, one issuing thread: 3 MMAs per k-step (hi*hi + lo*hi + hi*lo)
-            if (r == 0) {
-                tc::tc_fence_after();
-                // second K half: the two N halves commit separately so the epilogue starts on columns 0..31
+            const uint32_t off = ntc_swz(r, cb);
 #pragma unroll
-                for (int nh = 0; nh < 2; ++nh) {
-                    if (kh == 0 && nh == 1) break;
-                    const uint32_t idesc = kh == 0 ? idesc64 : idesc32;
-                    const uint32_t boff = (uint32_t)nh * (32 * 128);     // B rows 32.. = output units 32..
+            for (int v = 0; v < NV; ++v) {
+                uint32_t hi[4], lo[4];
 #pragma unroll
-                    for (int v = 0; v < NV; ++v) {
-#pragma unroll
-                        for (int kk = kh * 2; kk < kh * 2 + 2; ++kk) {
-                            const uint64_t ahi = tc::umma_desc_sw128(myA + (uint32_t)(v * 2) * NTC_PLANE_A + kk * 32);
-                            const uint64_t alo = tc::umma_desc_sw128(myA + (uint32_t)(v * 2 + 1) * NTC_PLANE_A + kk * 32);
-                            const uint64_t bhi = tc::umma_desc_sw128(sB + boff + kk * 32);
-                            const uint64_t blo = tc::umma_desc_sw128(sB + NTC_PLANE_B + boff + kk * 32);
-                            const uint32_t dcol = tmem + v * NTC_H + nh * 32;
-                            tc::umma_bf16(dcol, ahi, bhi, idesc, kk != 0);
-                            tc::umma_bf16(dcol, alo, bhi, idesc, 1);
-                            tc::umma_bf16(dcol, ahi, blo, idesc, 1);
-                        }
-                    }
-                    if (kh == 1) tc::umma_commit(&bars[g * 2 + nh]);
-                }
+                for (int q = 0; q < 4; ++q) tc_split2<0>(x[v][2 * q], x[v][2 * q + 1], hi[q], lo[q]);
+                ntc_sts128(myA + (uint32_t)(v * 2) * NTC_PLANE_A + off, hi);
+                ntc_sts128(myA + (uint32_t)(v * 2 + 1) * NTC_PLANE_A + off, lo);
             }
         }
+        tc::fence_proxy_async();     // generic-proxy writes -> visible to the tensor core's async proxy
+        tc::tc_fence_before();       // the previous tile's tcgen05.ld are ordered before the arrival
+        tc::mbar_arrive(&full[g]);   // the issuer warp starts this tile's MMAs after all 256 arrivals
         // ---- next tile's operands: in flight during the MMA wait and the epilogue
         if (tile + tstride < ntiles) load_raw(tile + tstride);
-        // ---- epilogue: tanh, tangent scaling, layer 3 (diagonal of the Jacobian product only)
+        // ---- epilogue on this thread's 32 columns: tanh, tangent scaling, layer 3 (diagonal of the
+        // Jacobian product only; the tangents carry the factor C until the end)
         float p3[D], r3[D];
 #pragma unroll
-        for (int j = 0; j < D; ++j) { p3[j] = p.b3[j]; r3[j] = 0.0f; }
+        for (int j = 0; j < D; ++j) { p3[j] = 0.0f; r3[j] = 0.0f; }
+        tc::mbar_wait(&bars[g], it & 1);
+        __syncwarp();
+        tc::tc_fence_after();
 #pragma unroll
-        for (int ch = 0; ch < NTC_H / 16; ++ch) {
-            if ((ch & 1) == 0) {
-                tc::mbar_wait(&bars[g * 2 + (ch >> 1)], it & 1);
-                __syncwarp();
-                tc::tc_fence_after();
-            }
+        for (int ch = 0; ch < 2; ++ch) {
             uint32_t va[NV][16];
 #pragma unroll
             for (int v = 0; v < NV; ++v) tc::tmem_ld_32x16(tlane + v * NTC_H + ch * 16, va[v]);
             tc::tmem_ld_wait();
 #pragma unroll
             for (int q = 0; q < 16; ++q) {
-                const int o = ch * 16 + q;
-                const float h = tc_tanh(__uint_as_float(va[0][q]) + p.b2[o]);
+                const float4 w = sw->l3[hw * 32 + ch * 16 + q];
+                const float h = ntc_tanh_scaled(fmaf(__uint_as_float(va[0][q]), NTC_C, w.x));
                 const float d = fmaf(-h, h, 1.0f);
-#pragma unroll
-                for (int j = 0; j < D; ++j) {
-                    const float w3 = p.w3[o * D + j];
-                    p3[j] = fmaf(w3, h, p3[j]);
-                    r3[j] = fmaf(w3, __uint_as_float(va[1 + j][q]) * d, r3[j]);
+                p3[0] = fmaf(w.y, h, p3[0]);
+                r3[0] = fmaf(w.y, __uint_as_float(va[1][q]) * d, r3[0]);
+                if (D > 1) {
+                    p3[D > 1 ? 1 : 0] = fmaf(w.z, h, p3[D > 1 ? 1 : 0]);
+                    r3[D > 1 ? 1 : 0] = fmaf(w.z, __uint_as_float(va[D > 1 ? 2 : 1][q]) * d, r3[D > 1 ? 1 : 0]);
                 }
             }
+        }
+        if (hw == 1) {
+            xch[g * 128 + r] = make_float4(p3[0], r3[0], D > 1 ? p3[D > 1 ? 1 : 0] : 0.0f, D > 1 ? r3[D > 1 ? 1 : 0] : 0.0f);
+            ntc_bar_arrive(barB);
+            continue;
+        }
+        ntc_bar_sync(barB);
+        {
+            const float4 o = xch[g * 128 + r];
+            p3[0] += o.x; r3[0] += o.y;
+            if (D > 1) { p3[D > 1 ? 1 : 0] += o.z; r3[D > 1 ? 1 : 0] += o.w; }
         }
         float y[D], tr = 0.0f;
 #pragma unroll
         for (int j = 0; j < D; ++j) {
-            y[j] = cnf_tanh_fastpath(p3[j]);
-            tr -= fmaf(-y[j], y[j], 1.0f) * r3[j];
+            y[j] = cnf_tanh_fastpath(p3[j] + sw->b3[j]);
+            tr -= fmaf(-y[j], y[j], 1.0f) * (r3[j] * (1.0f / NTC_C));
         }
 #pragma unroll
         for (int j = 0; j < D; ++j) kout[(long long)j * Bs + b] = y[j];
@@ -263,6 +314,7 @@ k_stage_narrow_tc(const __grid_constant__ NtcW<D> p, const __half* __restrict__ 
             }
         }
     }
+    }   // workers
     tc::tc_fence_before();
     if (stage == 6) {
         acc = cnf_block_sum(acc, sh_red);
@@ -273,17 +325,15 @@ k_stage_narrow_tc(const __grid_constant__ NtcW<D> p, const __half* __restrict__ 
 }
 
 // ------------------------------------------------------------------ host side
-template <int D>
-static void ntc_pack(const cnf_handle* h, const float* theta, NtcW<D>* out, __half* planes) {
+static void ntc_pack(const cnf_handle* h, const float* theta, NtcW* out, __half* planes) {
+    const int D = h->cfg.D;
     memset(out, 0, sizeof(*out));
     const float* W1 = theta + h->w_off[0];   // col-major H x D
     const float* W2 = theta + h->w_off[1];   // col-major H x H: W2[i * H + o]
     const float* W3 = theta + h->w_off[2];   // col-major D x H
     for (int o = 0; o < NTC_H; ++o) {
-        for (int i = 0; i < D; ++i) out->w1[o * D + i] = W1[i * NTC_H + o];
-        out->b1[o] = theta[h->b_off[0] + o];
-        out->b2[o] = theta[h->b_off[1] + o];
-        for (int j = 0; j < D; ++j) out->w3[o * D + j] = W3[o * D + j];
+        out->l1[o] = make_float4(NTC_C * W1[o], D > 1 ? NTC_C * W1[NTC_H + o] : 0.0f, NTC_C * theta[h->b_off[0] + o], 0.0f);
+        out->l3[o] = make_float4(NTC_C * theta[h->b_off[1] + o], W3[o * D], D > 1 ? W3[o * D + 1] : 0.0f, 0.0f);
     }
     for (int j = 0; j < D; ++j) out->b3[j] = theta[h->b_off[2] + j];
     // B operand: row n = output unit, K = input unit; K-major SWIZZLE_128B (same layout as ntc_swz)
@@ -315,15 +365,16 @@ int ntc_set_params(cnf_handle* h, const float* theta_host) {
         s->D = h->cfg.D;
         cudaDeviceProp prop;
         if (cudaGetDeviceProperties(&prop, h->device) == cudaSuccess) s->sms = prop.multiProcessorCount;
-        s->w_host = (s->D == 1) ? (void*)new NtcW<1>() : (void*)new NtcW<2>();
+        s->w_host = new NtcW();
+        h->ntc_state = s;
+        CNF_CUDA(cudaMalloc(&s->d_w, sizeof(NtcW)));
         CNF_CUDA(cudaMalloc(&s->d_w2, 2 * NTC_PLANE_B));
         CNF_CUDA(cudaFuncSetAttribute(k_stage_narrow_tc<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ntc_smem_bytes<1>()));
         CNF_CUDA(cudaFuncSetAttribute(k_stage_narrow_tc<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, ntc_smem_bytes<2>()));
-        h->ntc_state = s;
     }
     std::vector<__half> planes(NTC_PLANE_B);   // 2 planes x NTC_PLANE_B / 2 halves
-    if (s->D == 1) ntc_pack<1>(h, theta_host, (NtcW<1>*)s->w_host, planes.data());
-    else ntc_pack<2>(h, theta_host, (NtcW<2>*)s->w_host, planes.data());
+    ntc_pack(h, theta_host, s->w_host, planes.data());
+    CNF_CUDA(cudaMemcpyAsync(s->d_w, s->w_host, sizeof(NtcW), cudaMemcpyHostToDevice, h->stream));
     CNF_CUDA(cudaMemcpyAsync(s->d_w2, planes.data(), 2 * NTC_PLANE_B, cudaMemcpyHostToDevice, h->stream));
     CNF_CUDA(cudaStreamSynchronize(h->stream));
     return CNF_OK;
@@ -331,7 +382,8 @@ int ntc_set_params(cnf_handle* h, const float* theta_host) {
 void ntc_free(cnf_handle* h) {
     NtcState* s = (NtcState*)h->ntc_state;
     if (!s) return;
-    if (s->D == 1) delete (NtcW<1>*)s->w_host; else delete (NtcW<2>*)s->w_host;
+    delete s->w_host;
+    cudaFree(s->d_w);
     cudaFree(s->d_w2);
     delete s;
     h->ntc_state = nullptr;
@@ -343,11 +395,11 @@ int launch_stage_narrow_tc(cnf_handle* h, const CnfBufs& bf, int stage, int chec
     int grid = (ntiles + NTC_GROUPS - 1) / NTC_GROUPS;
     if (grid > s->sms) grid = s->sms;
     if (s->D == 1)
-        k_stage_narrow_tc<1><<<grid, NTC_THREADS, ntc_smem_bytes<1>(), h->stream>>>(*(const NtcW<1>*)s->w_host, s->d_w2, h->d_ctrl,
-                                                                                   bf, stage, check_done, ntiles);
+        k_stage_narrow_tc<1><<<grid, NTC_THREADS, ntc_smem_bytes<1>(), h->stream>>>(s->d_w, s->d_w2, h->d_ctrl, bf, stage,
+                                                                                   check_done, ntiles);
     else
-        k_stage_narrow_tc<2><<<grid, NTC_THREADS, ntc_smem_bytes<2>(), h->stream>>>(*(const NtcW<2>*)s->w_host, s->d_w2, h->d_ctrl,
-                                                                                   bf, stage, check_done, ntiles);
+        k_stage_narrow_tc<2><<<grid, NTC_THREADS, ntc_smem_bytes<2>(), h->stream>>>(s->d_w, s->d_w2, h->d_ctrl, bf, stage,
+                                                                                   check_done, ntiles);
     h->launches++;
     return CNF_OK;
 }
