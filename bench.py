@@ -289,6 +289,33 @@ def main():
                             "finish early idle inside the warp), so it is an upper bound on useful flops",
                     "stage_ms": solve_ms, "stage_launches": 1, "kernel_path": 4,
                     "stage_share_of_step": ms_solve / ms_dev if ms_dev else None}
+    elif st["kernel_path"] == 6:
+        # narrow exact-trace nets with layer 2 (94 % of the flops) on tcgen05: the MMAs execute 3 f16 flops per
+        # algorithmic flop of that layer (FP16 hi/lo split); layers 1 and 3 and all elementwise work stay SIMT
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except (OSError, ValueError):
+            pass
+        peak = float(peaks.get("bf16_tflops_sustained", 1400.0))
+        dims = c["dims"]
+        D = c["nvars"] + c["naug"]
+        mma_flops = 3 * 2 * dims[1] * dims[2] * (1 + D) * B      # executed by tcgen05.mma per evaluation
+        executed = mma_flops / (stage_ms * 1e-3) / 1e12 if stage_ms > 0 else 0.0
+        roofline = {"bound": "tensor", "achieved": executed, "peak": peak, "unit": "TFLOP/s",
+                    "frac": executed / peak, "traffic": traffic,
+                    "kernel": "k_stage_narrow_tc: RK stage kernel, layer 2 of the activation and the D tangents as "
+                              "tcgen05 MMAs on operands the SIMT phase writes into swizzled shared memory",
+                    "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback 1.4 PFLOP/s sustained",
+                    "note": "achieved = f16 MMA flops executed (3 per algorithmic flop of layer 2: hi*hi + lo*hi + hi*lo); "
+                            "the kernel is bound by the SIMT prologue/epilogue (tanh, hi/lo split, layers 1 and 3: "
+                            "~2.9 k instructions per sample, issue slots 56-65 % busy in ncu), not by the tensor pipe; "
+                            "algorithmic_tflops / fp32_fma_peak shows how far it is above the FP32-FMA roofline that "
+                            "bounded the register-resident kernel (kernel_path 2)",
+                    "algorithmic_tflops": achieved, "fp32_fma_peak": pk.value,
+                    "algorithmic_over_fp32_fma_peak": achieved / pk.value if pk.value else None,
+                    "stage_ms": stage_ms, "stage_launches": n_stage, "kernel_path": 6,
+                    "stage_share_of_step": ms_stage / ms_dev if ms_dev else None}
     elif st["kernel_path"] == 3:
         # tensor path: FP16 hi/lo operand splitting executes 3 f16 MMA flops per algorithmic flop
         peaks = {}

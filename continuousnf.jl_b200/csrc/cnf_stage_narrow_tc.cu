@@ -160,7 +160,8 @@ k_stage_narrow_tc(const NtcW* __restrict__ wsmall, const __half* __restrict__ w2
                         spins = 0;
                     }
                 }
-                if (++spins > (1u << 26)) { asm volatile("trap;"); }
+                __nanosleep(32);   // a busy poll would take issue slots from the four worker warps of this scheduler
+                if (++spins > (1u << 24)) { asm volatile("trap;"); }
             }
         }
     } else {
@@ -263,14 +264,14 @@ k_stage_narrow_tc(const NtcW* __restrict__ wsmall, const __half* __restrict__ w2
         __syncwarp();
         tc::tc_fence_after();
 #pragma unroll
-        for (int ch = 0; ch < 2; ++ch) {
-            uint32_t va[NV][16];
+        for (int ch = 0; ch < 4; ++ch) {
+            uint32_t va[NV][8];
 #pragma unroll
-            for (int v = 0; v < NV; ++v) tc::tmem_ld_32x16(tlane + v * NTC_H + ch * 16, va[v]);
+            for (int v = 0; v < NV; ++v) tc::tmem_ld_32x8(tlane + v * NTC_H + ch * 8, va[v]);
             tc::tmem_ld_wait();
 #pragma unroll
-            for (int q = 0; q < 16; ++q) {
-                const float4 w = sw->l3[hw * 32 + ch * 16 + q];
+            for (int q = 0; q < 8; ++q) {
+                const float4 w = sw->l3[hw * 32 + ch * 8 + q];
                 const float h = ntc_tanh_scaled(fmaf(__uint_as_float(va[0][q]), NTC_C, w.x));
                 const float d = fmaf(-h, h, 1.0f);
                 p3[0] = fmaf(w.y, h, p3[0]);

@@ -169,7 +169,60 @@ def test_tensor_path_is_selected_for_wide_train_and_narrow_for_c2():
     inp = wl.make_inputs("C2", B=256)
     icnf = make_icnf("C2")
     cnf.inference(icnf, cnf.TestMode(), inp["xs"].T, inp["theta"], {})
-    assert cnf.last_stats(icnf)["kernel_path"] == 2
+    assert cnf.last_stats(icnf)["kernel_path"] == 6     # narrow net, layer 2 on tcgen05
+    icnf = make_icnf("C2", kernel_path=2)
+    cnf.inference(icnf, cnf.TestMode(), inp["xs"].T, inp["theta"], {})
+    assert cnf.last_stats(icnf)["kernel_path"] == 2     # register-resident SIMT kernel stays reachable
+
+
+def _narrow_model(nvars, kernel_path, tspan=(0.0, 1.0)):
+    nn = cnf.Chain(cnf.Dense(nvars, 64, "tanh"), cnf.Dense(64, 64, "tanh"), cnf.Dense(64, nvars, "tanh"))
+    return cnf.construct(cnf.FFJORD, nn, nvars, 0, compute_mode=cnf.DIJacVecMatrixMode(), tspan=tspan,
+                         resource=cnf.B200Libs(0, kernel_path), rng=np.random.default_rng(1))
+
+
+@pytest.mark.parametrize("nvars,B", [(2, 1), (2, 129), (2, 1000), (2, 40000), (1, 77), (1, 5000)])
+def test_narrow_tensor_path_matches_oracle_and_simt_kernel(nvars, B):
+    """k_stage_narrow_tc (kernel_path 6: layer 2 as FP16 hi/lo x3 tcgen05 MMAs) against the oracle and the
+    register-resident FP32 kernel (kernel_path 2): ragged batches, one tile to several tiles per group,
+    D = 1 and D = 2"""
+    dims = [nvars, 64, 64, nvars]
+    rng = np.random.default_rng(100 + B)
+    theta = wl.glorot_theta(dims, rng)
+    theta = (theta + 0.05 * rng.normal(size=theta.shape)).astype(np.float32)   # non-zero biases
+    xs = rng.normal(0, 1.5, (B, nvars)).astype(np.float32)
+    out = {}
+    for kp in (0, 2):
+        icnf = _narrow_model(nvars, kp)
+        lp, _ = cnf.inference(icnf, cnf.TestMode(), xs.T, theta, {})
+        st = cnf.last_stats(icnf)
+        assert st["kernel_path"] == (6 if kp == 0 else 2) and st["retcode"] == 0
+        out[kp] = (np.asarray(lp), st["naccept"], st["nreject"])
+    assert abs(out[0][1] - out[2][1]) <= 1
+    if out[0][1:] == out[2][1:]:
+        assert relerr(out[0][0], out[2][0]) < 1e-4
+    if B <= 5000:
+        cfg = O.make_config(nvars, 0, dims, trace_mode=1)
+        rlp, _, _, rst = O.logdensity(cfg, theta, 0, xs, None, None, 0.0, 1.0)
+        assert abs(out[0][1] - rst["naccept"]) <= 1
+        if out[0][1] == rst["naccept"]:
+            assert relerr(out[0][0], rlp) < 1e-4
+
+
+def test_narrow_tensor_path_generate_roundtrip_and_nan():
+    """reverse-time solve (generate) on the narrow tensor path returns the data; a NaN sample poisons the
+    whole-batch error norm exactly like the reference's matrix-mode solve (retcode != 0, no hang)"""
+    inp = wl.make_inputs("C2", B=3000)
+    icnf = make_icnf("C2")
+    lp, _, z = cnf.inference(icnf, cnf.TestMode(), inp["xs"].T, inp["theta"], {}, return_z=True)
+    assert cnf.last_stats(icnf)["kernel_path"] == 6
+    xs2 = cnf.generate(icnf, cnf.TestMode(), inp["theta"], {}, 3000, z0=np.asarray(z))
+    assert cnf.last_stats(icnf)["kernel_path"] == 6
+    assert np.max(np.abs(np.asarray(xs2).T - inp["xs"])) < 5e-3
+    bad = inp["xs"].copy()
+    bad[17, 0] = np.nan
+    lpb, _ = cnf.inference(icnf, cnf.TestMode(), bad.T, inp["theta"], {})
+    assert cnf.last_stats(icnf)["retcode"] != 0 or not np.isfinite(np.asarray(lpb)[17])
 
 
 @pytest.mark.parametrize("nvars,naug,C,hidden,B", [(5, 0, 3, (160, 96), 300), (3, 2, 0, (64, 32, 96), 1000), (20, 0, 0, (320,), 130)])
