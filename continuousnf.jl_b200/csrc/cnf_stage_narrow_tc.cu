@@ -7,15 +7,16 @@
 //   1. SIMT: stage input u + dt*sum a_ij k_j, layer 1 and the D one-hot tangents in registers,
 //      written as IEEE-half hi/lo planes straight into shared memory in the canonical K-major
 //      SWIZZLE_128B operand layout (no TMA: the operand never exists in global memory);
-//   2. one thread issues (1+D) x 2 x 4 x 3 tcgen05.mma (hi*hi + lo*hi + hi*lo = FP32-level products,
-//      as in cnf_stage_tc.cu; N = 32 column halves committed separately) against the resident W2
-//      planes; accumulators in TMEM;
+//   2. the issuer thread launches (1+D) x 4 x 3 tcgen05.mma (M = 128, N = 64, K = 16; hi*hi + lo*hi + hi*lo
+//      = FP32-level products, as in cnf_stage_tc.cu) against the resident W2 planes; accumulators in TMEM;
 //   3. SIMT epilogue from TMEM: bias + tanh, tangent scaling, layer 3 (only the diagonal of the
 //      D x D Jacobian product is needed for the trace); the two halves of a sample meet through
 //      shared memory; output rows; at the 7th stage also the new state and the embedded-error
 //      partial sum.
-// Two such groups per CTA (one persistent CTA per SM, 16 warps) alternate, so the tensor pipe works
-// on one tile while the other group's SIMT phases run.  ~2.7 k instructions per sample instead of 17.7 k.
+// Two such groups per CTA (one persistent CTA per SM, 16 worker warps) alternate, so the tensor pipe works
+// on one tile while the other group's SIMT phases run; a 17th warp issues the MMAs of both groups as
+// soon as a tile's 256 writers have arrived on its mbarrier.  The SIMT phases use the packed f32x2
+// instructions (FFMA2/FMUL2/FADD2): ~2.4 k instructions per sample instead of 17.7 k.
 #include "cnf_internal.h"
 #include "cnf_tc_ptx.cuh"
 
@@ -28,11 +29,15 @@
 #define NTC_PLANE_B (NTC_H * NTC_H * 2) // 8 KB: one plane of W2
 #define NTC_C 2.8853900817779268f       // 2 log2(e): tanh(x) = 1 - 2 / (exp2(C x) + 1)
 
-// small weights, one float4 per hidden unit (broadcast LDS.128 in the kernel):
-// l1[o] = C * {W1[o][0], W1[o][1], b1[o], 0}; l3[o] = {C * b2[o], W3[0][o], W3[1][o], 0}
+// small weights per PAIR of hidden units (o, o+1) — the SIMT phases run on packed f32x2 instructions
+// (FFMA2 / FMUL2 / FADD2: one issue slot for two hidden units) — read with broadcast LDS.128 / LDS.64:
+// l1w[p] = C * {W1[o][0], W1[o+1][0], W1[o][1], W1[o+1][1]}, l1b[p] = C * {b1[o], b1[o+1]};
+// l3w[p] = {C * b2[o], C * b2[o+1], W3[0][o], W3[0][o+1]}, l3v[p] = {W3[1][o], W3[1][o+1]}
 struct alignas(16) NtcW {
-    float4 l1[NTC_H];
-    float4 l3[NTC_H];
+    float4 l1w[NTC_H / 2];
+    float4 l3w[NTC_H / 2];
+    float2 l1b[NTC_H / 2];
+    float2 l3v[NTC_H / 2];
     float b3[4];
 };
 
@@ -58,6 +63,52 @@ __device__ __forceinline__ void ntc_sts128(uint32_t addr, const uint32_t (&v)[4]
 }
 __device__ __forceinline__ void ntc_bar_sync(int id) { asm volatile("bar.sync %0, 256;" ::"r"(id) : "memory"); }
 __device__ __forceinline__ void ntc_bar_arrive(int id) { asm volatile("bar.arrive %0, 256;" ::"r"(id) : "memory"); }
+// wait with back-off: a spinning try_wait loop takes issue slots from the other group's warps on the same scheduler
+__device__ __forceinline__ void ntc_wait_sleep(uint64_t* bar, uint32_t parity) {
+    for (uint32_t it = 0; !tc::mbar_try_wait(bar, parity); ++it) {
+        __nanosleep(64);
+        if (it > (1u << 24)) { asm volatile("trap;"); }
+    }
+}
+// packed FP32 pairs (sm_100 f32x2 instructions); ptxas keeps the pairs in aligned registers, no moves
+__device__ __forceinline__ float2 ntc_fma2(float2 a, float2 b, float2 c) {
+    float2 d;
+    asm("{.reg .b64 ra, rb, rc, rd;\n\tmov.b64 ra, {%2,%3};\n\tmov.b64 rb, {%4,%5};\n\tmov.b64 rc, {%6,%7};\n\t"
+        "fma.rn.f32x2 rd, ra, rb, rc;\n\tmov.b64 {%0,%1}, rd;}"
+        : "=f"(d.x), "=f"(d.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y), "f"(c.x), "f"(c.y));
+    return d;
+}
+__device__ __forceinline__ float2 ntc_mul2(float2 a, float2 b) {
+    float2 d;
+    asm("{.reg .b64 ra, rb, rd;\n\tmov.b64 ra, {%2,%3};\n\tmov.b64 rb, {%4,%5};\n\tmul.rn.f32x2 rd, ra, rb;\n\tmov.b64 {%0,%1}, rd;}"
+        : "=f"(d.x), "=f"(d.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
+    return d;
+}
+__device__ __forceinline__ float2 ntc_add2(float2 a, float2 b) {
+    float2 d;
+    asm("{.reg .b64 ra, rb, rd;\n\tmov.b64 ra, {%2,%3};\n\tmov.b64 rb, {%4,%5};\n\tadd.rn.f32x2 rd, ra, rb;\n\tmov.b64 {%0,%1}, rd;}"
+        : "=f"(d.x), "=f"(d.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
+    return d;
+}
+// tanh of a pair given C * x: h = 1 - 2 / (exp2(C x) + 1); also dn = h^2 - 1 = -(1 - h^2)
+__device__ __forceinline__ void ntc_tanh2(float2 cx, float2& h, float2& dn) {
+    float2 t, rr;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(t.x) : "f"(cx.x));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(t.y) : "f"(cx.y));
+    t = ntc_add2(t, make_float2(1.0f, 1.0f));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rr.x) : "f"(t.x));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rr.y) : "f"(t.y));
+    h = ntc_fma2(rr, make_float2(-2.0f, -2.0f), make_float2(1.0f, 1.0f));
+    dn = ntc_fma2(h, h, make_float2(-1.0f, -1.0f));
+}
+// a pair -> packed IEEE-half hi and lo words
+__device__ __forceinline__ void ntc_split2(float2 x, uint32_t& hi, uint32_t& lo) {
+    const __half2 h = __floats2half2_rn(x.x, x.y);
+    const float2 l = ntc_fma2(__half22float2(h), make_float2(-1.0f, -1.0f), x);
+    const __half2 l2 = __floats2half2_rn(l.x, l.y);
+    hi = *reinterpret_cast<const uint32_t*>(&h);
+    lo = *reinterpret_cast<const uint32_t*>(&l2);
+}
 // tanh of x given cx = C * x
 __device__ __forceinline__ float ntc_tanh_scaled(float cx) {
     float t, r;
@@ -223,29 +274,29 @@ k_stage_narrow_tc(const NtcW* __restrict__ wsmall, const __half* __restrict__ w2
                 if (rr < D) z[rr < D ? rr : 0] = v;
             }
         }
-        // ---- layer 1 and the D one-hot tangents (scaled by C) of this thread's 32 hidden units -> hi/lo
-        // operand planes in shared memory
+        // ---- layer 1 and the D one-hot tangents (scaled by -C: dn = h^2 - 1) of this thread's 32 hidden units,
+        // two units per instruction -> hi/lo operand planes in shared memory
+        const float2 z0 = make_float2(z[0], z[0]), z1 = make_float2(z[D > 1 ? 1 : 0], z[D > 1 ? 1 : 0]);
 #pragma unroll
         for (int cq = 0; cq < 4; ++cq) {
             const int cb = hw * 4 + cq;
-            float x[NV][8];
+            float2 x[NV][4];
 #pragma unroll
-            for (int q = 0; q < 8; ++q) {
-                const float4 w = sw->l1[cb * 8 + q];
-                float a = fmaf(w.x, z[0], w.z);
-                if (D > 1) a = fmaf(w.y, z[D > 1 ? 1 : 0], a);
-                const float h = ntc_tanh_scaled(a);
-                const float d = fmaf(-h, h, 1.0f);
-                x[0][q] = h;
-                x[1][q] = w.x * d;
-                if (D > 1) x[D > 1 ? 2 : 1][q] = w.y * d;
+            for (int q = 0; q < 4; ++q) {
+                const float4 w = sw->l1w[cb * 4 + q];
+                float2 a = ntc_fma2(make_float2(w.x, w.y), z0, sw->l1b[cb * 4 + q]);
+                if (D > 1) a = ntc_fma2(make_float2(w.z, w.w), z1, a);
+                float2 dn;
+                ntc_tanh2(a, x[0][q], dn);
+                x[1][q] = ntc_mul2(make_float2(w.x, w.y), dn);
+                if (D > 1) x[D > 1 ? 2 : 1][q] = ntc_mul2(make_float2(w.z, w.w), dn);
             }
             const uint32_t off = ntc_swz(r, cb);
 #pragma unroll
             for (int v = 0; v < NV; ++v) {
                 uint32_t hi[4], lo[4];
 #pragma unroll
-                for (int q = 0; q < 4; ++q) tc_split2<0>(x[v][2 * q], x[v][2 * q + 1], hi[q], lo[q]);
+                for (int q = 0; q < 4; ++q) ntc_split2(x[v][q], hi[q], lo[q]);
                 ntc_sts128(myA + (uint32_t)(v * 2) * NTC_PLANE_A + off, hi);
                 ntc_sts128(myA + (uint32_t)(v * 2 + 1) * NTC_PLANE_A + off, lo);
             }
@@ -257,10 +308,9 @@ k_stage_narrow_tc(const NtcW* __restrict__ wsmall, const __half* __restrict__ w2
         if (tile + tstride < ntiles) load_raw(tile + tstride);
         // ---- epilogue on this thread's 32 columns: tanh, tangent scaling, layer 3 (diagonal of the
         // Jacobian product only; the tangents carry the factor C until the end)
-        float p3[D], r3[D];
-#pragma unroll
-        for (int j = 0; j < D; ++j) { p3[j] = 0.0f; r3[j] = 0.0f; }
-        tc::mbar_wait(&bars[g], it & 1);
+        // (both the tangents and dn carry a minus sign: their product does not)
+        float2 p3a = make_float2(0.0f, 0.0f), p3b = p3a, r3a = p3a, r3b = p3a;   // even / odd hidden units
+        ntc_wait_sleep(&bars[g], it & 1);
         __syncwarp();
         tc::tc_fence_after();
 #pragma unroll
@@ -270,18 +320,25 @@ k_stage_narrow_tc(const NtcW* __restrict__ wsmall, const __half* __restrict__ w2
             for (int v = 0; v < NV; ++v) tc::tmem_ld_32x8(tlane + v * NTC_H + ch * 8, va[v]);
             tc::tmem_ld_wait();
 #pragma unroll
-            for (int q = 0; q < 8; ++q) {
-                const float4 w = sw->l3[hw * 32 + ch * 8 + q];
-                const float h = ntc_tanh_scaled(fmaf(__uint_as_float(va[0][q]), NTC_C, w.x));
-                const float d = fmaf(-h, h, 1.0f);
-                p3[0] = fmaf(w.y, h, p3[0]);
-                r3[0] = fmaf(w.y, __uint_as_float(va[1][q]) * d, r3[0]);
+            for (int q = 0; q < 4; ++q) {
+                const float4 w = sw->l3w[hw * 16 + ch * 4 + q];
+                float2 h, dn;
+                ntc_tanh2(ntc_fma2(make_float2(__uint_as_float(va[0][2 * q]), __uint_as_float(va[0][2 * q + 1])),
+                                   make_float2(NTC_C, NTC_C), make_float2(w.x, w.y)), h, dn);
+                p3a = ntc_fma2(make_float2(w.z, w.w), h, p3a);
+                r3a = ntc_fma2(make_float2(w.z, w.w),
+                               ntc_mul2(make_float2(__uint_as_float(va[1][2 * q]), __uint_as_float(va[1][2 * q + 1])), dn), r3a);
                 if (D > 1) {
-                    p3[D > 1 ? 1 : 0] = fmaf(w.z, h, p3[D > 1 ? 1 : 0]);
-                    r3[D > 1 ? 1 : 0] = fmaf(w.z, __uint_as_float(va[D > 1 ? 2 : 1][q]) * d, r3[D > 1 ? 1 : 0]);
+                    const float2 w1 = sw->l3v[hw * 16 + ch * 4 + q];
+                    p3b = ntc_fma2(w1, h, p3b);
+                    r3b = ntc_fma2(w1, ntc_mul2(make_float2(__uint_as_float(va[D > 1 ? 2 : 1][2 * q]),
+                                                            __uint_as_float(va[D > 1 ? 2 : 1][2 * q + 1])), dn), r3b);
                 }
             }
         }
+        float p3[D], r3[D];
+        p3[0] = p3a.x + p3a.y; r3[0] = r3a.x + r3a.y;
+        if (D > 1) { p3[D > 1 ? 1 : 0] = p3b.x + p3b.y; r3[D > 1 ? 1 : 0] = r3b.x + r3b.y; }
         if (hw == 1) {
             xch[g * 128 + r] = make_float4(p3[0], r3[0], D > 1 ? p3[D > 1 ? 1 : 0] : 0.0f, D > 1 ? r3[D > 1 ? 1 : 0] : 0.0f);
             ntc_bar_arrive(barB);
@@ -332,9 +389,15 @@ static void ntc_pack(const cnf_handle* h, const float* theta, NtcW* out, __half*
     const float* W1 = theta + h->w_off[0];   // col-major H x D
     const float* W2 = theta + h->w_off[1];   // col-major H x H: W2[i * H + o]
     const float* W3 = theta + h->w_off[2];   // col-major D x H
-    for (int o = 0; o < NTC_H; ++o) {
-        out->l1[o] = make_float4(NTC_C * W1[o], D > 1 ? NTC_C * W1[NTC_H + o] : 0.0f, NTC_C * theta[h->b_off[0] + o], 0.0f);
-        out->l3[o] = make_float4(NTC_C * theta[h->b_off[1] + o], W3[o * D], D > 1 ? W3[o * D + 1] : 0.0f, 0.0f);
+    for (int p = 0; p < NTC_H / 2; ++p) {
+        const int o = 2 * p;
+        const float* b1 = theta + h->b_off[0];
+        const float* b2 = theta + h->b_off[1];
+        out->l1w[p] = make_float4(NTC_C * W1[o], NTC_C * W1[o + 1], D > 1 ? NTC_C * W1[NTC_H + o] : 0.0f,
+                                  D > 1 ? NTC_C * W1[NTC_H + o + 1] : 0.0f);
+        out->l1b[p] = make_float2(NTC_C * b1[o], NTC_C * b1[o + 1]);
+        out->l3w[p] = make_float4(NTC_C * b2[o], NTC_C * b2[o + 1], W3[o * D], W3[(o + 1) * D]);
+        out->l3v[p] = D > 1 ? make_float2(W3[o * D + 1], W3[(o + 1) * D + 1]) : make_float2(0.0f, 0.0f);
     }
     for (int j = 0; j < D; ++j) out->b3[j] = theta[h->b_off[2] + j];
     // B operand: row n = output unit, K = input unit; K-major SWIZZLE_128B (same layout as ntc_swz)

@@ -42,3 +42,4 @@ for kp in ((0,) if os.environ.get("NTC_BIG_ONLY") else (0, 2)):
         st = cnf.last_stats(icnf)
     print(f"B={Bbig} kernel_path {st['kernel_path']}: ms_solve {st['ms_solve']:.3f} stage ms {st['ms_stage'] / max(st['n_stage'], 1):.4f} "
           f"x{st['n_stage']} naccept {st['naccept']} nreject {st['nreject']}", flush=True)
+
