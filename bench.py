@@ -309,7 +309,7 @@ def main():
                     "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback 1.4 PFLOP/s sustained",
                     "note": "achieved = f16 MMA flops executed (3 per algorithmic flop of layer 2: hi*hi + lo*hi + hi*lo); "
                             "the kernel is bound by the SIMT prologue/epilogue (tanh, hi/lo split, layers 1 and 3: "
-                            "~2.9 k instructions per sample, issue slots 56-65 % busy in ncu), not by the tensor pipe; "
+                            "~2.2 k instructions per sample, issue slots 46 % and the MUFU pipe 43 % busy in ncu), not by the tensor pipe; "
                             "algorithmic_tflops / fp32_fma_peak shows how far it is above the FP32-FMA roofline that "
                             "bounded the register-resident kernel (kernel_path 2)",
                     "algorithmic_tflops": achieved, "fp32_fma_peak": pk.value,

@@ -417,7 +417,7 @@ static bool ntc_shape(const cnf_config& c) {
            c.dims[1] == NTC_H && c.dims[2] == NTC_H;
 }
 bool ntc_supported(const cnf_handle* h, int mode) {
-    return mode == CNF_MODE_TEST && h->cfg.trace_mode == CNF_TRACE_JVP && ntc_shape(h->cfg) && h->ntc_state != nullptr;
+    return mode == CNF_MODE_TEST && ntc_shape(h->cfg) && h->ntc_state != nullptr;   // both trace modes: see narrow_supported
 }
 
 // called from set_params with a host copy of theta

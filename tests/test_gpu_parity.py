@@ -173,6 +173,14 @@ def test_tensor_path_is_selected_for_wide_train_and_narrow_for_c2():
     icnf = make_icnf("C2", kernel_path=2)
     cnf.inference(icnf, cnf.TestMode(), inp["xs"].T, inp["theta"], {})
     assert cnf.last_stats(icnf)["kernel_path"] == 2     # register-resident SIMT kernel stays reachable
+    # the reference's default compute mode (VecJac) builds the same Jacobian row by row: same fast path
+    icnf = make_icnf("C2", trace_mode=0)
+    lp0, _ = cnf.inference(icnf, cnf.TestMode(), inp["xs"].T, inp["theta"], {})
+    assert cnf.last_stats(icnf)["kernel_path"] == 6
+    rlp, _, _, rst = O.logdensity(oracle_cfg("C2", trace_mode=0), inp["theta"], 0, inp["xs"], None, None, 0.0, 1.0)
+    assert abs(cnf.last_stats(icnf)["naccept"] - rst["naccept"]) <= 1
+    if cnf.last_stats(icnf)["naccept"] == rst["naccept"]:
+        assert relerr(lp0, rlp) < 1e-4
 
 
 def _narrow_model(nvars, kernel_path, tspan=(0.0, 1.0)):
