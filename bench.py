@@ -43,6 +43,9 @@ def parse():
     p.add_argument("--kernel-path", type=int, default=0)
     p.add_argument("--compute-mode", default="matrix", choices=["matrix", "vector"],
                    help="vector = per-sample step control (row N4; TestMode configs on narrow shapes)")
+    p.add_argument("--mode", default="", choices=["", "test", "hutchinson"],
+                   help="override the config's headline mode: log-density inference in TestMode (exact trace) "
+                        "or in TrainMode (Hutchinson estimate)")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--cpu-sample", type=int, default=0)
     return p.parse_args()
@@ -185,6 +188,8 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     cid = args.config
     c = wl.CONFIGS[cid]
+    if args.mode:   # inference on a training config (e.g. C4: "Test (inference) and Train")
+        c = dict(c, mode="test")
     train = c["mode"] == "train"
     B = args.batch or c["B"]
     D = c["nvars"] + c["naug"]
@@ -193,7 +198,7 @@ def main():
     if world > 1:
         cnf.parallel.init_comm(icnf, rank, world)
     cnf.set_option(icnf, "time_stages", 1)
-    mode = cnf.TrainMode() if train else cnf.TestMode()
+    mode = cnf.TrainMode() if (train or args.mode == "hutchinson") else cnf.TestMode()
     dev = torch.device("cuda", local)
     # device-resident inputs (value) and pinned host inputs (e2e); `rows x B` views, Julia-style
     xs_d = torch.from_numpy(inp["xs"]).to(dev).t()
@@ -211,7 +216,7 @@ def main():
         if train:
             out = cnf.loss_and_grad(icnf, mode, xs, *tail, eps=eps)
         else:
-            out = cnf.inference(icnf, mode, xs, *tail)
+            out = cnf.inference(icnf, mode, xs, *tail, **({"eps": eps} if args.mode == "hutchinson" else {}))
         return out, cnf.last_stats(icnf)
 
     def barrier():
@@ -264,7 +269,7 @@ def main():
         (inp["eps"].nbytes if train else 0) + theta.nbytes
     d2h = (theta.nbytes + 4) if train else (B * 4 + B * 4)
     # roofline of the dominant kernel: one RK stage kernel = one augmented_f evaluation of B samples
-    flops_eval = wl.flops_per_eval(cid) * B
+    flops_eval = wl.flops_per_eval(cid, "train" if args.mode == "hutchinson" else c["mode"]) * B
     lib = cnf._cabi.load()
     import ctypes
     pk = ctypes.c_double(0.0)

@@ -434,6 +434,7 @@ static int solve_device(cnf_handle* h, const CnfBufs& bf, int mode, int R, long 
     int rc;
     const bool nar = use_narrow(h, mode);
     const bool tcp = !nar && use_tc(h, mode);
+    h->tc_mode = mode;
     h->path_used = nar ? (use_ntc(h, mode) ? 6 : 2) : (tcp ? 3 : 1);
     if (nar) rc = narrow_stage(h, bf, 0, 0);
     else if (tcp) rc = tc_stage(h, bf, h->slots[0], 0, nullptr, 0);
@@ -597,6 +598,7 @@ extern "C" int32_t cnfb200_augmented_f(cnf_handle* h, int32_t mode, const float*
     h->path_used = 1;
     if (use_tc(h, mode)) {
         h->path_used = 3;
+        h->tc_mode = mode;
         if ((rc = tc_eval(h, bf, h->slots[0], -1, h->d_K[0], 0))) return rc;
     } else if ((rc = launch_eval_generic(h, bf, mode, h->slots[0], h->d_K[0]))) return rc;
     float* dout = is_device_ptr(du) ? du : h->d_io + io.total;

@@ -319,7 +319,7 @@ static int launch_vjp_generic_stage(cnf_handle* h, const CnfBufs& bf, const floa
 static int bw_eval(cnf_handle* h, const CnfBufs& bf, int mode, const float* src, float* kout) {
     if (mode == CNF_MODE_TEST) return launch_eval_generic(h, bf, CNF_MODE_TEST, src, kout);
     if (tc_bw_supported(h)) return tc_eval_z(h, bf, src, kout);   // only the zdot rows feed the stage inputs
-    if (tc_supported(h->cfg, CNF_MODE_TRAIN) && h->tc_state) return tc_eval(h, bf, src, -1, kout, 0);
+    if (tc_supported(h->cfg, CNF_MODE_TRAIN) && h->tc_state) { h->tc_mode = CNF_MODE_TRAIN; return tc_eval(h, bf, src, -1, kout, 0); }
     return launch_eval_generic(h, bf, CNF_MODE_TRAIN, src, kout);
 }
 

@@ -63,6 +63,7 @@ struct cnf_handle {
     int path_used = 0;
     void* tc_state = nullptr;   // tensor-core path state (cnf_stage_tc.cu)
     int tc_dbg = 0;
+    int tc_mode = CNF_MODE_TRAIN;   // mode of the solve tc_eval serves: TrainMode Hutchinson rows, or TestMode exact trace
     bool tc_noring = false;     // option "tc_ring" = 0: epilogue operands through registers instead of the shared-memory ring
     bool tc_bw_off = false;     // option "tc_backward" = 0: reverse sweep on the generic SIMT kernels
     long long wg_lbo = 0, wg_sbo = 0;   // debug override of the MN-major descriptor strides (0 = default)

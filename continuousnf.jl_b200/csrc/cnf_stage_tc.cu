@@ -58,6 +58,8 @@ struct TcEpi {
     int D;
     unsigned flags;
     int vjp;                       // FWD_LAST: also emit g_L = eps .* (1-y^2) planes; 2: z rows only
+    int test;                      // TestMode (exact trace): R = D + 1 rows, no regulariser rows; JVP_LAST adds pass i's -(J e_i)_i
+    int pass;                      // index i of the one-hot tangent
     // ---- reverse sweep
     float* f32a;                   // fp32 side array [rows x ld_f] (q_{l+1} / dbar_l ; y)
     float* f32b;                   // second fp32 side array (ybar)
@@ -358,7 +360,11 @@ __device__ __forceinline__ void tc_epilogue_fwd(const TcEpi& ep, TcSmemCtl* ctl,
     const float2 r = tc_quad_reduce(ctl, quad, sub, lane, par, s0, s1);
     if (sub != 0) return;
     if (KIND == TC_FWD_LAST) {
-        ep.kout[(long long)(ep.D + 1) * ep.Bs + grow] = (ep.flags & CNF_FLAG_NORM_Z) ? sqrtf(r.x) : 0.0f;
+        if (!ep.test) ep.kout[(long long)(ep.D + 1) * ep.Bs + grow] = (ep.flags & CNF_FLAG_NORM_Z) ? sqrtf(r.x) : 0.0f;
+    } else if (ep.test) {
+        // exact trace: with eps = e_i, -eps . (J eps) = -(J e_i)_i; the passes i = 0..D-1 add up to -tr J
+        float* tr = ep.kout + (long long)ep.D * ep.Bs + grow;
+        *tr = ep.pass ? *tr + r.x : r.x;
     } else {
         ep.kout[(long long)ep.D * ep.Bs + grow] = r.x;
         ep.kout[(long long)(ep.D + 2) * ep.Bs + grow] = (ep.flags & CNF_FLAG_NORM_J) ? sqrtf(r.y) : 0.0f;
@@ -807,8 +813,11 @@ static int tc_alloc_f32(cnf_handle* h, TcF32& f, int rows, int ld) {
 
 // the tensor path covers TrainMode (Hutchinson) on chains of >= 2 layers whose hidden widths are
 // multiples of 32 and >= 128 (auto) — or any multiple of 32 when forced with kernel_path = 3
+// TrainMode (Hutchinson rows, both trace modes) and TestMode (exact trace = D one-hot tangent chains on the
+// same layer-GEMM kernels; D passes, so only for moderate D)
 bool tc_supported(const cnf_config& c, int mode) {
-    if (mode != CNF_MODE_TRAIN || c.n_layers < 2 || c.D > 256) return false;
+    if ((mode != CNF_MODE_TRAIN && mode != CNF_MODE_TEST) || c.n_layers < 2 || c.D > 256) return false;
+    if (mode == CNF_MODE_TEST && c.D > 64) return false;
     if (c.flags & CNF_FLAG_LAST_LINEAR) return false;   // generic kernels only
     bool wide = true;
     for (int l = 1; l < c.n_layers; ++l) {
@@ -1015,7 +1024,15 @@ static void tc_forward_hidden(cnf_handle* h, TcState* s, const TcEpi& base, int 
     }
 }
 
-// du = augmented_f(src) in TrainMode on the tensor path.  src: D x Bs z rows (host-known pointer);
+// eps rows = e_i for every sample (seed of the i-th tangent chain of the exact trace)
+__global__ void k_tc_onehot(float* __restrict__ eps, long long Bs, int D, int i) {
+    const long long n = (long long)D * Bs;
+    for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += (long long)gridDim.x * blockDim.x)
+        eps[p] = (p / Bs == i) ? 1.0f : 0.0f;
+}
+
+// du = augmented_f(src) on the tensor path: TrainMode (Hutchinson rows) or, with h->tc_mode = TestMode, the
+// exact trace (reference src/icnf.jl:148-164: zdot rows and -tr J, J from jacobian_batched src/utils.jl:1-36).  src: D x Bs z rows (host-known pointer);
 // output buffer either fixed (kout_fixed) or resolved on the device from kidx (FSAL index).
 int tc_eval(cnf_handle* h, const CnfBufs& bf, const float* src, int kidx, float* kout_fixed, int check_done) {
     TcState* s = (TcState*)h->tc_state;
@@ -1024,10 +1041,13 @@ int tc_eval(cnf_handle* h, const CnfBufs& bf, const float* src, int kidx, float*
     int rc;
     if ((rc = tc_ensure_acts(h, s, bf.Bs))) return rc;
     const int L = c.n_layers;
-    const bool jvp = c.trace_mode == CNF_TRACE_JVP;
+    const bool test = h->tc_mode == CNF_MODE_TEST;
+    const bool jvp = c.trace_mode == CNF_TRACE_JVP || test;   // the exact trace pushes one-hot tangents forward
+    const int npass = test ? c.D : 1;
     for (long long row0 = 0; row0 < bf.Bs; row0 += s->Mc) {
         const int mc = (int)((bf.Bs - row0) < s->Mc ? (bf.Bs - row0) : s->Mc);
         TcEpi base = tc_base_epi(h, s, bf, row0, check_done);
+        base.test = test ? 1 : 0;
         // h_0 = [z; ys] planes (+ resolve the output buffer)
         k_tc_prep<0><<<(mc + 255) / 256, 256, 0, h->stream>>>(h->d_ctrl, bf, src, c.D, bf.ys, c.C, row0, mc, s->H[0].p[0],
                                                           s->H[0].p[1], s->H[0].ld, kidx, kout_fixed, s->dyn, check_done);
@@ -1059,8 +1079,14 @@ int tc_eval(cnf_handle* h, const CnfBufs& bf, const float* src, int kidx, float*
                 }
                 tc_launch_gemm<0, false>(h, s, s->G[l + 1], s->wb[l], mc, ep);
             }
-        } else {
+        } else for (int pass = 0; pass < npass; ++pass) {
             // tangent chain: tau_0 = eps, tau_l = (tau_{l-1} W_l^T) .* (1 - h_l^2), J eps = tau_L
+            // (TestMode: eps = e_pass, D passes over the same forward activations)
+            if (test) {
+                k_tc_onehot<<<592, 256, 0, h->stream>>>(h->d_eps, bf.Bs, c.D, pass);
+                h->launches++;
+                base.pass = pass;
+            }
             k_tc_prep<0><<<(mc + 255) / 256, 256, 0, h->stream>>>(h->d_ctrl, bf, bf.eps, c.D, nullptr, 0, row0, mc,
                                                               s->G[0].p[0], s->G[0].p[1], s->G[0].ld, 0,
                                                               nullptr, nullptr,

@@ -524,3 +524,31 @@ def test_small_batches_run_in_whole_solve_kernels_with_identical_results(cid, B)
     assert a[8]["kernel_path"] == 5 and b[8]["kernel_path"] == 1
     assert a[8]["naccept"] == b[8]["naccept"] and a[9]["naccept"] == b[9]["naccept"]
     assert a[9]["gpu_launches"] < 30 < b[9]["gpu_launches"]
+
+
+@pytest.mark.parametrize("cid,B", [("C4", 700), ("C3", 300)])
+@pytest.mark.parametrize("trace_mode", [0, 1])
+def test_tensor_path_exact_trace_testmode(cid, B, trace_mode):
+    """TestMode (exact trace) on wide nets runs on the tensor path as D one-hot tangent chains over the same
+    layer GEMMs: one evaluation against the oracle, and a whole solve against the oracle and the generic path"""
+    inp = wl.make_inputs(cid, B=B)
+    c = wl.CONFIGS[cid]
+    D = c["nvars"] + c["naug"]
+    u = np.random.default_rng(9).normal(0, 1, (B, D + 1)).astype(np.float32)
+    icnf = make_icnf(cid, trace_mode=trace_mode)
+    du = np.asarray(cnf.augmented_f(icnf, cnf.TestMode(), u.T, *args_of(inp))).T
+    ref = O.augmented_f(oracle_cfg(cid, trace_mode=trace_mode), inp["theta"], 0, u, inp["ys"], inp["eps"])
+    scale = np.maximum(np.abs(ref).max(axis=0, keepdims=True), 1e-6)
+    assert np.max(np.abs(du - ref) / scale) < 1e-4
+    out = {}
+    for kp in (0, 1):
+        m = make_icnf(cid, kernel_path=kp, trace_mode=trace_mode)
+        lp, _ = cnf.inference(m, cnf.TestMode(), inp["xs"].T, *args_of(inp))
+        st = cnf.last_stats(m)
+        assert st["kernel_path"] == (3 if kp == 0 else 1) and st["retcode"] == 0
+        out[kp] = (np.asarray(lp), st["naccept"])
+    rlp, _, _, rst = O.logdensity(oracle_cfg(cid, trace_mode=trace_mode), inp["theta"], 0, inp["xs"], inp["ys"], None,
+                                  *c["tspan"])
+    assert abs(out[0][1] - rst["naccept"]) <= 1 and abs(out[0][1] - out[1][1]) <= 1
+    if out[0][1] == rst["naccept"]:
+        assert relerr(out[0][0], rlp) < 1e-4
