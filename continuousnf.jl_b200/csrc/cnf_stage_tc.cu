@@ -213,7 +213,7 @@ __device__ __forceinline__ void tc_aux_load(const TcEpi& ep, long long rloc, lon
         } else if (k == TC_BWD_HIDDEN) {
             tc_ld256_nc(ep.hp[0] + rloc * ep.ld_h + ng, a.p[0]);
             tc_ld256_nc(ep.hp[1] + rloc * ep.ld_h + ng, a.p[1]);
-        } else if (k != TC_FWD_LAST || ep.vjp == 1) {
+        } else if ((k != TC_FWD_LAST || ep.vjp == 1) && !ep.test) {
             tc_load_soa16(ep.eps, ep.Bs, grow, ng, ep.D, a.f);
         }
     } else {
@@ -348,7 +348,7 @@ __device__ __forceinline__ void tc_epilogue_fwd(const TcEpi& ep, TcSmemCtl* ctl,
                 if (c0 + j < ep.D) {
                     float vv = __uint_as_float(v[j]);
                     if (KIND == TC_JVP_LAST) vv *= fmaf(-y[j], y[j], 1.0f);
-                    s0 = fmaf(-vv, cur.f[j], s0);
+                    s0 = fmaf(-vv, ep.test ? (c0 + j == ep.pass ? 1.0f : 0.0f) : cur.f[j], s0);
                     s1 = fmaf(vv, vv, s1);
                 }
             }
@@ -1024,11 +1024,27 @@ static void tc_forward_hidden(cnf_handle* h, TcState* s, const TcEpi& base, int 
     }
 }
 
-// eps rows = e_i for every sample (seed of the i-th tangent chain of the exact trace)
-__global__ void k_tc_onehot(float* __restrict__ eps, long long Bs, int D, int i) {
-    const long long n = (long long)D * Bs;
-    for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += (long long)gridDim.x * blockDim.x)
-        eps[p] = (p / Bs == i) ? 1.0f : 0.0f;
+// first layer of the i-th one-hot tangent chain of the exact trace: tau_1 = (e_i W_1^T) .* (1 - h_1^2) =
+// W_1[:, i] .* (1 - h_1^2) — no GEMM and no seed planes; one thread = 16 columns of one sample row
+template <int PREC>
+__global__ void k_tc_onehot_l1(const CnfCtrl* __restrict__ ctrl, const float* __restrict__ wcol, int N,
+                               const __nv_bfloat16* __restrict__ h0, const __nv_bfloat16* __restrict__ h1, int ld_h,
+                               __nv_bfloat16* o0, __nv_bfloat16* o1, int ld_o, int mc) {
+    if (ctrl && ctrl->done) return;
+    const int nch = N / TC_CW;
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long row = idx / nch;
+    const int c0 = (int)(idx % nch) * TC_CW;
+    if (row >= mc) return;
+    uint32_t p[2][8];
+    tc_ld256_nc(h0 + row * ld_h + c0, p[0]);
+    tc_ld256_nc(h1 + row * ld_h + c0, p[1]);
+    float h[TC_CW], x[TC_CW];
+    tc_unpack_planes16<PREC>(p, h);
+#pragma unroll
+    for (int j = 0; j < TC_CW; ++j) x[j] = __ldg(wcol + c0 + j) * fmaf(-h[j], h[j], 1.0f);
+    __nv_bfloat16* const out[2] = {o0, o1};
+    tc_store_planes16<PREC>(x, out, row * ld_o + c0);
 }
 
 // du = augmented_f(src) on the tensor path: TrainMode (Hutchinson rows) or, with h->tc_mode = TestMode, the
@@ -1083,16 +1099,21 @@ int tc_eval(cnf_handle* h, const CnfBufs& bf, const float* src, int kidx, float*
             // tangent chain: tau_0 = eps, tau_l = (tau_{l-1} W_l^T) .* (1 - h_l^2), J eps = tau_L
             // (TestMode: eps = e_pass, D passes over the same forward activations)
             if (test) {
-                k_tc_onehot<<<592, 256, 0, h->stream>>>(h->d_eps, bf.Bs, c.D, pass);
-                h->launches++;
                 base.pass = pass;
-            }
+                const int N1 = c.dims[1];
+                const long long nthr = (long long)mc * (N1 / TC_CW);
+                k_tc_onehot_l1<0><<<(unsigned)((nthr + 255) / 256), 256, 0, h->stream>>>(
+                    check_done ? h->d_ctrl : nullptr, h->d_theta + h->w_off[0] + (long long)pass * N1, N1, s->H[1].p[0],
+                    s->H[1].p[1], s->H[1].ld, s->G[1].p[0], s->G[1].p[1], s->G[1].ld, mc);
+                h->launches++;
+            } else {
             k_tc_prep<0><<<(mc + 255) / 256, 256, 0, h->stream>>>(h->d_ctrl, bf, bf.eps, c.D, nullptr, 0, row0, mc,
                                                               s->G[0].p[0], s->G[0].p[1], s->G[0].ld, 0,
                                                               nullptr, nullptr,
                                                               check_done);
             h->launches++;
-            for (int l = 0; l < L; ++l) {
+            }
+            for (int l = test ? 1 : 0; l < L; ++l) {   // (TestMode: layer 1 of the chain was the elementwise kernel)
                 TcEpi ep = base;
                 ep.N = c.dims[l + 1];
                 if (l < L - 1) {
