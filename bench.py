@@ -330,7 +330,7 @@ def main():
             pass
         peak = float(peaks.get("bf16_tflops_sustained", 1400.0))
         hbm_peak = float(peaks.get("hbm_gbs", 6400.0))
-        bytes_eval = wl.tc_bytes_per_eval(cid) * B
+        bytes_eval = (wl.tc_bytes_per_eval_exact(cid) if (c["mode"] == "test" and args.mode != "hutchinson") else wl.tc_bytes_per_eval(cid)) * B
         t_hbm = bytes_eval / (hbm_peak * 1e9)
         t_tensor = 3 * flops_eval / (peak * 1e12)
         if t_hbm > t_tensor:

@@ -112,6 +112,25 @@ def tc_bytes_per_eval(cid):
     return 4 * e
 
 
+def tc_bytes_per_eval_exact(cid):
+    """same for one TestMode (exact trace) evaluation on the tensor path: the forward chain, then D one-hot
+    tangent chains (first layer elementwise from the h_1 planes, then one GEMM per layer)."""
+    c = CONFIGS[cid]
+    dims = c["dims"]
+    L = len(dims) - 1
+    D = c["nvars"] + c["naug"]
+    pad = lambda n: (n + 63) // 64 * 64
+    e = D + pad(dims[0])                                              # prep
+    for l in range(1, L):
+        e += pad(dims[l - 1]) + pad(dims[l])                          # forward hidden layers
+    e += pad(dims[L - 1]) + D                                         # last layer: zdot rows
+    chain = 2 * pad(dims[1])                                          # tau_1 = W_1[:, i] .* (1 - h_1^2)
+    for l in range(2, L):
+        chain += pad(dims[l - 1]) + 2 * pad(dims[l])                  # tau_l: read tau_{l-1}, h_l; write tau_l
+    chain += pad(dims[L - 1]) + D + 2                                 # last layer: read tau_{L-1}, y rows; trace row r/w
+    return 4 * (e + D * chain)
+
+
 def flops_backward_per_eval(cid):
     dims = CONFIGS[cid]["dims"]
     return 8 * sum(dims[l] * dims[l + 1] for l in range(len(dims) - 1))
