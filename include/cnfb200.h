@@ -76,13 +76,13 @@ typedef struct cnf_config {
     int64_t maxiters;         /* 0 => 1e5 */
     float dt0, dtmax, dtmin;  /* 0 => solver default */
     int32_t device;           /* CUDA device ordinal of this process */
-    int32_t kernel_path;      /* 0 auto; 1 force generic SIMT; 2 force register-resident narrow; 3 force tcgen05 */
+    int32_t kernel_path;      /* 0 auto; 1 force generic SIMT; 2 force register-resident narrow (instead of 6); 3 force tcgen05 layer GEMMs */
 } cnf_config;
 
 typedef struct cnf_stats {
     int64_t naccept, nreject, nf; /* nf = augmented_f evaluations */
     int32_t retcode;
-    int32_t kernel_path;          /* path actually used (1,2,3) */
+    int32_t kernel_path;          /* path actually used: 1 generic SIMT, 2 register-resident narrow, 3 tcgen05 layer GEMMs, 4 VectorMode, 5 whole-solve single-launch kernels, 6 narrow nets with layer 2 on tcgen05 */
     float t_final, dt_last;
     double ms_total;              /* device time of the whole call (CUDA events) */
     double ms_solve;              /* device time of the RK loop only */
