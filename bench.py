@@ -371,7 +371,7 @@ def main():
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{cid}: {c['tag']} dims={c['dims']} B={B}/GPU mode={c['mode']} "
                                f"trace={'JVP' if c['trace_mode'] else 'VJP'} tspan={c['tspan']}",
-                   "global_batch": B * world, "parallelism": f"dp{world} (columns sharded)",
+                   "global_batch": B * world, "parallelism": f"dp{world} (columns sharded)" + (f", error-norm exchange: {cnf.parallel.errnorm_exchange(icnf)}" if world > 1 else ""),
                    "l2": "256 MB flush between timed steps", "naccept": st["naccept"],
                    "nreject": st["nreject"], "nf": st["nf"], "timing": "sum of per-call CUDA-event "
                    "times on the library stream, max over ranks", "wall_ms_per_step_incl_flush":

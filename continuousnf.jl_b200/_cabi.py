@@ -15,7 +15,7 @@ RETCODES = {0: "Success", 1: "MaxIters", 2: "DtLessThanMin", 3: "Unstable"}
 
 EXPORTS = [
     "cnfb200_version", "cnfb200_create", "cnfb200_destroy", "cnfb200_set_option", "cnfb200_last_error",
-    "cnfb200_set_params", "cnfb200_comm_unique_id", "cnfb200_comm_init", "cnfb200_augmented_f",
+    "cnfb200_set_params", "cnfb200_comm_unique_id", "cnfb200_comm_init", "cnfb200_comm_p2p", "cnfb200_augmented_f",
     "cnfb200_logdensity", "cnfb200_loss_grad", "cnfb200_loss_grad_mode", "cnfb200_generate", "cnfb200_measure_fp32_peak",
     "cnfb200_seed_rng", "cnfb200_last_eps", "cnfb200_fit_epochs",
 ]
@@ -72,6 +72,8 @@ def load():
     lib.cnfb200_set_params.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, _I64P, _I64P]
     lib.cnfb200_comm_unique_id.argtypes = [C.c_char_p]
     lib.cnfb200_comm_init.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_char_p]
+    lib.cnfb200_comm_p2p.argtypes = [C.c_void_p]
+    lib.cnfb200_comm_p2p.restype = C.c_int32
     lib.cnfb200_augmented_f.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
                                         C.c_int64, C.c_void_p]
     lib.cnfb200_logdensity.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,

@@ -130,6 +130,7 @@ extern "C" int32_t cnfb200_destroy(cnf_handle* h) {
     free_workspaces(h);
     narrow_free(h);
     ntc_free(h);
+    cnf_p2p_free(h);
     tc_free(h);
     cudaFree(h->d_io);
     cudaFree(h->d_theta); cudaFree(h->d_wt); cudaFree(h->d_grad);
@@ -379,7 +380,7 @@ static int enqueue_attempt(cnf_handle* h, const CnfBufs& bf, int mode) {
     if (use_narrow(h, mode)) {   // fused path: 6 stage launches (the 7th stage carries the error norm)
         for (int i = 1; i <= 6; ++i)
             if ((rc = narrow_stage(h, bf, i, 1))) return rc;
-        if (h->nranks > 1 && (rc = cnf_nccl_allreduce_f64(h, &h->d_ctrl->errsum, 1))) return rc;
+        if (h->nranks > 1 && !h->p2p_ok && (rc = cnf_nccl_allreduce_f64(h, &h->d_ctrl->errsum, 1))) return rc;
         launch_controller(h);
         return CNF_OK;
     }
@@ -391,7 +392,7 @@ static int enqueue_attempt(cnf_handle* h, const CnfBufs& bf, int mode) {
         launch_combine(h, bf, 6, 1);
         if ((rc = tc_stage(h, bf, bf.S, 6, nullptr, 1))) return rc;
         launch_errnorm(h, bf);
-        if (h->nranks > 1 && (rc = cnf_nccl_allreduce_f64(h, &h->d_ctrl->errsum, 1))) return rc;
+        if (h->nranks > 1 && !h->p2p_ok && (rc = cnf_nccl_allreduce_f64(h, &h->d_ctrl->errsum, 1))) return rc;
         launch_controller(h);
         return CNF_OK;
     }
@@ -402,7 +403,7 @@ static int enqueue_attempt(cnf_handle* h, const CnfBufs& bf, int mode) {
     launch_combine(h, bf, 6);
     if ((rc = eval_stage(h, bf, mode, 1 /*SRC_UNEW*/, 6, 1))) return rc;
     launch_errnorm(h, bf);
-    if (h->nranks > 1 && (rc = cnf_nccl_allreduce_f64(h, &h->d_ctrl->errsum, 1))) return rc;
+    if (h->nranks > 1 && !h->p2p_ok && (rc = cnf_nccl_allreduce_f64(h, &h->d_ctrl->errsum, 1))) return rc;
     launch_controller(h);
     return CNF_OK;
 }

@@ -4,6 +4,8 @@
 #include <string>
 #include <vector>
 
+struct CnfXSlot { double v; unsigned long long seq; };   // one mailbox slot of the peer-memory error-norm exchange
+
 struct cnf_handle {
     cnf_config cfg;
     int device = 0;
@@ -53,6 +55,13 @@ struct cnf_handle {
     // communicator (NCCL via dlopen)
     void* nccl_comm = nullptr;
     int nranks = 1, rank = 0;
+    // error-norm exchange over NVLink peer memory (cnf_nccl.cu): every rank owns a mailbox of
+    // [2 parities][nranks] slots that its peers write into; the controller kernel does the exchange itself
+    CnfXSlot* d_xslots = nullptr;
+    CnfXSlot** d_xpeers = nullptr;       // device table: base of rank r's mailbox (peer-mapped)
+    unsigned long long* d_xseq = nullptr;        // exchanges done so far
+    std::vector<void*> xpeer_maps;               // cudaIpcOpenMemHandle mappings to close
+    bool p2p_ok = false;
     long long launches = 0;
     // optional per-stage-kernel timing (cnfb200_set_option "time_stages")
     bool time_stages = false;
@@ -138,5 +147,6 @@ int tc_vjp_stage(cnf_handle* h, const CnfBufs& bf, const float* src, const float
                  const float* dtp, float c_l, float c_E, float c_n, float* ubar, float** kb, float* grad);
 
 // ---- cnf_nccl.cu
+void cnf_p2p_free(cnf_handle* h);
 int cnf_nccl_allreduce_f64(cnf_handle* h, double* dptr, int n);
 int cnf_nccl_allreduce_f32(cnf_handle* h, float* dptr, long long n);

@@ -197,8 +197,56 @@ void launch_tape_stages(cnf_handle* h, const CnfBufs& bf) {
 }
 
 __global__ void k_controller(CnfCtrl* c, float* dts) { d_controller(c, dts); }
+
+// Controller fused with the multi-GPU exchange of the error-norm partial (one warp; lane r talks to rank r):
+// store {partial, sequence number} into the slot [parity][my rank] of every rank's mailbox (peer memory over
+// NVLink), wait until the nranks slots of the own mailbox carry this sequence number, add them in rank order
+// (the same sum, bit for bit, on every rank: the replicated controller needs no broadcast) and run the
+// controller.  Slots alternate by parity: a rank can be at most one exchange ahead of another, because
+// finishing exchange s needs every rank's store of s.  Nothing is exchanged once `done` is set (every rank
+// sets it at the same attempt), so the speculative attempts after the end of a solve stay no-ops.
+__global__ void k_controller_p2p(CnfCtrl* c, float* dts, CnfXSlot* mine, CnfXSlot* const* peers,
+                                 unsigned long long* xseq, int rank, int nranks) {
+    __shared__ double sh_v[32];
+    const int lane = threadIdx.x;
+    if (c->done) {
+        if (lane == 0) c->accepted = 0;
+        return;
+    }
+    const unsigned long long seq = *xseq + 1;
+    const int par = (int)(seq & 1);
+    const double v = c->errsum;
+    __syncwarp();
+    if (lane < nranks) {
+        volatile CnfXSlot* dst = peers[lane] + par * nranks + rank;
+        dst->v = v;
+        __threadfence_system();
+        dst->seq = seq;
+        volatile CnfXSlot* src = mine + par * nranks + lane;
+        unsigned long long t0 = 0, t1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        while (src->seq != seq) {
+            __nanosleep(100);
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+            if (t1 - t0 > 60000000000ull) { asm volatile("trap;"); }   // a peer that never arrives: fail, do not hang
+        }
+        __threadfence_system();
+        sh_v[lane] = src->v;
+    }
+    __syncwarp();
+    if (lane == 0) {
+        double s = 0.0;
+        for (int r = 0; r < nranks; ++r) s += sh_v[r];
+        c->errsum = s;
+        *xseq = seq;
+        d_controller(c, dts);
+    }
+}
 void launch_controller(cnf_handle* h) {
-    k_controller<<<1, 1, 0, h->stream>>>(h->d_ctrl, h->d_dts);
+    if (h->nranks > 1 && h->p2p_ok)
+        k_controller_p2p<<<1, 32, 0, h->stream>>>(h->d_ctrl, h->d_dts, h->d_xslots, h->d_xpeers, h->d_xseq, h->rank, h->nranks);
+    else
+        k_controller<<<1, 1, 0, h->stream>>>(h->d_ctrl, h->d_dts);
     h->launches++;
 }
 

@@ -1,7 +1,7 @@
 """Batch sharding over one-process-per-GPU ranks.  Columns (samples) are split in
 contiguous blocks; theta is replicated.  The only data-path exchange is the scalar error-norm
-allreduce every attempted step (whole-batch RMS norm of the matrix-valued ODE state, reference
-src/base_icnf.jl:280-285) plus the loss/gradient allreduce in training; both happen inside
+exchange every attempted step (whole-batch RMS norm of the matrix-valued ODE state, reference
+src/base_icnf.jl:280-285; inside the controller kernel over NVLink peer memory, NCCL as the fallback) plus the loss/gradient allreduce in training; both happen inside
 libcnfb200 on its NCCL communicator.  torch.distributed is only used to hand the NCCL unique id
 from rank 0 to the other ranks."""
 import ctypes as C
@@ -50,3 +50,9 @@ def init_comm(icnf, rank=None, world=None):
     uid = broadcast_unique_id(make_id, rank)
     h = icnf.handle()
     icnf._check(lib.cnfb200_comm_init(h, world, rank, uid), "cnfb200_comm_init")
+
+
+def errnorm_exchange(icnf):
+    """how the per-attempt error-norm partials travel: 'peer-memory' (inside the controller kernel, P2P stores
+    over NVLink) or 'nccl' (an ncclAllReduce launch per attempt)"""
+    return "peer-memory" if _cabi.load().cnfb200_comm_p2p(icnf.handle()) else "nccl"

@@ -114,6 +114,10 @@ CNF_API int32_t cnfb200_set_params(cnf_handle* h, const float* theta, int64_t n,
  * and cnfb200_loss_grad allreduces loss and gradient.  B_global = sum of local B. */
 CNF_API int32_t cnfb200_comm_unique_id(char id_out[128]);
 CNF_API int32_t cnfb200_comm_init(cnf_handle* h, int32_t nranks, int32_t rank, const char id[128]);
+/* 1 if the per-attempt error-norm exchange runs over NVLink peer memory inside the controller kernel
+ * (mailboxes shared through CUDA IPC at cnfb200_comm_init), 0 if it is an ncclAllReduce launch
+ * (single rank, set-up refused on some rank, or CNFB200_P2P=0 in the environment) */
+CNF_API int32_t cnfb200_comm_p2p(const cnf_handle* h);
 
 /* one evaluation du = augmented_f(u, p, t, icnf, mode, nn, st, eps)
  * (src/icnf.jl:148-164 Test; :318-350 Train/VecJac; :384-420 Train/JacVec).  u, du: R x B. */
