@@ -265,8 +265,9 @@ def main():
     metric, unit = METRIC[c["mode"]]
     total = B * world * args.steps
     value = total / (ms_dev * 1e-3)
+    # (theta is the same host vector in every step: the host mirror uploads it once and skips the copy afterwards)
     h2d = inp["xs"].nbytes + (inp["ys"].nbytes if inp["ys"] is not None else 0) + \
-        (inp["eps"].nbytes if train else 0) + theta.nbytes
+        (inp["eps"].nbytes if train else 0)
     d2h = (theta.nbytes + 4) if train else (B * 4 + B * 4)
     # roofline of the dominant kernel: one RK stage kernel = one augmented_f evaluation of B samples
     flops_eval = wl.flops_per_eval(cid, "train" if args.mode == "hutchinson" else c["mode"]) * B

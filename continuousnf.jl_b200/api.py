@@ -12,6 +12,8 @@ memory (sample-major), which is what Julia would pass.
 import ctypes as C
 import math
 
+import weakref
+
 import numpy as np
 
 from . import _cabi
@@ -314,13 +316,52 @@ class _Mat:
             self.keep, self.ptr, self.device = t, t.ctypes.data, None
 
 
+class _PinnedPool:
+    """page-locked host buffers for output matrices (cnfb200_host_alloc): the device->host copy of a result
+    runs at PCIe rate into them, ~6x faster than into pageable numpy memory.  A buffer goes back to the pool
+    when the array that wraps it is garbage-collected; small outputs stay ordinary numpy arrays."""
+    MIN_BYTES = 1 << 16
+    MAX_KEEP = 8        # free buffers kept per size
+
+    def __init__(self):
+        self.free = {}
+
+    def take(self, nbytes):
+        lst = self.free.get(nbytes)
+        if lst:
+            return lst.pop()
+        p = C.c_void_p()
+        if _cabi.load().cnfb200_host_alloc(nbytes, C.byref(p)) != 0 or not p.value:
+            return None
+        return p.value
+
+    def give(self, nbytes, addr):
+        lst = self.free.setdefault(nbytes, [])
+        if len(lst) < self.MAX_KEEP:
+            lst.append(addr)
+        else:
+            _cabi.load().cnfb200_host_free(addr)
+
+    def empty(self, shape):
+        nbytes = int(np.prod(shape)) * 4
+        addr = self.take(nbytes) if nbytes >= self.MIN_BYTES else None
+        if addr is None:
+            return np.empty(shape, np.float32)
+        buf = (C.c_float * (nbytes // 4)).from_address(addr)
+        weakref.finalize(buf, self.give, nbytes, addr)     # the numpy array keeps `buf` alive through .base
+        return np.frombuffer(buf, dtype=np.float32).reshape(shape)
+
+
+_pinned = _PinnedPool()
+
+
 def _out(rows, B, like):
     """allocate a `rows x B` output in sample-major memory; returns (holder, ptr)"""
     if like is not None and like.torch and like.device.type == "cuda":
         import torch
         t = torch.empty((B, rows), dtype=torch.float32, device=like.device)
         return t, t.data_ptr()
-    t = np.empty((B, rows), np.float32)
+    t = _pinned.empty((B, rows))
     return t, t.ctypes.data
 
 
@@ -340,10 +381,16 @@ def _upload_params(icnf, ps):
     else:
         p = np.ascontiguousarray(ps, dtype=np.float32)
         ptr, cnt = p.ctypes.data, p.size
+        # the same host parameter vector as in the previous call (pdf / logpdf / rand of a fitted model):
+        # every derived form is already on the device, skip the upload and its synchronisations
+        last = getattr(icnf, "_theta_uploaded", None)
+        if last is not None and last[0] == h and last[1].shape == p.reshape(-1).shape and np.array_equal(last[1], p.reshape(-1)):
+            return h
     if cnt != n:
         raise ValueError(f"ps has {cnt} parameters, the network needs {n}")
     icnf._check(lib.cnfb200_set_params(h, ptr, n, w.ctypes.data_as(_cabi._I64P),
                                        b.ctypes.data_as(_cabi._I64P)), "cnfb200_set_params")
+    icnf._theta_uploaded = None if _is_torch(ps) else (h, p.reshape(-1).copy())
     return h
 
 
@@ -416,6 +463,7 @@ def fit_epochs(icnf, X, Y, ps, *, batch_size, n_epochs, perm=None, eta=1e-3, bet
     rc = lib.cnfb200_fit_epochs(h, x.ptr, y.ptr if y else None, x.B, int(batch_size), int(n_epochs),
                                 p.ctypes.data if p is not None else None, t0, t1, float(eta), float(beta[0]),
                                 float(beta[1]), out.ctypes.data, hist.ctypes.data, C.byref(st_))
+    icnf._theta_uploaded = None      # the device copy of theta has been trained: never skip the next upload
     icnf._check(rc, "cnfb200_fit_epochs")
     icnf._last_stats = st_.as_dict()
     return out, hist

@@ -813,6 +813,17 @@ __global__ void k_ffma_peak(float* out, int iters) {
     out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
 }
 
+extern "C" int32_t cnfb200_host_alloc(size_t bytes, void** out) {
+    if (!out || bytes == 0) return CNF_ERR_BADARG;
+    *out = nullptr;
+    if (cudaHostAlloc(out, bytes, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); *out = nullptr; return CNF_ERR_OOM; }
+    return CNF_OK;
+}
+extern "C" int32_t cnfb200_host_free(void* p) {
+    if (p && cudaFreeHost(p) != cudaSuccess) { cudaGetLastError(); return CNF_ERR_CUDA; }
+    return CNF_OK;
+}
+
 extern "C" int32_t cnfb200_measure_fp32_peak(int32_t device, double* tflops_out) {
     if (!tflops_out) return CNF_ERR_BADARG;
     if (cudaSetDevice(device) != cudaSuccess) return CNF_ERR_CUDA;

@@ -188,6 +188,12 @@ CNF_API int32_t cnfb200_fit_epochs(cnf_handle* h, const float* X, const float* Y
  * the roofline denominator MEASURED_PEAKS.json does not provide. */
 CNF_API int32_t cnfb200_measure_fp32_peak(int32_t device, double* tflops_out);
 
+/* page-locked host memory for the caller's input / output matrices: the copies inside the entry points
+ * above run at full PCIe rate from / into such buffers (a pageable destination costs ~1 ms per 8 MB).
+ * The Julia shim wraps them with unsafe_wrap(Array, ...); the library never keeps the pointers. */
+CNF_API int32_t cnfb200_host_alloc(size_t bytes, void** out);
+CNF_API int32_t cnfb200_host_free(void* p);
+
 #ifdef __cplusplus
 }
 #endif
