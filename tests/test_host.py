@@ -96,3 +96,46 @@ def test_workload_flop_model_matches_survey():
     assert wl.flops_per_eval("C4") == 75776
     assert wl.flops_per_eval("C5") == 5242880
     assert wl.flops_backward_per_eval("C3") == 655360
+
+
+def test_pinned_output_pool_recycles_buffers_only_after_every_view_is_gone():
+    """host mirror: results land in page-locked buffers from a pool (cnfb200_host_alloc); a buffer may only be
+    handed out again once the array AND its views (the `rows x B` orientation returned to the caller) are dead"""
+    import gc
+    pool = cnf.api._PinnedPool()
+    backing = [np.zeros(1 << 16, np.float32) for _ in range(2)]   # stand-ins for cudaHostAlloc memory
+    handed = []
+
+    def take(nbytes):
+        free = pool.free.get(nbytes)
+        if free:
+            return free.pop()
+        handed.append(backing[len(handed)].ctypes.data)
+        return handed[-1]
+
+    pool.take = take
+    a = pool.empty((1 << 14, 4))
+    a[:] = 3.0
+    assert a.flags["C_CONTIGUOUS"] and backing[0][0] == 3.0 and a.ctypes.data == handed[0]
+    view = a.T
+    del a
+    gc.collect()
+    assert not pool.free                       # the view still owns the buffer
+    b = pool.empty((1 << 14, 4))
+    assert b.ctypes.data == handed[1]          # so a second buffer is handed out
+    del view
+    gc.collect()
+    assert pool.free == {1 << 18: [handed[0]]}
+    c = pool.empty((1 << 14, 4))
+    assert c.ctypes.data == handed[0]          # recycled
+    small = pool.empty((8, 4))                 # small results stay ordinary numpy arrays
+    assert small.base is None and len(handed) == 2
+    # without a CUDA device cnfb200_host_alloc refuses and the pool falls back to pageable memory
+    assert cnf.api._pinned.empty((1 << 14, 4)).shape == (1 << 14, 4)
+
+
+def test_algorithmic_bytes_of_the_tensor_path():
+    """bench.py's HBM roofline figures: the exact-trace evaluation is the forward chain plus D tangent chains"""
+    hutch, exact = wl.tc_bytes_per_eval("C4"), wl.tc_bytes_per_eval_exact("C4")
+    assert hutch == 6304 and exact == 27520
+    assert exact > 8 * 2 * 4 * 128             # at least the tau_1 planes of the 8 passes
