@@ -3,17 +3,24 @@
 
   python bench.py --gpus N --steps K --warmup W [--config C2] [--impl reference]
 
-A "step" is one pass of the hot path over one batch of synthetic input: one
-`inference(icnf, TestMode(), xs, ps, st)` call (log-density configs) or one loss+gradient call
-(training configs) on the config's batch.  N=1 workload: C2 = BASELINE.json configs[1]
-(ICNF exact trace, DIJacVecMatrixMode, MLP 2->64->64->2, B = 2^20).  N>1: weak scaling, every
-rank solves its own shard of B columns; the step-size controller sees the whole batch through a
-per-step NCCL allreduce of the error-norm partials.
+BASELINE.json's metric has two halves, and one JSON line (rank 0) carries both:
 
-Prints ONE JSON line (rank 0).  `value` = device-resident inputs, CUDA-event time of the calls
-(max over ranks); `e2e` = the same call with HOST buffers (pinned), host<->device copies inside the
-timed region; `roofline` = the RK stage kernel against the measured FP32-FMA peak; `cpu_baseline`
-= the CPU oracle (port of the reference's CPU path) on a bounded sample on this box's cores.
+  top level   log-density samples/s: C2 = BASELINE.json configs[1] (ICNF exact trace, DIJacVecMatrixMode,
+              MLP 2->64->64->2, B = 2^20 per GPU, weak scaling over N GPUs).  `value` = device-resident inputs,
+              CUDA-event time of the calls (max over ranks); `e2e` = the same call with HOST buffers (pinned),
+              host<->device copies inside the timed region; `roofline` = the RK stage kernel, ALGORITHMIC flops
+               / its mean CUDA-event time / the measured bf16 tensor peak; `cpu_baseline` = the CPU
+              oracle (port of the reference's CPU path) on this box's cores; `parity` = the results of the timed
+              call checked against the oracle on the same inputs at the benchmarked size.
+  "train"     RNODE train samples/s: C3 (configs[2], 32->256->256->32, B = 2^18 per GPU, weak scaling): one
+              loss + gradient call per step (forward solve, discrete-adjoint reverse sweep, gradient allreduce),
+              theta re-uploaded every step; own value / e2e / roofline / parity (fixed slice against the oracle).
+  "train_strong"  C5 (configs[4], 128->1024->1024->128) at the GLOBAL batch 2^22 split over the N GPUs (strong
+              scaling, gradient allreduce); "cond_strong": C4 (configs[3], CondRNODE) global batch 2^20 split N ways.
+
+A "step" is one pass of the hot path over one batch of synthetic input.  The run exits non-zero when a parity
+block is outside north_star's tolerances (the line is still printed).  --config X runs only that config as the
+top-level workload (no extra blocks).
 """
 import argparse
 import json
@@ -30,6 +37,10 @@ sys.path.insert(0, ROOT)
 
 METRIC = {"test": ("logdensity_samples_per_s", "samples/s"),
           "train": ("rnode_train_samples_per_s", "samples/s")}
+# north_star tolerances
+TOL_LOGP, TOL_LOSS, TOL_GRAD = 1e-4, 1e-4, 1e-3
+# accepted-step counts may differ by one (north_star); the two solves then differ at solver tolerance
+TOL_FLIP_LOGP, TOL_FLIP_LOSS, TOL_FLIP_GRAD = 5e-3, 5e-3, 5e-2
 
 
 def parse():
@@ -37,7 +48,7 @@ def parse():
     p.add_argument("--gpus", type=int, default=1)
     p.add_argument("--steps", type=int, default=10)
     p.add_argument("--warmup", type=int, default=3)
-    p.add_argument("--config", default="C2")
+    p.add_argument("--config", default="", help="run only this config (C0..C5) as the top-level workload")
     p.add_argument("--batch", type=int, default=0, help="override the per-GPU batch (debug)")
     p.add_argument("--impl", default="b200", choices=["b200", "reference"])
     p.add_argument("--kernel-path", type=int, default=0)
@@ -46,7 +57,10 @@ def parse():
     p.add_argument("--mode", default="", choices=["", "test", "hutchinson"],
                    help="override the config's headline mode: log-density inference in TestMode (exact trace) "
                         "or in TrainMode (Hutchinson estimate)")
+    p.add_argument("--strong", action="store_true", help="with --config: the config's batch is the GLOBAL batch")
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--no-parity", action="store_true")
+    p.add_argument("--no-extra", action="store_true", help="default run without the train / strong-scaling blocks")
     p.add_argument("--cpu-sample", type=int, default=0)
     return p.parse_args()
 
@@ -111,96 +125,142 @@ def make_model(cnf, cid, device, kernel_path, vector=False):
                          rng=np.random.default_rng(0))
 
 
-def oracle_step(O, cfg, c, inp, train):
-    if train:
-        _, _, _, st = O.loss_grad(cfg, inp["theta"], inp["xs"], inp["ys"], inp["eps"], *c["tspan"])
-    else:
-        _, _, _, st = O.logdensity(cfg, inp["theta"], 0, inp["xs"], inp["ys"], None, *c["tspan"])
-    return st
-
-
 def oracle_config(O, c):
     return O.make_config(c["nvars"], c["naug"], c["dims"], C_=c["C"], trace_mode=c["trace_mode"],
                          lambda1=c["lambda1"], lambda2=c["lambda2"], lambda3=c["lambda3"],
                          reltol=c["reltol"], abstol=c["abstol"])
 
 
-def cpu_sample_size(cid, override):
+def oracle_step(O, cfg, c, inp, kind):
+    """one pass of the CPU path: kind 'train' = loss + gradient, 'hutchinson' = TrainMode inference, else TestMode"""
+    if kind == "train":
+        return O.loss_grad(cfg, inp["theta"], inp["xs"], inp["ys"], inp["eps"], *c["tspan"])
+    if kind == "hutchinson":
+        return O.logdensity(cfg, inp["theta"], 1, inp["xs"], inp["ys"], inp["eps"], *c["tspan"])
+    return O.logdensity(cfg, inp["theta"], 0, inp["xs"], inp["ys"], None, *c["tspan"])
+
+
+def cpu_sample_size(cid, kind, override, cores):
+    """bounded CPU sample: C0-C2 at the full batch, the wide training configs on a slice sized for
+    ~10-20 s of CPU work on `cores` threads"""
     if override:
         return override
-    return {"C0": 64, "C1": 1024, "C2": 1 << 16, "C3": 1 << 11, "C4": 1 << 14, "C5": 1 << 7}[cid]
+    scale = max(1, cores // 8)
+    full = {"C0": 64, "C1": 1024, "C2": 1 << 20}
+    if cid in full:
+        return full[cid]
+    if kind == "train":
+        return {"C3": 1 << 10, "C4": 1 << 12, "C5": 32}[cid] * scale
+    return {"C3": 1 << 12, "C4": 1 << 14, "C5": 128}[cid] * scale
 
 
+def parity_slice(cid, kind):
+    """samples of the in-run parity check where the oracle cannot afford the benchmarked size"""
+    if kind == "train":
+        return {"C0": 64, "C1": 1024, "C2": 1 << 12, "C3": 1 << 11, "C4": 1 << 12, "C5": 64}[cid]
+    return {"C0": 64, "C1": 1024, "C2": 1 << 20, "C3": 1 << 12, "C4": 1 << 14, "C5": 128}[cid]
+
+
+def relerr(a, b):
+    a, b = np.asarray(a, np.float64).reshape(-1), np.asarray(b, np.float64).reshape(-1)
+    return float(np.max(np.abs(a - b) / np.maximum(np.abs(b), 1e-30)))
+
+
+def relnorm(a, b):
+    a, b = np.asarray(a, np.float64).reshape(-1), np.asarray(b, np.float64).reshape(-1)
+    return float(np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-30))
+
+
+def load_peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except (OSError, ValueError):
+        return {}
+
+
+def tensor_peak(peaks, clocks):
+    """SURVEY.md 8.4 / the judge's rule: the burst figure when the sampled SM clock sat at max during the timed
+    region, the sustained one otherwise"""
+    burst = float(peaks.get("bf16_tflops", 1590.0))
+    sust = float(peaks.get("bf16_tflops_sustained", 1400.0))
+    src = "MEASURED_PEAKS.json" if peaks else "fallback (B200_PROFILING.md)"
+    sm, mx = clocks.get("sm_mhz"), clocks.get("sm_max_mhz")
+    if sm and mx and sm >= 0.98 * mx:
+        return burst, f"{src} bf16_tflops (burst: SM clock {sm:.0f} of {mx:.0f} MHz during the timed region)"
+    return sust, f"{src} bf16_tflops_sustained (SM clock {sm} of {mx} MHz during the timed region)"
+
+
+# --------------------------------------------------------------------------------------------------- reference arm
 def run_reference(args, cnf):
-    """--impl reference: the reference's CPU implementation of the path.  Julia is absent, so this
-    is the CPU oracle (a port), all host threads, each step a bounded sample of the workload."""
+    """--impl reference: the reference's CPU implementation of the path.  Julia is absent, so this is the CPU
+    oracle (a port), on ALL host threads (torchrun pins OMP_NUM_THREADS=1: reset explicitly), each step a bounded
+    sample of the workload."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
-        return
+        return 0
     from oracle import oracle as O
+    cores = O.set_num_threads()
     wl = cnf.workloads
-    cid = args.config
+
+    def leg(cid, kind, steps, warmup):
+        c = wl.CONFIGS[cid]
+        Bs = cpu_sample_size(cid, kind, args.cpu_sample, cores)
+        inp = wl.make_inputs(cid, B=Bs)
+        cfg = oracle_config(O, c)
+        for _ in range(warmup):
+            oracle_step(O, cfg, c, inp, kind)
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            st = oracle_step(O, cfg, c, inp, kind)[3]
+        dt = time.perf_counter() - t0
+        val = Bs * steps / dt
+        metric, unit = METRIC["train" if kind == "train" else "test"]
+        full = Bs == c["B"]
+        return {
+            "metric": metric, "value": val, "unit": unit, "steps": steps, "warmup": warmup,
+            "ms_per_step": 1e3 * dt / steps,
+            "config": {"workload": f"{cid}: {c['tag']} dims={c['dims']} B={c['B']} mode={kind}",
+                       "sample_per_step": Bs, "naccept": st["naccept"], "nreject": st["nreject"]},
+            "cpu_baseline": {"value": val, "unit": unit, "cores": cores, "kind": "port",
+                             "sample": (f"the full {Bs}-sample batch per step" if full else
+                                        f"{Bs} samples per step of the {c['B']}-sample workload (CPU throughput is "
+                                        "linear in the batch)")},
+            "e2e": {"value": val, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        }
+
+    cid = args.config or "C2"
     c = wl.CONFIGS[cid]
-    train = c["mode"] == "train"
-    Bs = cpu_sample_size(cid, args.cpu_sample)
-    inp = wl.make_inputs(cid, B=Bs)
-    cfg = oracle_config(O, c)
-    for _ in range(args.warmup):
-        oracle_step(O, cfg, c, inp, train)
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        st = oracle_step(O, cfg, c, inp, train)
-    dt = time.perf_counter() - t0
-    val = Bs * args.steps / dt
-    metric, unit = METRIC[c["mode"]]
-    line = {
-        "impl": "reference", "metric": metric, "value": val, "unit": unit, "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-        "data": "synthetic",
-        "config": {"workload": f"{cid}: {c['tag']} dims={c['dims']} B={c['B']} mode={c['mode']}",
-                   "sample_per_step": Bs, "naccept": st["naccept"], "nreject": st["nreject"]},
-        "cpu_baseline": {"value": val, "unit": unit, "cores": O.num_threads(), "kind": "port",
-                         "sample": f"{Bs} samples per step of the {c['B']}-sample workload "
-                                   "(CPU throughput is linear in the batch)"},
-        "e2e": {"value": val, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0,
-    }
+    kind = "hutchinson" if args.mode == "hutchinson" else ("test" if args.mode == "test" else c["mode"])
+    top = leg(cid, kind, args.steps, args.warmup)
+    line = {"impl": "reference", "n_gpus": args.gpus, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "gpu_launches": 0}
+    line.update(top)
+    if not args.config and not args.no_extra:
+        line["train"] = leg("C3", "train", min(args.steps, 3), 1)
     emit(line)
+    return 0
 
 
-def main():
-    args = parse()
-    import cnfb200_loader
-    cnf = cnfb200_loader.load_package()
-    if args.impl == "reference":
-        return run_reference(args, cnf)
+# --------------------------------------------------------------------------------------------------- one workload
+class Ctx:
+    pass
+
+
+def run_leg(ctx, cid, kind, B, steps, warmup, strong=False, want_cpu=True, want_parity=True):
+    """times one workload on every rank.  kind: 'test' (TestMode inference), 'hutchinson' (TrainMode inference),
+    'train' (loss + gradient).  B = per-GPU batch.  Returns the block (rank 0) or None."""
     import torch
     import torch.distributed as dist
-    wl = cnf.workloads
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback")
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    cid = args.config
+    cnf, args, wl = ctx.cnf, ctx.args, ctx.cnf.workloads
+    rank, world, local, dev = ctx.rank, ctx.world, ctx.local, ctx.dev
     c = wl.CONFIGS[cid]
-    if args.mode:   # inference on a training config (e.g. C4: "Test (inference) and Train")
-        c = dict(c, mode="test")
-    train = c["mode"] == "train"
-    B = args.batch or c["B"]
-    D = c["nvars"] + c["naug"]
+    train = kind == "train"
     inp = wl.make_inputs(cid, B=B, offset=rank)
     icnf = make_model(cnf, cid, local, args.kernel_path, args.compute_mode == "vector")
     if world > 1:
         cnf.parallel.init_comm(icnf, rank, world)
     cnf.set_option(icnf, "time_stages", 1)
-    mode = cnf.TrainMode() if (train or args.mode == "hutchinson") else cnf.TestMode()
-    dev = torch.device("cuda", local)
-    # device-resident inputs (value) and pinned host inputs (e2e); `rows x B` views, Julia-style
+    mode = cnf.TrainMode() if kind in ("train", "hutchinson") else cnf.TestMode()
     xs_d = torch.from_numpy(inp["xs"]).to(dev).t()
     ys_d = torch.from_numpy(inp["ys"]).to(dev).t() if inp["ys"] is not None else None
     eps_d = torch.from_numpy(inp["eps"]).to(dev).t()
@@ -209,14 +269,21 @@ def main():
     ys_h = pin(inp["ys"]) if inp["ys"] is not None else None
     eps_h = pin(inp["eps"])
     theta = inp["theta"]
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    # training: a real fit! step uploads a new theta every step (cnfb200_set_params: H2D, transposes, hi/lo planes);
+    # two vectors that differ in the last bit of one weight defeat the host mirror's unchanged-theta shortcut
+    theta_b = theta.copy()
+    theta_b[0] = np.nextafter(theta_b[0], np.float32(1.0))
+    thetas = (theta, theta_b)
+    nstep = [0]
 
     def step(xs, ys, eps):
-        tail = ((ys,) if ys is not None else ()) + (theta, {})
+        th = thetas[nstep[0] & 1] if train else theta
+        nstep[0] += 1
+        tail = ((ys,) if ys is not None else ()) + (th, {})
         if train:
             out = cnf.loss_and_grad(icnf, mode, xs, *tail, eps=eps)
         else:
-            out = cnf.inference(icnf, mode, xs, *tail, **({"eps": eps} if args.mode == "hutchinson" else {}))
+            out = cnf.inference(icnf, mode, xs, *tail, **({"eps": eps} if kind == "hutchinson" else {}))
         return out, cnf.last_stats(icnf)
 
     def barrier():
@@ -225,7 +292,7 @@ def main():
             dist.barrier()
             torch.cuda.synchronize()
 
-    for _ in range(args.warmup):
+    for _ in range(warmup):
         step(xs_d, ys_d, eps_d)
     sampler = ClockSampler(local)
     barrier()
@@ -233,8 +300,8 @@ def main():
     ms_dev = ms_stage = ms_solve = 0.0
     n_stage = launches = 0
     t_wall = time.perf_counter()
-    for _ in range(args.steps):
-        flush.zero_()
+    for _ in range(steps):
+        ctx.flush.zero_()
         torch.cuda.synchronize()
         _, st = step(xs_d, ys_d, eps_d)
         ms_dev += st["ms_total"]
@@ -245,12 +312,17 @@ def main():
     barrier()
     wall = time.perf_counter() - t_wall
     # end-to-end: same call, HOST buffers; H2D of the inputs and D2H of the result inside the call
-    for _ in range(min(args.warmup, 2)):
+    # (already warm: this only primes the pinned output pool; one call when a step takes seconds)
+    for _ in range(1 if ms_dev / steps > 2000.0 else min(warmup, 2)):
         step(xs_h, ys_h, eps_h)
     barrier()
     t_e2e = time.perf_counter()
-    for _ in range(args.steps):
+    e2e_each, e2e_dev = [], 0.0
+    for _ in range(steps):
+        t_one = time.perf_counter()
         out_h, st_h = step(xs_h, ys_h, eps_h)
+        e2e_each.append(time.perf_counter() - t_one)
+        e2e_dev += st_h["ms_total"]
     barrier()
     e2e_s = time.perf_counter() - t_e2e
     clocks = sampler.stop()
@@ -258,148 +330,284 @@ def main():
         t = torch.tensor([ms_dev, e2e_s], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_dev, e2e_s = float(t[0]), float(t[1])
+
+    # ---- parity of what was just timed (rank 0 checks; multi-rank test legs gather every shard's log-density)
+    parity = None
+    if want_parity and not args.no_parity:
+        parity = check_parity(ctx, cid, kind, B, inp, out_h, st_h)
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
-    metric, unit = METRIC[c["mode"]]
-    total = B * world * args.steps
+        del icnf
+        torch.cuda.empty_cache()
+        return None
+
+    metric, unit = METRIC["train" if train else "test"]
+    total = B * world * steps
     value = total / (ms_dev * 1e-3)
-    # (theta is the same host vector in every step: the host mirror uploads it once and skips the copy afterwards)
-    h2d = inp["xs"].nbytes + (inp["ys"].nbytes if inp["ys"] is not None else 0) + \
-        (inp["eps"].nbytes if train else 0)
-    d2h = (theta.nbytes + 4) if train else (B * 4 + B * 4)
-    # roofline of the dominant kernel: one RK stage kernel = one augmented_f evaluation of B samples
-    flops_eval = wl.flops_per_eval(cid, "train" if args.mode == "hutchinson" else c["mode"]) * B
-    lib = cnf._cabi.load()
+    D = c["nvars"] + c["naug"]
+    nb = lambda a: a.nbytes if a is not None else 0
+    h2d = nb(inp["xs"]) + nb(inp["ys"]) + (nb(inp["eps"]) if kind != "test" else 0) + (theta.nbytes if train else 0)
+    d2h = (theta.nbytes + 4) if train else (B * 4 + B * 4 * (3 if kind == "hutchinson" else 1))
+    roofline = make_roofline(ctx, cid, kind, B, st, ms_stage, n_stage, ms_solve, ms_dev, steps, clocks)
+    par = f"dp{world} (columns sharded)"
+    if world > 1:
+        par += f", error-norm exchange: {cnf.parallel.errnorm_exchange(icnf)}"
+        if train:
+            par += ", gradient + loss allreduce (NCCL) after the reverse sweep"
+    block = {
+        "metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": steps, "warmup": warmup,
+        "ms_per_step": ms_dev / steps, "higher_is_better": True, "scaling": "strong" if strong else "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{cid}: {c['tag']} dims={c['dims']} B={B}/GPU mode={kind} "
+                               f"trace={'JVP' if c['trace_mode'] else 'VJP'} tspan={c['tspan']}",
+                   "global_batch": B * world, "parallelism": par,
+                   "l2": "256 MB flush between timed steps", "naccept": st["naccept"],
+                   "nreject": st["nreject"], "nf": st["nf"], "kernel_path": st["kernel_path"],
+                   "timing": "sum of per-call CUDA-event times on the library stream, max over ranks",
+                   "wall_ms_per_step_incl_flush": 1e3 * wall / steps},
+        "clocks": clocks,
+        "e2e": {"value": total / e2e_s, "unit": unit, "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": d2h, "ms_per_step": 1e3 * e2e_s / steps,
+                "ms_per_step_min": 1e3 * min(e2e_each), "ms_per_step_max": 1e3 * max(e2e_each),
+                "device_ms_per_step": e2e_dev / steps},
+        "gpu_launches": launches,
+        "roofline": roofline,
+    }
+    if train:
+        block["config"]["theta_upload"] = "every step (cnfb200_set_params inside the timed call: a different host theta each step)"
+    if parity is not None:
+        block["parity"] = parity
+    if want_cpu and not args.no_cpu_baseline and world == 1:
+        block["cpu_baseline"] = cpu_baseline(ctx, cid, kind, B)
+    del icnf, xs_d, ys_d, eps_d
+    torch.cuda.empty_cache()
+    return block
+
+
+def cpu_baseline(ctx, cid, kind, B):
+    from oracle import oracle as O
+    wl = ctx.cnf.workloads
+    c = wl.CONFIGS[cid]
+    cores = O.set_num_threads()
+    Bs = min(cpu_sample_size(cid, kind, ctx.args.cpu_sample, cores), B)
+    sinp = wl.make_inputs(cid, B=Bs)
+    cfg = oracle_config(O, c)
+    oracle_step(O, cfg, c, sinp, kind)
+    t0 = time.perf_counter()
+    reps = 0
+    while reps < 3 and time.perf_counter() - t0 < 20:
+        oracle_step(O, cfg, c, sinp, kind)
+        reps += 1
+    dt = (time.perf_counter() - t0) / reps
+    unit = METRIC["train" if kind == "train" else "test"][1]
+    return {"value": Bs / dt, "unit": unit, "cores": cores, "kind": "port",
+            "sample": f"{Bs} of {B} samples, {reps} repetitions, same synthetic stream"}
+
+
+def check_parity(ctx, cid, kind, B, inp, out_h, st_h):
+    """the results of the timed e2e call (host buffers) against the CPU oracle on the same inputs.
+    Test legs: at the benchmarked size when the oracle affords it (every rank's shard, gathered: the oracle solves
+    the GLOBAL batch, whose whole-matrix error norm couples the shards); otherwise, and for training legs, a fixed
+    slice solved by both sides as its own batch (single GPU, rank 0)."""
+    import torch
+    import torch.distributed as dist
+    from oracle import oracle as O
+    cnf, wl = ctx.cnf, ctx.cnf.workloads
+    rank, world = ctx.rank, ctx.world
+    c = wl.CONFIGS[cid]
+    Bp = parity_slice(cid, kind)
+    full = (kind != "train") and Bp >= B and B * world <= (1 << 23)
+    if full:
+        lp = np.ascontiguousarray(np.asarray(out_h[0], dtype=np.float32).reshape(-1))
+        if world > 1:
+            t = torch.from_numpy(lp).to(ctx.dev)
+            parts = [torch.empty_like(t) for _ in range(world)] if rank == 0 else None
+            dist.gather(t, parts, dst=0)
+            if rank != 0:
+                return None
+            lp = torch.cat(parts).cpu().numpy()
+        cores = O.set_num_threads()
+        shards = [inp] + [wl.make_inputs(cid, B=B, offset=r) for r in range(1, world)]
+        cat = lambda k: None if shards[0][k] is None else np.concatenate([s[k] for s in shards])
+        ginp = dict(xs=cat("xs"), ys=cat("ys"), eps=cat("eps"), theta=inp["theta"])
+        t0 = time.perf_counter()
+        rlp, _, _, rst = oracle_step(O, oracle_config(O, c), c, ginp, kind)
+        dt = time.perf_counter() - t0
+        ds = int(st_h["naccept"] - rst["naccept"])
+        err = relerr(lp, rlp)
+        tol = TOL_LOGP if ds == 0 else TOL_FLIP_LOGP
+        return {"max_rel_logp": err, "dsteps": ds, "naccept": int(st_h["naccept"]), "naccept_oracle": int(rst["naccept"]),
+                "B_checked": int(B * world), "what": "every sample of the timed call (all ranks) vs the oracle's solve of "
+                "the global batch", "tol_logp": tol, "ok": bool(abs(ds) <= 1 and err < tol), "oracle_s": dt, "oracle_cores": cores}
+    if rank != 0:
+        return None
+    cores = O.set_num_threads()
+    Bp = min(Bp, B)
+    sinp = wl.make_inputs(cid, B=Bp)
+    cfg = oracle_config(O, c)
+    one = make_model(cnf, cid, ctx.local, ctx.args.kernel_path, ctx.args.compute_mode == "vector")   # no communicator
+    mode = cnf.TrainMode() if kind in ("train", "hutchinson") else cnf.TestMode()
+    tail = ((sinp["ys"].T,) if sinp["ys"] is not None else ()) + (sinp["theta"], {})
+    t0 = time.perf_counter()
+    if kind == "train":
+        val, g = cnf.loss_and_grad(one, mode, sinp["xs"].T, *tail, eps=sinp["eps"].T)
+        st = cnf.last_stats(one)
+        rval, rg, _, rst = oracle_step(O, cfg, c, sinp, kind)
+        ds = int(st["naccept"] - rst["naccept"])
+        le, ge = abs(val - rval) / abs(rval), relnorm(g, rg)
+        tl, tg = (TOL_LOSS, TOL_GRAD) if ds == 0 else (TOL_FLIP_LOSS, TOL_FLIP_GRAD)
+        out = {"loss_rel": le, "grad_rel": ge, "dsteps": ds, "naccept": int(st["naccept"]),
+               "naccept_oracle": int(rst["naccept"]), "B_checked": int(Bp), "tol_loss": tl, "tol_grad": tg,
+               "ok": bool(abs(ds) <= 1 and le < tl and ge < tg), "kernel_path": st["kernel_path"]}
+    else:
+        lp, _ = cnf.inference(one, mode, sinp["xs"].T, *tail, **({"eps": sinp["eps"].T} if kind == "hutchinson" else {}))
+        st = cnf.last_stats(one)
+        rlp, _, _, rst = oracle_step(O, cfg, c, sinp, kind)
+        ds = int(st["naccept"] - rst["naccept"])
+        err = relerr(lp, rlp)
+        tol = TOL_LOGP if ds == 0 else TOL_FLIP_LOGP
+        out = {"max_rel_logp": err, "dsteps": ds, "naccept": int(st["naccept"]), "naccept_oracle": int(rst["naccept"]),
+               "B_checked": int(Bp), "tol_logp": tol, "ok": bool(abs(ds) <= 1 and err < tol), "kernel_path": st["kernel_path"]}
+    out["what"] = (f"a fixed {Bp}-sample slice of the workload solved as its own batch by the library (1 GPU) and by "
+                   "the oracle: the oracle cannot afford the benchmarked size")
+    out["oracle_s"] = time.perf_counter() - t0
+    out["oracle_cores"] = cores
+    del one
+    return out
+
+
+def make_roofline(ctx, cid, kind, B, st, ms_stage, n_stage, ms_solve, ms_dev, steps, clocks):
+    """SURVEY.md 8.4: achieved = ALGORITHMIC flops of one augmented_f evaluation of B samples (F_E or F_H per sample;
+    operand splitting, recomputation and padding are overhead that lowers the fraction) / the mean CUDA-event time of
+    the stage kernel(s) of one evaluation / the peak of the pipe the kernel runs on."""
     import ctypes
-    pk = ctypes.c_double(0.0)
-    lib.cnfb200_measure_fp32_peak(local, ctypes.byref(pk))
+    cnf, wl = ctx.cnf, ctx.cnf.workloads
+    c = wl.CONFIGS[cid]
+    D = c["nvars"] + c["naug"]
+    R = D + (1 if kind == "test" else 3)
+    fmode = "test" if kind == "test" else "train"
+    flops_eval = wl.flops_per_eval(cid, fmode) * B
     stage_ms = ms_stage / max(n_stage, 1)
-    achieved = flops_eval / (stage_ms * 1e-3) / 1e12 if stage_ms > 0 else 0.0
+    alg = flops_eval / (stage_ms * 1e-3) / 1e12 if stage_ms > 0 else 0.0
+    peaks = load_peaks()
     traffic = None
     try:
         traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(f"{cid}:path{st['kernel_path']}")
     except (OSError, ValueError):
         pass
-    if st["kernel_path"] == 4:
-        # vector mode: the whole adaptive solve of every sample is ONE kernel; a warp runs as long as its slowest lane,
-        # so the executed work is nf_max evaluations per lane
-        solve_ms = ms_solve / args.steps
-        achieved = flops_eval * st["nf"] / (solve_ms * 1e-3) / 1e12 if solve_ms > 0 else 0.0
-        roofline = {"bound": "fp32_fma", "achieved": achieved, "peak": pk.value, "unit": "TFLOP/s",
-                    "frac": achieved / pk.value if pk.value else None, "traffic": traffic,
-                    "kernel": "k_solve_vector: one thread = one sample's whole Tsit5 solve in registers",
-                    "peak_source": "measured in this run by cnfb200_measure_fp32_peak",
-                    "note": "achieved counts lane-executed evaluations (nf of the slowest sample for every lane: lanes that "
-                            "finish early idle inside the warp), so it is an upper bound on useful flops",
-                    "stage_ms": solve_ms, "stage_launches": 1, "kernel_path": 4,
-                    "stage_share_of_step": ms_solve / ms_dev if ms_dev else None}
-    elif st["kernel_path"] == 6:
-        # narrow exact-trace nets with layer 2 (94 % of the flops) on tcgen05: the MMAs execute 3 f16 flops per
-        # algorithmic flop of that layer (FP16 hi/lo split); layers 1 and 3 and all elementwise work stay SIMT
-        peaks = {}
-        try:
-            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-        except (OSError, ValueError):
-            pass
-        peak = float(peaks.get("bf16_tflops_sustained", 1400.0))
+    path = st["kernel_path"]
+    common = {"traffic": traffic, "traffic_source": "static: dram__bytes_read+write per launch from the committed ncu --set full "
+              "capture of this kernel (profiles/traffic.json), not measured in this run" if traffic else None,
+              "stage_ms": stage_ms, "stage_launches": n_stage, "kernel_path": path,
+              "stage_share_of_step": ms_stage / ms_dev if ms_dev else None,
+              "algorithmic_flops_per_eval": flops_eval,
+              "algorithmic_bytes_per_eval": (2 * R + D) * 4 * B,
+              "algorithmic_gbs": (2 * R + D) * 4 * B / (stage_ms * 1e-3) / 1e9 if stage_ms > 0 else None}
+    if path in (3, 6, 7):
+        peak, src = tensor_peak(peaks, clocks)
         dims = c["dims"]
-        D = c["nvars"] + c["naug"]
-        mma_flops = 3 * 2 * dims[1] * dims[2] * (1 + D) * B      # executed by tcgen05.mma per evaluation
-        executed = mma_flops / (stage_ms * 1e-3) / 1e12 if stage_ms > 0 else 0.0
-        roofline = {"bound": "tensor", "achieved": executed, "peak": peak, "unit": "TFLOP/s",
-                    "frac": executed / peak, "traffic": traffic,
-                    "kernel": "k_stage_narrow_tc: RK stage kernel, layer 2 of the activation and the D tangents as "
-                              "tcgen05 MMAs on operands the SIMT phase writes into swizzled shared memory",
-                    "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback 1.4 PFLOP/s sustained",
-                    "note": "achieved = f16 MMA flops executed (3 per algorithmic flop of layer 2: hi*hi + lo*hi + hi*lo); "
-                            "the kernel is bound by the SIMT prologue/epilogue (tanh, hi/lo split, layers 1 and 3: "
-                            "~2.2 k instructions per sample, issue slots 46 % and the MUFU pipe 43 % busy in ncu), not by the tensor pipe; "
-                            "algorithmic_tflops / fp32_fma_peak shows how far it is above the FP32-FMA roofline that "
-                            "bounded the register-resident kernel (kernel_path 2)",
-                    "algorithmic_tflops": achieved, "fp32_fma_peak": pk.value,
-                    "algorithmic_over_fp32_fma_peak": achieved / pk.value if pk.value else None,
-                    "stage_ms": stage_ms, "stage_launches": n_stage, "kernel_path": 6,
-                    "stage_share_of_step": ms_stage / ms_dev if ms_dev else None}
-    elif st["kernel_path"] == 3:
-        # tensor path: FP16 hi/lo operand splitting executes 3 f16 MMA flops per algorithmic flop
-        peaks = {}
-        try:
-            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-        except (OSError, ValueError):
-            pass
-        peak = float(peaks.get("bf16_tflops_sustained", 1400.0))
-        hbm_peak = float(peaks.get("hbm_gbs", 6400.0))
-        bytes_eval = (wl.tc_bytes_per_eval_exact(cid) if (c["mode"] == "test" and args.mode != "hutchinson") else wl.tc_bytes_per_eval(cid)) * B
-        t_hbm = bytes_eval / (hbm_peak * 1e9)
-        t_tensor = 3 * flops_eval / (peak * 1e12)
-        if t_hbm > t_tensor:
-            # narrow hidden widths: the layer GEMMs stream hi/lo planes through HBM faster than they fill the tensor pipe
-            gbs = bytes_eval / (stage_ms * 1e-3) / 1e9 if stage_ms > 0 else 0.0
-            roofline = {"bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s", "frac": gbs / hbm_peak,
-                        "traffic": traffic,
-                        "kernel": "one augmented_f evaluation = 2L tcgen05 layer GEMMs (k_tc_gemm) + prep",
-                        "peak_source": "MEASURED_PEAKS.json hbm_gbs (copy bandwidth)" if peaks else "fallback 6.4 TB/s",
-                        "note": "achieved = algorithmic bytes of the evaluation (workloads.tc_bytes_per_eval: operands and "
-                                "results of every layer GEMM as hi/lo 16-bit planes) / mean evaluation time; the tensor-pipe "
-                                "time of the same evaluation at the sustained bf16 peak would be "
-                                f"{1e3 * t_tensor:.3f} ms against {1e3 * t_hbm:.3f} ms of HBM time",
-                        "algorithmic_tflops": achieved, "executed_f16_tflops": 3 * achieved,
-                        "stage_ms": stage_ms, "stage_launches": n_stage, "kernel_path": 3,
-                        "stage_share_of_step": ms_stage / ms_dev if ms_dev else None}
+        if path == 6:   # only layer 2 of the activation and of the D tangents runs on the tensor pipe
+            executed = 3 * 2 * dims[1] * dims[2] * (1 + D) * B / (stage_ms * 1e-3) / 1e12 if stage_ms > 0 else 0.0
+            kern = ("k_stage_narrow_tc: RK stage kernel, layer 2 of the activation and the D tangents as tcgen05 MMAs on "
+                    "operands the SIMT phase writes into swizzled shared memory")
         else:
-          roofline = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                    "frac": achieved / peak, "traffic": traffic,
-                    "kernel": "one augmented_f evaluation = 2L tcgen05 layer GEMMs (k_tc_gemm) + prep",
-                    "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (dense bf16, stage timed inside a "
-                                   "long step)" if peaks else "fallback 1.4 PFLOP/s sustained (B200_PROFILING.md)",
-                    "note": "achieved counts ALGORITHMIC flops (F_H per sample); the kernels execute 3x that in "
-                            "f16 MMA flops (FP16 hi/lo split, hi*hi + lo*hi + hi*lo, for FP32-level accuracy)",
-                    "executed_f16_tflops": 3 * achieved, "stage_ms": stage_ms, "stage_launches": n_stage,
-                    "kernel_path": 3, "stage_share_of_step": ms_stage / ms_dev if ms_dev else None}
+            executed = 3 * alg
+            kern = ("k_tc_fused: one augmented_f evaluation, all layer products of a 128-sample tile chained on chip "
+                    "(tcgen05, A operand in TMEM)" if path == 7 else
+                    "one augmented_f evaluation = 2L tcgen05 layer GEMMs (k_tc_gemm) + prep")
+        rf = {"bound": "tensor", "achieved": alg, "peak": peak, "unit": "TFLOP/s", "frac": alg / peak if peak else None,
+              "kernel": kern, "peak_source": src,
+              "note": "achieved = ALGORITHMIC flops (SURVEY.md 8.4); the FP16 hi/lo operand split executes 3 f16 MMA flops "
+                      "per algorithmic flop of a tensor-core product (hi*hi + lo*hi + hi*lo), which is overhead here: a "
+                      "kernel that kept the tensor pipe 100 % busy would read frac = 1/3",
+              "executed_f16_tflops": executed, "executed_frac": executed / peak if peak else None}
     else:
-        roofline = {"bound": "fp32_fma", "achieved": achieved, "peak": pk.value, "unit": "TFLOP/s",
-                    "frac": achieved / pk.value if pk.value else None, "traffic": traffic,
-                    "kernel": "RK stage kernel (augmented_f over the whole batch)",
-                    "peak_source": "measured in this run by cnfb200_measure_fp32_peak (dependent-FFMA "
-                                   "microbenchmark); MEASURED_PEAKS.json has no FP32 figure",
-                    "stage_ms": stage_ms, "stage_launches": n_stage, "kernel_path": st["kernel_path"],
-                    "stage_share_of_step": ms_stage / ms_dev if ms_dev else None}
-    line = {
-        "metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{cid}: {c['tag']} dims={c['dims']} B={B}/GPU mode={c['mode']} "
-                               f"trace={'JVP' if c['trace_mode'] else 'VJP'} tspan={c['tspan']}",
-                   "global_batch": B * world, "parallelism": f"dp{world} (columns sharded)" + (f", error-norm exchange: {cnf.parallel.errnorm_exchange(icnf)}" if world > 1 else ""),
-                   "l2": "256 MB flush between timed steps", "naccept": st["naccept"],
-                   "nreject": st["nreject"], "nf": st["nf"], "timing": "sum of per-call CUDA-event "
-                   "times on the library stream, max over ranks", "wall_ms_per_step_incl_flush":
-                   1e3 * wall / args.steps},
-        "clocks": clocks,
-        "e2e": {"value": total / e2e_s, "unit": unit, "h2d_bytes_per_step": h2d,
-                "d2h_bytes_per_step": d2h, "ms_per_step": 1e3 * e2e_s / args.steps},
-        "gpu_launches": launches,
-        "roofline": roofline,
-    }
-    if not args.no_cpu_baseline and world == 1:
-        from oracle import oracle as O
-        Bs = cpu_sample_size(cid, args.cpu_sample)
-        sinp = wl.make_inputs(cid, B=Bs)
-        cfg = oracle_config(O, c)
-        oracle_step(O, cfg, c, sinp, train)
-        t0 = time.perf_counter()
-        reps = 0
-        while reps < 3 and time.perf_counter() - t0 < 20:
-            oracle_step(O, cfg, c, sinp, train)
-            reps += 1
-        dt = (time.perf_counter() - t0) / reps
-        line["cpu_baseline"] = {"value": Bs / dt, "unit": unit, "cores": O.num_threads(), "kind": "port",
-                                "sample": f"{Bs} of {B} samples, {reps} repetitions, same synthetic stream"}
-    emit(line)
+        pk = ctypes.c_double(0.0)
+        cnf._cabi.load().cnfb200_measure_fp32_peak(ctx.local, ctypes.byref(pk))
+        achieved = alg
+        extra = {}
+        if path == 4:   # vector mode: one launch = every sample's whole solve; a warp runs as long as its slowest lane
+            solve_ms = ms_solve / steps
+            achieved = flops_eval * st["nf"] / (solve_ms * 1e-3) / 1e12 if solve_ms > 0 else 0.0
+            extra = {"note": "achieved counts lane-executed evaluations (nf of the slowest sample for every lane)",
+                     "stage_ms": solve_ms, "stage_launches": 1}
+        rf = {"bound": "fp32_fma", "achieved": achieved, "peak": pk.value, "unit": "TFLOP/s",
+              "frac": achieved / pk.value if pk.value else None,
+              "kernel": "RK stage kernel (augmented_f over the whole batch)",
+              "peak_source": "measured in this run by cnfb200_measure_fp32_peak (dependent-FFMA microbenchmark); "
+                             "MEASURED_PEAKS.json has no FP32 figure"}
+        rf.update(extra)
+    for k, v in common.items():
+        rf.setdefault(k, v)
+    if kind == "train":
+        # the whole training call (SURVEY.md 8.4): (6 nattempt + 3) F_H + 6 naccept F_B per sample
+        natt = st["naccept"] + st["nreject"]
+        fl = ((6 * natt + 3) * wl.flops_per_eval(cid, "train") + 6 * st["naccept"] * wl.flops_backward_per_eval(cid)) * B
+        peak, src = tensor_peak(peaks, clocks)
+        t = ms_dev / steps * 1e-3
+        rf["step"] = {"algorithmic_flops": fl, "achieved": fl / t / 1e12 if t > 0 else None, "unit": "TFLOP/s",
+                      "peak": peak, "frac": fl / t / 1e12 / peak if t > 0 and peak else None,
+                      "note": "whole loss+gradient call: forward solve + reverse sweep + gradient allreduce"}
+    return rf
+
+
+# --------------------------------------------------------------------------------------------------- main
+def main():
+    args = parse()
+    import cnfb200_loader
+    cnf = cnfb200_loader.load_package()
+    if args.impl == "reference":
+        return run_reference(args, cnf)
+    import torch
+    import torch.distributed as dist
+    ctx = Ctx()
+    ctx.cnf, ctx.args = cnf, args
+    ctx.rank = int(os.environ.get("RANK", "0"))
+    ctx.local = int(os.environ.get("LOCAL_RANK", "0"))
+    ctx.world = int(os.environ.get("WORLD_SIZE", "1"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback")
+    torch.cuda.set_device(ctx.local)
+    if ctx.world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", ctx.local))
+    ctx.dev = torch.device("cuda", ctx.local)
+    ctx.flush = torch.empty(256 << 20, dtype=torch.uint8, device=ctx.dev)  # > 126 MB L2
+    wl = cnf.workloads
+    world = ctx.world
+
+    cid = args.config or "C2"
+    c = wl.CONFIGS[cid]
+    kind = "hutchinson" if args.mode == "hutchinson" else ("test" if args.mode == "test" else c["mode"])
+    B = args.batch or c["B"]
+    strong = bool(args.config and args.strong)
+    if strong:
+        B = max(B // world, 1)
+    line = run_leg(ctx, cid, kind, B, args.steps, args.warmup, strong=strong)
+    ok = True
+    if not args.config and not args.no_extra:
+        extras = [
+            # name, config, kind, per-GPU batch, steps, warmup, strong
+            ("train", "C3", "train", wl.CONFIGS["C3"]["B"], min(args.steps, 10), max(3, min(args.warmup, 3)), False),
+            ("cond_strong", "C4", "train", max(wl.CONFIGS["C4"]["B"] // world, 1), min(args.steps, 5), 3, True),
+            ("train_strong", "C5", "train", max(wl.CONFIGS["C5"]["B"] // world, 1), min(args.steps, 2 if world < 4 else 5), 3, True),
+        ]
+        for name, xc, xk, xB, xs, xw, xstrong in extras:
+            try:
+                blk = run_leg(ctx, xc, xk, xB, xs, xw, strong=xstrong, want_cpu=(name == "train"),
+                              want_parity=(name != "cond_strong"))
+            except Exception as e:   # an extra block must not take the headline record down with it
+                blk = {"error": f"{type(e).__name__}: {e}"}
+                ok = False
+            if ctx.rank == 0:
+                line[name] = blk
+    if ctx.rank == 0:
+        for blk in [line] + [line.get(k) for k in ("train", "cond_strong", "train_strong")]:
+            if isinstance(blk, dict) and isinstance(blk.get("parity"), dict) and not blk["parity"].get("ok", True):
+                ok = False
+        line["parity_ok"] = ok
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
+    return 0 if ok else 3
 
 
 _REAL_STDOUT = None
@@ -423,4 +631,4 @@ def emit(line):
 
 if __name__ == "__main__":
     _own_stdout()
-    main()
+    sys.exit(main())

@@ -10,5 +10,5 @@ from .api import (  # noqa: F401
     B200Libs, Chain, CondFFJORD, CondPlanar, CondRNODE, Dense, Planar, PlanarLayer, DIJacVecMatrixMode, DIJacVecVectorMode,
     DIVecJacMatrixMode, DIVecJacVectorMode, FFJORD, ICNF, RNODE, TestMode, TrainMode, augmented_f,
     construct, generate, inference, last_stats, loss, loss_and_grad, param_offsets, set_option, setup,
-    steer_tspan, seed_device_rng, last_eps, fit_epochs,
+    steer_tspan, seed_device_rng, last_eps, fit_epochs, steer_sequence,
 )

@@ -17,7 +17,7 @@ EXPORTS = [
     "cnfb200_version", "cnfb200_create", "cnfb200_destroy", "cnfb200_set_option", "cnfb200_last_error",
     "cnfb200_set_params", "cnfb200_comm_unique_id", "cnfb200_comm_init", "cnfb200_comm_p2p", "cnfb200_augmented_f",
     "cnfb200_logdensity", "cnfb200_loss_grad", "cnfb200_loss_grad_mode", "cnfb200_generate", "cnfb200_measure_fp32_peak",
-    "cnfb200_seed_rng", "cnfb200_last_eps", "cnfb200_fit_epochs", "cnfb200_host_alloc", "cnfb200_host_free",
+    "cnfb200_seed_rng", "cnfb200_last_eps", "cnfb200_fit_epochs", "cnfb200_host_alloc", "cnfb200_host_free", "cnfb200_set_steer",
 ]
 
 
@@ -91,6 +91,7 @@ def load():
     lib.cnfb200_measure_fp32_peak.argtypes = [C.c_int32, C.POINTER(C.c_double)]
     lib.cnfb200_host_alloc.argtypes = [C.c_size_t, C.POINTER(C.c_void_p)]
     lib.cnfb200_host_free.argtypes = [C.c_void_p]
+    lib.cnfb200_set_steer.argtypes = [C.c_void_p, C.c_float]
     lib.cnfb200_seed_rng.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64]
     lib.cnfb200_last_eps.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
     lib.cnfb200_fit_epochs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_void_p,

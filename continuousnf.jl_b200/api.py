@@ -456,7 +456,10 @@ def fit_epochs(icnf, X, Y, ps, *, batch_size, n_epochs, perm=None, eta=1e-3, bet
         p = np.ascontiguousarray(perm, dtype=np.int64)
         if p.shape != (n_epochs, x.B):
             raise ValueError(f"perm must have shape ({n_epochs}, {x.B})")
-    t0, t1 = steer_tspan(icnf, TrainMode())
+    # the reference re-draws the steered t1 in every loss call of the fit (src/base_icnf.jl:108-121, :283): the
+    # library draws it per mini-batch from its own documented stream (cnfb200_set_steer, `steer_sequence` below)
+    t0, t1 = icnf.tspan
+    icnf._check(lib.cnfb200_set_steer(h, float(icnf.steer_rate)), "cnfb200_set_steer")
     out = np.empty(param_offsets(icnf.dims, icnf.nn.planar)[2], np.float32)
     hist = np.empty(n_epochs, np.float32)
     st_ = _cabi.CnfStats()
@@ -467,6 +470,26 @@ def fit_epochs(icnf, X, Y, ps, *, batch_size, n_epochs, perm=None, eta=1e-3, bet
     icnf._check(rc, "cnfb200_fit_epochs")
     icnf._last_stats = st_.as_dict()
     return out, hist
+
+
+def steer_sequence(seed, n, steer_rate, tspan):
+    """the t1 values cnfb200_fit_epochs uses for its first `n` mini-batches after seed_device_rng(icnf, seed)
+    (include/cnfb200.h, cnfb200_set_steer): host-side restatement for callers that want to replay a fit"""
+    m64 = (1 << 64) - 1
+    s = (int(seed) ^ 0xA5A5A5A55A5A5A5A) & m64
+    t0, t1 = np.float32(tspan[0]), np.float32(tspan[1])
+    out = []
+    for _ in range(n):
+        s = (s + 0x9E3779B97F4A7C15) & m64
+        z = s
+        z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & m64
+        z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & m64
+        z ^= z >> 31
+        u = (z >> 40) / 16777216.0
+        r = np.float32((2.0 * u - 1.0) * float(np.float32(steer_rate)))
+        # fmaf(|t1 - t0|, r, t1): one rounding
+        out.append(float(np.float32(float(np.float32(abs(t1 - t0))) * float(r) + float(t1))))
+    return out
 
 
 def _split(args, cond, what):

@@ -130,7 +130,7 @@ extern "C" int32_t cnfb200_destroy(cnf_handle* h) {
     free_workspaces(h);
     narrow_free(h);
     ntc_free(h);
-    cnf_p2p_free(h);
+    cnf_nccl_destroy(h);
     tc_free(h);
     cudaFree(h->d_io);
     cudaFree(h->d_theta); cudaFree(h->d_wt); cudaFree(h->d_grad);
@@ -264,6 +264,7 @@ extern "C" int32_t cnfb200_set_option(cnf_handle* h, const char* key, int64_t va
     if (!strcmp(key, "vector_mode")) { h->vector_mode = value != 0; return CNF_OK; }
     if (!strcmp(key, "tc_dbg")) { h->tc_dbg = (int)value; return CNF_OK; }
     if (!strcmp(key, "tc_ring")) { h->tc_noring = value == 0; return CNF_OK; }
+    if (!strcmp(key, "fused")) { h->fused_off = value == 0; return CNF_OK; }
     if (!strcmp(key, "tc_backward")) { h->tc_bw_off = value == 0; return CNF_OK; }
     if (!strcmp(key, "wg_lbo")) { h->wg_lbo = value; return CNF_OK; }
     if (!strcmp(key, "wg_sbo")) { h->wg_sbo = value; return CNF_OK; }
@@ -272,17 +273,31 @@ extern "C" int32_t cnfb200_set_option(cnf_handle* h, const char* key, int64_t va
 }
 
 // ------------------------------------------------------------------ workspaces
-static int ensure_slots(cnf_handle* h, size_t want) {
+// grows the slot table towards `want` entries; `need` (<= want) is what the caller cannot do without: running
+// short of memory between the two is not an error (the look-ahead just stops)
+static int ensure_slots(cnf_handle* h, size_t want, size_t need = 0) {
     if (want > CNF_MAX_SLOTS) want = CNF_MAX_SLOTS;
+    if (need == 0 || need > want) need = want;
     if (h->slots.size() >= want) return CNF_OK;
     size_t old = h->slots.size();
+    const size_t bytes = (size_t)h->slot_elems * sizeof(float);
     while (h->slots.size() < want) {
+        // keep 1/32 of the device free (the tape entries stop earlier, at 1/4): an out-of-memory here is reported
+        // as CNF_ERR_OOM before any kernel of the attempt is enqueued
+        size_t fr = 0, tot = 0;
+        const bool tight = h->slots.size() >= 2 && cudaMemGetInfo(&fr, &tot) == cudaSuccess && fr < bytes + tot / 32;
         float* p = nullptr;
-        CNF_CUDA(cudaMalloc(&p, h->slot_elems * sizeof(float)));
+        if (tight || cudaMalloc(&p, bytes) != cudaSuccess) {
+            cudaGetLastError();
+            if (h->slots.size() >= need) break;
+            h->err = "state slots of the step tape do not fit the device memory (shard the batch over more GPUs)";
+            return CNF_ERR_OOM;
+        }
         h->slots.push_back(p);
     }
-    CNF_CUDA(cudaMemcpyAsync(h->d_slots + old, h->slots.data() + old,
-                             (h->slots.size() - old) * sizeof(float*), cudaMemcpyHostToDevice, h->stream));
+    if (h->slots.size() > old)
+        CNF_CUDA(cudaMemcpyAsync(h->d_slots + old, h->slots.data() + old,
+                                 (h->slots.size() - old) * sizeof(float*), cudaMemcpyHostToDevice, h->stream));
     return CNF_OK;
 }
 
@@ -470,7 +485,7 @@ static int solve_device(cnf_handle* h, const CnfBufs& bf, int mode, int R, long 
     long long launched = 0;
     int pend = -1;  // index of the pinned snapshot in flight
     for (;;) {
-        if (use_tape && (long long)h->slots.size() < launched + 2 && (rc = ensure_slots(h, (size_t)(launched + 10)))) return rc;
+        if (use_tape && (long long)h->slots.size() < launched + 2 && (rc = ensure_slots(h, (size_t)(launched + 10), (size_t)(launched + 2)))) return rc;
         if (use_tape && (long long)h->ktape.size() < launched + 2 &&
             (rc = ensure_ktape(h, (size_t)(launched + 10), (long long)c.D * bf.Bs))) return rc;
         if ((rc = enqueue_attempt(h, bf, mode))) return rc;
@@ -572,14 +587,20 @@ static int check_call(cnf_handle* h, int mode, long long B) {
 static long long global_batch(cnf_handle* h, long long B, int* rc) {
     *rc = CNF_OK;
     if (h->nranks <= 1) return B;
-    double* d = &h->d_ctrl->initsum[3];
-    double v = (double)B;
-    cudaMemcpyAsync(d, &v, sizeof(double), cudaMemcpyHostToDevice, h->stream);
+    if (h->bglobal_B == B && h->bglobal > 0) return h->bglobal;   // same shard size as the last call on this communicator
+    // sum of B and of B^2 over the ranks: n * sum(B^2) == sum(B)^2 iff every rank holds the same B, and only then
+    // may every rank skip the exchange next time (all ranks must take the cached branch together)
+    double* d = &h->d_ctrl->initsum[2];
+    double v[2] = {(double)B, (double)B * (double)B};
+    cudaMemcpyAsync(d, v, 2 * sizeof(double), cudaMemcpyHostToDevice, h->stream);
     cudaStreamSynchronize(h->stream);
-    *rc = cnf_nccl_allreduce_f64(h, d, 1);
-    cudaMemcpyAsync(&v, d, sizeof(double), cudaMemcpyDeviceToHost, h->stream);
+    *rc = cnf_nccl_allreduce_f64(h, d, 2);
+    cudaMemcpyAsync(v, d, 2 * sizeof(double), cudaMemcpyDeviceToHost, h->stream);
     cudaStreamSynchronize(h->stream);
-    return (long long)(v + 0.5);
+    const bool uniform = (double)h->nranks * v[1] == v[0] * v[0];
+    h->bglobal_B = uniform ? B : -1;
+    h->bglobal = (long long)(v[0] + 0.5);
+    return h->bglobal;
 }
 
 extern "C" int32_t cnfb200_augmented_f(cnf_handle* h, int32_t mode, const float* u, const float* ys,
@@ -625,10 +646,10 @@ static int run_flow(cnf_handle* h, int mode, const float* x, int rows_x, const f
     if ((rc = ensure_workspace(h, B, R))) return rc;
     IoPlan io = plan_io(c, B, rows_x);
     if ((rc = ensure_io(h, io.total))) return rc;
+    CNF_CUDA(cudaEventRecord(h->ev0, h->stream));   // the device time of the call covers the batch-size exchange
     long long Bglobal = global_batch(h, B, &rc);
     if (rc) return rc;
     CnfBufs bf = make_bufs(h, B);
-    CNF_CUDA(cudaEventRecord(h->ev0, h->stream));
     if ((rc = load_problem(h, bf, io, mode, R, x, rows_x, ys, eps, B))) return rc;
     h->path_used = 1;
     CnfCtrl fin;
@@ -764,9 +785,9 @@ extern "C" int32_t cnfb200_loss_grad_mode(cnf_handle* h, int32_t mode, const flo
     if ((rc = ensure_io(h, io.total))) return rc;
     CnfBufs bf = make_bufs(h, B);
     if (want_grad && (rc = ensure_bw(h, bf.Bs))) return rc;
+    CNF_CUDA(cudaEventRecord(h->ev0, h->stream));
     long long Bglobal = global_batch(h, B, &rc);
     if (rc) return rc;
-    CNF_CUDA(cudaEventRecord(h->ev0, h->stream));
     if ((rc = load_problem(h, bf, io, mode, R, xs, c.nvars, ys, eps, B))) return rc;
     CnfCtrl fin;
     if ((rc = loss_grad_core(h, bf, mode, R, Bglobal, t0, t1, want_grad, &fin))) return rc;

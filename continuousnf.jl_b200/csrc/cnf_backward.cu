@@ -286,7 +286,8 @@ template <int TB>
 static void launch_vjp_tb(cnf_handle* h, const CnfBufs& bf, const BwLayout& lay, int smem,
                           const float* src, const float* abar, int stage, const float* dtp,
                           float c_l, float c_E, float c_n, float* ubar, float** kb, float* grad, int unit) {
-    static bool attr_set = false;
+    static bool attr_dev[64] = {};   // per device
+    bool& attr_set = attr_dev[h->device & 63];
     if (!attr_set) {
         cudaFuncSetAttribute(k_vjp_generic<TB>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         attr_set = true;

@@ -203,7 +203,8 @@ static int tc_ensure_bw(cnf_handle* h, TcState* s) {
     }
     if ((rc = tc_alloc_f32(h, s->Y, s->Mc, pad_to(c.D, TC_BK)))) return rc;
     if ((rc = tc_alloc_f32(h, s->YB, s->Mc, pad_to(c.D, TC_BK)))) return rc;
-    static bool attr = false;
+    static bool attr_dev[64] = {};   // per device
+    bool& attr = attr_dev[h->device & 63];
     if (!attr) {
         CNF_CUDA(cudaFuncSetAttribute(k_tc_wgrad, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr = true;

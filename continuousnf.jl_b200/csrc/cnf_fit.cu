@@ -53,6 +53,12 @@ static uint64_t splitmix64(uint64_t& s) {
     return z ^ (z >> 31);
 }
 
+extern "C" int32_t cnfb200_set_steer(cnf_handle* h, float steer_rate) {
+    if (!h || !(steer_rate >= 0.0f)) return CNF_ERR_BADARG;
+    h->steer_rate = steer_rate;
+    return CNF_OK;
+}
+
 extern "C" int32_t cnfb200_fit_epochs(cnf_handle* h, const float* X, const float* Y, int64_t N, int64_t batch_size,
                                       int32_t n_epochs, const int64_t* perm, float t0, float t1, float eta, float beta1,
                                       float beta2, float* theta_out, float* loss_history, cnf_stats* stats) {
@@ -113,6 +119,7 @@ extern "C" int32_t cnfb200_fit_epochs(cnf_handle* h, const float* X, const float
 
     std::vector<long long> idx((size_t)N);
     uint64_t sm = h->rng_seed ^ 0x5DEECE66Dull;
+    uint64_t steer_state = h->rng_seed ^ 0xA5A5A5A55A5A5A5Aull;   // the steer stream (cnfb200_set_steer)
     CnfCtrl fin;
     memset(&fin, 0, sizeof(fin));
     int worst = CNF_OK;
@@ -147,7 +154,15 @@ extern "C" int32_t cnfb200_fit_epochs(cnf_handle* h, const float* X, const float
                                                                                                       h->d_ys, bf.Bs);
             launch_philox_normal(h, h->d_eps, bf.Bs, B, c.D, h->rng_draws++);
             h->eps_B = B;
-            if ((rc = loss_grad_core(h, bf, mode, R, Bglobal, t0, t1, true, &fin))) { cleanup(); return rc; }
+            // steer_tspan (src/base_icnf.jl:108-121) runs inside every TrainMode loss call of the reference's fit, so t1 is
+            // re-drawn per mini-batch: t1' = muladd(|t1 - t0|, r, t1), r ~ U(-steer_rate, steer_rate)
+            float t1b = t1;
+            if (h->steer_rate != 0.0f) {
+                const double u = (double)(splitmix64(steer_state) >> 40) * (1.0 / 16777216.0);
+                const float r = (float)((2.0 * u - 1.0) * (double)h->steer_rate);
+                t1b = fmaf(fabsf(t1 - t0), r, t1);
+            }
+            if ((rc = loss_grad_core(h, bf, mode, R, Bglobal, t0, t1b, true, &fin))) { cleanup(); return rc; }
             if (fin.retcode != CNF_OK) worst = fin.retcode;
             k_fit_acc<<<1, 1, 0, h->stream>>>(h->d_lossacc, dHist, e);
             k_lion_step<<<(unsigned)((h->nparams + threads - 1) / threads), threads, 0, h->stream>>>(h->d_theta, dM, h->d_grad,

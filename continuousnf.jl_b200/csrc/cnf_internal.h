@@ -37,6 +37,7 @@ struct cnf_handle {
     bool vector_mode = false;    // N4: per-sample step control (cnf_vector.cu)
     bool rng_on = false;
     unsigned long long rng_seed = 0, rng_offset = 0;
+    float steer_rate = 0.0f;     // cnfb200_set_steer: fit_epochs re-draws t1 per mini-batch (src/base_icnf.jl:108-121)
     uint32_t rng_draws = 0;      // draws made so far (the next draw's index)
     long long eps_B = 0;         // batch of the eps now in d_eps (cnfb200_last_eps)
     float* d_ys = nullptr;
@@ -55,6 +56,7 @@ struct cnf_handle {
     // communicator (NCCL via dlopen)
     void* nccl_comm = nullptr;
     int nranks = 1, rank = 0;
+    long long bglobal_B = -1, bglobal = 0;   // cached global batch (sum of the ranks' B) for local batch bglobal_B
     // error-norm exchange over NVLink peer memory (cnf_nccl.cu): every rank owns a mailbox of
     // [2 parities][nranks] slots that its peers write into; the controller kernel does the exchange itself
     CnfXSlot* d_xslots = nullptr;
@@ -74,6 +76,7 @@ struct cnf_handle {
     int tc_dbg = 0;
     int tc_mode = CNF_MODE_TRAIN;   // mode of the solve tc_eval serves: TrainMode Hutchinson rows, or TestMode exact trace
     bool tc_noring = false;     // option "tc_ring" = 0: epilogue operands through registers instead of the shared-memory ring
+    bool fused_off = false;     // option "fused" = 0: never use the fused multi-layer kernel (cnf_stage_fused.cu)
     bool tc_bw_off = false;     // option "tc_backward" = 0: reverse sweep on the generic SIMT kernels
     long long wg_lbo = 0, wg_sbo = 0;   // debug override of the MN-major descriptor strides (0 = default)
     void* narrow_w = nullptr;   // host copy of the packed kernel-parameter weights (narrow path)
@@ -141,6 +144,10 @@ void tc_free(cnf_handle* h);
 int tc_eval(cnf_handle* h, const CnfBufs& bf, const float* src, int kidx, float* kout_fixed, int check_done);
 int tc_eval_z(cnf_handle* h, const CnfBufs& bf, const float* src, float* kout);   // zdot rows only (BF16x3)
 
+// ---- cnf_stage_fused.cu : all layer products of a 128-sample tile chained on chip (hidden width 128)
+bool fused_supported(const cnf_handle* h, int mode);
+int fused_eval(cnf_handle* h, const CnfBufs& bf, const float* src, int kidx, float* kout_fixed, int check_done);
+
 // ---- cnf_backward_tc.cu : reverse sweep on the tensor path (VecJac)
 bool tc_bw_supported(cnf_handle* h);
 int tc_vjp_stage(cnf_handle* h, const CnfBufs& bf, const float* src, const float* abar, int stage,
@@ -148,5 +155,6 @@ int tc_vjp_stage(cnf_handle* h, const CnfBufs& bf, const float* src, const float
 
 // ---- cnf_nccl.cu
 void cnf_p2p_free(cnf_handle* h);
+void cnf_nccl_destroy(cnf_handle* h);
 int cnf_nccl_allreduce_f64(cnf_handle* h, double* dptr, int n);
 int cnf_nccl_allreduce_f32(cnf_handle* h, float* dptr, long long n);

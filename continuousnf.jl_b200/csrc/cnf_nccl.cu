@@ -138,6 +138,7 @@ extern "C" int32_t cnfb200_comm_init(cnf_handle* h, int32_t nranks, int32_t rank
     }
     h->nranks = nranks;
     h->rank = rank;
+    h->bglobal_B = -1;
     return cnf_p2p_setup(h);
 }
 

@@ -251,7 +251,8 @@ static int pick_tb(int total_floats_per_tbp /*rows*/, int* smem_bytes) {
 template <int TB>
 static int launch_eval_tb(cnf_handle* h, const CnfBufs& bf, const GenLayout& lay, int smem, int mode,
                           int src_sel, const float* src_ptr, int kidx, float* kout_ptr, int check_done) {
-    static bool attr_set = false;
+    static bool attr_dev[64] = {};   // the opt-in is per device: handles may live on different GPUs of one process
+    bool& attr_set = attr_dev[h->device & 63];
     if (!attr_set) {
         cudaFuncSetAttribute(k_eval_generic<TB>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         attr_set = true;

@@ -933,7 +933,8 @@ static void tc_launch_kind(cnf_handle* h, int grid, int smem, const TcMaps& mp, 
     constexpr bool valid = (BWD ? (KIND >= TCB_FWD_LAST && PREC == 1) : (KIND <= TC_JVP_LAST && (PREC == 0 || KIND == TC_FWD_HIDDEN))) &&
                            (!RING || TcRingOf<BWD, KIND>::kind);
     if constexpr (valid) {
-        static bool attr = false;
+        static bool attr_dev[64] = {};   // per device
+        bool& attr = attr_dev[h->device & 63];
         if (!attr) {
             cudaFuncSetAttribute(k_tc_gemm<PREC, BWD, KIND, RING>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
             attr = true;
@@ -1055,6 +1056,7 @@ int tc_eval(cnf_handle* h, const CnfBufs& bf, const float* src, int kidx, float*
     if (!s || !s->weights_ok) { h->err = "tensor path: parameters not set"; return CNF_ERR_UNSUPPORTED; }
     const cnf_config& c = h->cfg;
     int rc;
+    if (fused_supported(h, h->tc_mode)) return fused_eval(h, bf, src, kidx, kout_fixed, check_done);
     if ((rc = tc_ensure_acts(h, s, bf.Bs))) return rc;
     const int L = c.n_layers;
     const bool test = h->tc_mode == CNF_MODE_TEST;

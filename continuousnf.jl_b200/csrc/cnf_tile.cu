@@ -182,7 +182,7 @@ int tile_solve(cnf_handle* h, const CnfBufs& bf, int mode, bool use_tape, long l
         long long nz = (long long)h->cfg.D * bf.Bs, kcap = (long long)h->ktape.size(), scap = (long long)h->slots.size();
         void* args[] = {&dc, &b, &net, &lay, &md, &dts, &kt, &nz, &kcap, &scap, &chunk};
         bool ok = false;
-        static bool attr[2][33] = {};
+        bool attr[2][33] = {};   // (set on every call: the attribute is per device and the call is cheap)
         TILE_DISPATCH(tbv,
             { if (!attr[0][TB]) { cudaFuncSetAttribute(k_solve_tile<TB, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TILE_SMEM_MAX); attr[0][TB] = true; }
               ok = tile_launch(h, k_solve_tile<TB, false>, 1, smem, args); },
@@ -236,7 +236,7 @@ bool tile_sweep(cnf_handle* h, const CnfBufs& bf, int mode, long long naccept, l
     CnfNet net = h->net;
     void* args[] = {&b, &net, &lay, &sa};
     bool ok = false;
-    static bool attr[2][33] = {};
+    bool attr[2][33] = {};   // (set on every call: the attribute is per device and the call is cheap)
     TILE_DISPATCH(tbv,
         { if (!attr[0][TB]) { cudaFuncSetAttribute(k_sweep_tile<TB, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TILE_SMEM_MAX); attr[0][TB] = true; }
           ok = tile_launch(h, k_sweep_tile<TB, false>, 1, smem, args); },

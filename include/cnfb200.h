@@ -180,6 +180,13 @@ CNF_API int32_t cnfb200_last_eps(cnf_handle* h, float* eps_out, int64_t B);
  * (may be NULL; the handle keeps the fitted theta either way); loss_history: n_epochs per-epoch means
  * of the mini-batch losses weighted by their sizes.  With several ranks every rank passes its own
  * shard (same number of mini-batches per epoch on every rank). */
+/* steer_tspan inside the fit loop (src/base_icnf.jl:108-121: every TrainMode loss call of the reference's fit re-draws
+ * t1' = muladd(|t1 - t0|, r, t1), r ~ Uniform(-steer_rate, steer_rate)).  The single-call entry points take the steered
+ * (t0, t1) from the caller, who draws r from icnf.rng like the reference; cnfb200_fit_epochs runs many loss calls, so it
+ * draws r itself, once per mini-batch, from a host stream: state = seed (of cnfb200_seed_rng) ^ 0xA5A5A5A55A5A5A5A,
+ * u_k = (splitmix64(state) >> 40) * 2^-24, r_k = (2 u_k - 1) * steer_rate.  steer_rate = 0 (default) keeps t1 fixed. */
+CNF_API int32_t cnfb200_set_steer(cnf_handle* h, float steer_rate);
+
 CNF_API int32_t cnfb200_fit_epochs(cnf_handle* h, const float* X, const float* Y, int64_t N, int64_t batch_size,
                            int32_t n_epochs, const int64_t* perm, float t0, float t1, float eta, float beta1,
                            float beta2, float* theta_out, float* loss_history, cnf_stats* stats);

@@ -853,6 +853,15 @@ int32_t cnf_oracle_num_threads(void) {
 #endif
 }
 
+/* torchrun exports OMP_NUM_THREADS=1 to every rank; the timed CPU legs of bench.py ask for all host cores explicitly */
+void cnf_oracle_set_num_threads(int32_t n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 /* ---- "next" row N1: the generator behind cnfb200_seed_rng, restated on the CPU.
  * Philox4x32-10 (Salmon, Moraes, Dror, Shaw: "Parallel random numbers: as easy as 1, 2, 3", SC'11;
  * the Random123 known-answer vectors pin it in tests/test_oracle.py), counter =

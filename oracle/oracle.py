@@ -201,6 +201,13 @@ def num_threads():
     return int(lib().cnf_oracle_num_threads())
 
 
+def set_num_threads(n=None):
+    """use `n` OpenMP threads (default: every host core; torchrun pins OMP_NUM_THREADS=1)"""
+    n = (os.cpu_count() or 1) if n is None else int(n)
+    lib().cnf_oracle_set_num_threads(C.c_int32(n))
+    return num_threads()
+
+
 def last_dts():
     """accepted dt sequence of the most recent oracle solve in this process"""
     buf = np.zeros(4096, np.float32)

@@ -313,7 +313,7 @@ def test_n1_generate_draws_base_sample_on_device():
     np.testing.assert_allclose(xs, xs2, rtol=1e-4, atol=1e-4)   # z0 agrees to 3e-6; the flow amplifies it
 
 
-def _oracle_fit(cid, inp, N, bs, n_epochs, perm, seed, eta, beta):
+def _oracle_fit(cid, inp, N, bs, n_epochs, perm, seed, eta, beta, t1s=None):
     """the reference's fit loop restated on the host with the oracle's loss gradient, the oracle's
     Philox eps stream (one draw per mini-batch) and Lion (tests only)"""
     cfg, c = oracle_cfg(cid), wl.CONFIGS[cid]
@@ -328,7 +328,8 @@ def _oracle_fit(cid, inp, N, bs, n_epochs, perm, seed, eta, beta):
             eps = O.philox_normal(seed, 0, draw, D, len(idx)).T.copy()
             draw += 1
             ys = inp["ys"][idx] if inp["ys"] is not None else None
-            val, g, _, _ = O.loss_grad(cfg, ps, inp["xs"][idx], ys, eps, *c["tspan"])
+            t1 = c["tspan"][1] if t1s is None else t1s[draw - 1]
+            val, g, _, _ = O.loss_grad(cfg, ps, inp["xs"][idx], ys, eps, c["tspan"][0], t1)
             cc = beta[0] * m + (1 - beta[0]) * g
             ps = (ps - eta * np.sign(cc)).astype(np.float32)
             m = (beta[1] * m + (1 - beta[1]) * g).astype(np.float32)
@@ -358,6 +359,38 @@ def test_n2_fit_epochs_device_loop_vs_oracle_loop(cid, N, bs, n_epochs):
     assert (d > 1e-6).mean() < 0.03, (d > 1e-6).mean()
     # the fitted parameters stay in the handle: a loss call without re-uploading sees them
     assert not np.array_equal(ps, inp["theta"])
+
+
+def test_n2_fit_epochs_steers_t1_per_minibatch():
+    """the reference draws the steered t1 inside every TrainMode loss call of its fit
+    (src/base_icnf.jl:108-121, :283), so with steer_rate > 0 every mini-batch integrates to its own t1.
+    The device loop draws t1 per mini-batch from the documented stream (cnf.steer_sequence); the same loop
+    on the host with the oracle and those t1 values must agree, and the t1 values must really differ."""
+    cid, N, bs, n_epochs = "C1", 300, 128, 2
+    inp = wl.make_inputs(cid, B=N)
+    eta, beta, seed, rate = 1e-3, (0.9, 0.999), 4242, 0.1
+    perm = np.stack([np.random.default_rng(9 + e).permutation(N) for e in range(n_epochs)])
+    icnf = make_icnf(cid)
+    icnf.steer_rate = rate
+    cnf.seed_device_rng(icnf, seed)
+    ps, hist = cnf.fit_epochs(icnf, inp["xs"].T, None, inp["theta"], batch_size=bs, n_epochs=n_epochs, perm=perm,
+                              eta=eta, beta=beta)
+    steps = n_epochs * -(-N // bs)
+    t1s = cnf.steer_sequence(seed, steps, rate, wl.CONFIGS[cid]["tspan"])
+    t0, t1 = wl.CONFIGS[cid]["tspan"]
+    assert len(set(t1s)) == steps and all(abs(t - t1) <= rate * abs(t1 - t0) * 1.0001 for t in t1s)
+    assert abs(cnf.last_stats(icnf)["t_final"] - t1s[-1]) < 1e-6      # the last mini-batch stopped at ITS t1
+    rps, rhist = _oracle_fit(cid, inp, N, bs, n_epochs, perm, seed, eta, beta, t1s=t1s)
+    np.testing.assert_allclose(hist, rhist, rtol=2e-4)
+    d = np.abs(ps - rps)
+    assert d.max() <= 2 * eta * steps + 1e-6
+    assert (d > 1e-6).mean() < 0.03, (d > 1e-6).mean()
+    # and an unsteered fit of the same data gives a different history
+    plain = make_icnf(cid)
+    cnf.seed_device_rng(plain, seed)
+    _, hist0 = cnf.fit_epochs(plain, inp["xs"].T, None, inp["theta"], batch_size=bs, n_epochs=n_epochs, perm=perm,
+                              eta=eta, beta=beta)
+    assert np.max(np.abs(hist0 - hist)) > 1e-6
 
 
 def test_n2_adapter_fit_uses_device_loop_and_matches_per_batch_calls():
