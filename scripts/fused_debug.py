@@ -45,3 +45,27 @@ for fused in (0, 1):
         lp0 = np.asarray(lp).copy()
     else:
         print("  max rel logp diff fused vs per-layer:", float(np.max(np.abs(np.asarray(lp) - lp0) / np.abs(lp0))))
+
+# timing experiments (wrong results by design for dbg != 0)
+if len(sys.argv) > 4:
+    Bt = 1 << 20
+    big = wl.make_inputs(cid, B=Bt)
+    for dbg in [int(x) for x in sys.argv[4].split(",")]:
+        icnf = make_icnf(cid)
+        cnf.set_option(icnf, "time_stages", 1)
+        cnf.set_option(icnf, "tc_dbg", dbg)
+        try:
+            for _ in range(2):
+                cnf.inference(icnf, cnf.TrainMode(), big["xs"].T, *args_of(big), eps=big["eps"].T)
+            st = cnf.last_stats(icnf)
+            print(f"dbg={dbg}: B={Bt} nf={st['nf']} retcode={st['retcode']} stage_ms={st['ms_stage'] / max(st['n_stage'], 1):.4f}", flush=True)
+        except Exception as e:
+            print(f"dbg={dbg}: {e}")
+
+if len(sys.argv) > 5:   # phase trace of CTA 0 (tc_dbg & 16): one evaluation
+    icnf = make_icnf(cid)
+    cnf.set_option(icnf, "tc_dbg", 16)
+    Bt = 1 << 20
+    big = wl.make_inputs(cid, B=Bt)
+    uu = np.zeros((Bt, R), np.float32); uu[:, :big["xs"].shape[1]] = big["xs"]
+    cnf.augmented_f(icnf, cnf.TrainMode(), uu.T, *args_of(big), eps=big["eps"].T)

@@ -31,13 +31,19 @@ def test_augmented_f(cid, B, trace_mode, mode):
     assert np.max(np.abs(du - ref) / scale) < tol
 
 
-@pytest.mark.parametrize("cid,B", SMALL)
-@pytest.mark.parametrize("trace_mode", [0, 1])
-@pytest.mark.parametrize("mode", [0, 1])
-def test_logdensity(cid, B, trace_mode, mode):
-    inp = wl.make_inputs(cid, B=B)
+# ---- bookkeeping of the two documented widenings of north_star's tolerances ("What's weak" 2):
+# (a) the conditioning floor of the tspan = (0, 13) configs, (b) a +-1 difference of the accepted-step count.
+# Every case records what it actually used; test_zz_tolerance_report prints the table and bounds both.
+FLOORS = {}      # test id -> tolerance applied to the relative log-density / loss error
+FLIPS = {}       # test id -> True when the accepted-step counts differed by one
+FLOOR_MAX = 1e-3  # no case may need a floor above this
+FLIP_FRACTION_MAX = 0.25
+
+
+def _logdensity_case(name, cid, B, trace_mode, mode, inp=None, kernel_path=0):
+    inp = wl.make_inputs(cid, B=B) if inp is None else inp
     c = wl.CONFIGS[cid]
-    icnf = make_icnf(cid, trace_mode=trace_mode)
+    icnf = make_icnf(cid, trace_mode=trace_mode, kernel_path=kernel_path)
     m = cnf.TrainMode() if mode else cnf.TestMode()
     lp, regs, z = cnf.inference(icnf, m, inp["xs"].T, *args_of(inp), eps=inp["eps"].T, return_z=True)
     st = cnf.last_stats(icnf)
@@ -53,12 +59,48 @@ def test_logdensity(cid, B, trace_mode, mode):
     O.set_perturb(False)
     floor = 4 * relerr(plp, rlp) if pst["naccept"] == rst["naccept"] else 0.0
     tol = max(1e-4, floor)
+    FLIPS[name] = st["naccept"] != rst["naccept"]
+    err = relerr(lp, rlp)
     if st["naccept"] == rst["naccept"]:
-        assert relerr(lp, rlp) < tol
+        FLOORS[name] = tol
+        print(f"{name}: max rel logp err {err:.2e}, tolerance applied {tol:.2e} (floor {floor:.2e}), naccept {st['naccept']}")
+        assert tol <= FLOOR_MAX, (name, tol)
+        assert err < tol
         assert relnorm(np.asarray(z).T, rz) < tol
         assert np.allclose(np.stack(regs, 1), rregs, rtol=1e-4, atol=1e-5)
     else:  # a borderline accept/reject flip: both are valid solves, compare at solver tolerance
-        assert relerr(lp, rlp) < 5e-3
+        print(f"{name}: accepted steps {st['naccept']} vs oracle {rst['naccept']}: max rel logp err {err:.2e} (bound 5e-3)")
+        assert err < 5e-3
+    return st
+
+
+@pytest.mark.parametrize("cid,B", SMALL)
+@pytest.mark.parametrize("trace_mode", [0, 1])
+@pytest.mark.parametrize("mode", [0, 1])
+def test_logdensity(cid, B, trace_mode, mode):
+    _logdensity_case(f"logdensity[{cid},B={B},tm={trace_mode},mode={mode}]", cid, B, trace_mode, mode)
+
+
+def test_logdensity_c2_at_the_benchmarked_size():
+    """C2 at B = 2^20, the size bench.py times: ntiles >> grid, the persistent tile loop of k_stage_narrow_tc and the
+    whole-batch RMS norm over 3 x 2^20 entries against the oracle's solve of the same batch"""
+    st = _logdensity_case("logdensity[C2,B=2^20]", "C2", 1 << 20, 1, 0)
+    assert st["kernel_path"] == 6
+
+
+def test_logdensity_c5_shape():
+    """C5 (128 -> 1024 -> 1024 -> 128, tensor-bound layer GEMMs): per-sample log-density, not only loss/gradient"""
+    st = _logdensity_case("logdensity[C5,B=256]", "C5", 256, 0, 1)
+    assert st["kernel_path"] == 3
+
+
+def test_logdensity_c4_hutchinson_large():
+    """C4 Hutchinson inference at 2^16 samples on the fused multi-layer kernel (one 128-sample tile per CTA pass, many
+    passes per CTA); the full 2^20 of BASELINE.json's config runs with CNFB200_SLOW=1 (the oracle needs minutes)"""
+    import os
+    B = (1 << 20) if os.environ.get("CNFB200_SLOW") == "1" else (1 << 16)
+    st = _logdensity_case(f"logdensity[C4,B={B},hutchinson]", "C4", B, 0, 1)
+    assert st["kernel_path"] == 7
 
 
 @pytest.mark.parametrize("cid,B", [("C0", 64), ("C1", 1024), ("C3", 256), ("C4", 1024), ("C5", 64)])
@@ -83,6 +125,13 @@ def test_loss_grad(cid, B, trace_mode):
     fl_l = 4 * abs(pval - rval) / abs(rval) if same else 0.0
     fl_g = 4 * relnorm(pg, rg) if same else 0.0
     tol_l, tol_g = (max(1e-4, fl_l), max(1e-3, fl_g)) if st["naccept"] == rst["naccept"] else (5e-3, 5e-2)
+    name = f"loss_grad[{cid},B={B},tm={trace_mode}]"
+    FLIPS[name] = st["naccept"] != rst["naccept"]
+    if not FLIPS[name]:
+        FLOORS[name] = tol_l
+        assert tol_l <= FLOOR_MAX and tol_g <= 10 * FLOOR_MAX, (name, tol_l, tol_g)
+    print(f"{name}: loss rel err {abs(val - rval) / abs(rval):.2e} (tol {tol_l:.1e}), grad rel err {relnorm(g, rg):.2e} "
+          f"(tol {tol_g:.1e}), naccept {st['naccept']} vs {rst['naccept']}")
     assert abs(val - rval) / abs(rval) < tol_l
     assert relnorm(g, rg) < tol_g
     assert relnorm(np.asarray(gx).T, rgx) < tol_g
@@ -585,3 +634,17 @@ def test_tensor_path_exact_trace_testmode(cid, B, trace_mode):
     assert abs(out[0][1] - rst["naccept"]) <= 1 and abs(out[0][1] - out[1][1]) <= 1
     if out[0][1] == rst["naccept"]:
         assert relerr(out[0][0], rlp) < 1e-4
+
+
+def test_zz_tolerance_report():
+    """runs last in this file: the tolerance every parity case above actually used.  north_star asks for 1e-4 / 1e-4 /
+    1e-3 AND steps +-1; the two documented widenings (conditioning floor on the tspan = (0, 13) configs; solver-level
+    comparison when the step counts differ by one) are bounded here instead of being silent."""
+    if not FLIPS:
+        pytest.skip("no parity case ran in this session")
+    widened = {k: v for k, v in FLOORS.items() if v > 1e-4}
+    flips = [k for k, v in FLIPS.items() if v]
+    print(f"{len(FLIPS)} parity cases; tolerance floor above 1e-4 in {len(widened)}: {widened}")
+    print(f"accepted-step count differed by one in {len(flips)}: {flips}")
+    assert all(v <= FLOOR_MAX for v in FLOORS.values())
+    assert len(flips) <= FLIP_FRACTION_MAX * len(FLIPS), flips
