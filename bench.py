@@ -39,8 +39,9 @@ METRIC = {"test": ("logdensity_samples_per_s", "samples/s"),
           "train": ("rnode_train_samples_per_s", "samples/s")}
 # north_star tolerances
 TOL_LOGP, TOL_LOSS, TOL_GRAD = 1e-4, 1e-4, 1e-3
-# accepted-step counts may differ by one (north_star); the two solves then differ at solver tolerance
-TOL_FLIP_LOGP, TOL_FLIP_LOSS, TOL_FLIP_GRAD = 5e-3, 5e-3, 5e-2
+# accepted-step counts may differ by one (north_star); the SAME value tolerances apply then (measured: the two solves
+# still agree to ~1e-6)
+TOL_FLIP_LOGP, TOL_FLIP_LOSS, TOL_FLIP_GRAD = TOL_LOGP, TOL_LOSS, TOL_GRAD
 
 
 def parse():

@@ -1,6 +1,8 @@
 // cnf_api.cu — C-ABI entry points of libcnfb200.so (include/cnfb200.h) and the host-side
 // orchestration: the host only enqueues kernels and polls the device controller block.
 #include "cnf_internal.h"
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -507,6 +509,13 @@ static int solve_device(cnf_handle* h, const CnfBufs& bf, int mode, int R, long 
     CNF_CUDA(cudaStreamSynchronize(h->stream));
     *out = h->h_ctrl[0];
     CNF_CUDA(cudaGetLastError());
+    if (getenv("CNFB200_DEBUG_DTS")) {   // debug: the accepted step sizes of this solve
+        std::vector<float> dts((size_t)(out->naccept < CNF_MAX_SLOTS ? out->naccept : CNF_MAX_SLOTS));
+        cudaMemcpy(dts.data(), h->d_dts, dts.size() * sizeof(float), cudaMemcpyDeviceToHost);
+        fprintf(stderr, "cnfb200 dts (naccept %lld nreject %lld):", (long long)out->naccept, (long long)out->nreject);
+        for (float d : dts) fprintf(stderr, " %.7g", d);
+        fprintf(stderr, "\n");
+    }
     return CNF_OK;
 }
 
@@ -739,7 +748,7 @@ static int ensure_bw(cnf_handle* h, long long Bs) {
     const long long need = (long long)h->cfg.D * Bs;
     if (need <= h->cap_bw) return CNF_OK;
     CNF_CUDA(cudaStreamSynchronize(h->stream));
-    for (int j = 0; j < 13; ++j) {   // [12]: zbar scratch of the tensor-path reverse sweep
+    for (int j = 0; j < 15; ++j) {   // [12]: zbar scratch of the tensor-path reverse sweep; [13], [14]: one-hot eps / zero cotangent (exact trace)
         cudaFree(h->d_bw[j]);
         h->d_bw[j] = nullptr;
         CNF_CUDA(cudaMalloc(&h->d_bw[j], (size_t)need * sizeof(float)));

@@ -330,6 +330,13 @@ static unsigned bw_grid(long long n) {
     return (unsigned)(g < 1 ? 1 : g);
 }
 
+// eps = e_unit for every sample (exact-trace reverse sweep on the tensor path)
+__global__ void k_onehot_rows(float* __restrict__ e, long long Bs, int D, int unit) {
+    const long long n = (long long)D * Bs;
+    for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += (long long)gridDim.x * blockDim.x)
+        e[p] = (p / Bs == unit) ? 1.0f : 0.0f;
+}
+
 // reverse sweep over the accepted steps; d_bw: [0..4] stage inputs s_2..s_6, [5..10] kb_1..kb_6,
 // [11] ubar.  On return ubar holds d loss / d z(t0) and h->d_grad the parameter gradient.
 static int backward_sweep(cnf_handle* h, const CnfBufs& bf, int mode, long long naccept, long long Bglobal) {
@@ -344,6 +351,10 @@ static int backward_sweep(cnf_handle* h, const CnfBufs& bf, int mode, long long 
     int rc;
     if (tile_sweep(h, bf, mode, naccept, Bglobal)) return CNF_OK;   // one-tile batch: the whole sweep in one launch
     const bool tcb = train && tc_bw_supported(h);
+    // TestMode (exact trace) on wide nets: the D unit-vector VJPs on the tensor-core sweep as well (eps = e_unit in
+    // d_bw[13], zero zdot cotangent in d_bw[14] for unit > 0)
+    const bool tct = !train && tc_supported(c, CNF_MODE_TEST) && tc_bw_supported(h);
+    if (tct) CNF_CUDA(cudaMemsetAsync(w[14], 0, (size_t)nz * sizeof(float), h->stream));
     for (long long n = naccept - 1; n >= 0; --n) {
         const float* un = h->slots[n];
         const float* dtp = h->d_dts + n;
@@ -365,6 +376,14 @@ static int backward_sweep(cnf_handle* h, const CnfBufs& bf, int mode, long long 
             const float* src = (i == 0) ? un : w[i - 1];
             if (tcb) rc = tc_vjp_stage(h, bf, src, kb[i], i, dtp, c_l, c_E, c_n, ubar, kb, h->d_grad);
             else if (train) rc = launch_vjp_generic_stage(h, bf, src, kb[i], i, dtp, c_l, c_E, c_n, ubar, kb, h->d_grad);
+            else if (tct)
+                for (int unit = 0; unit < c.D && !rc; ++unit) {
+                    k_onehot_rows<<<bw_grid(nz), CNF_NT, 0, h->stream>>>(w[13], bf.Bs, c.D, unit);
+                    h->launches++;
+                    CnfBufs bu = bf;
+                    bu.eps = w[13];
+                    rc = tc_vjp_stage(h, bu, src, unit == 0 ? kb[i] : w[14], i, dtp, c_l, 0.0f, 0.0f, ubar, kb, h->d_grad);
+                }
             else   // exact trace: one Hutchinson-shaped VJP per unit vector (reference src/utils.jl:1-36 seeds)
                 for (int unit = 0; unit < c.D && !rc; ++unit)
                     rc = launch_vjp_generic_stage(h, bf, src, kb[i], i, dtp, c_l, 0.0f, 0.0f, ubar, kb, h->d_grad, unit);

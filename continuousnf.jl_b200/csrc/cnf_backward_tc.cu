@@ -187,8 +187,9 @@ __global__ void k_zbar_apply(const float* __restrict__ zbar, const float* __rest
 
 // ------------------------------------------------------------------ host side
 bool tc_bw_supported(cnf_handle* h) {
-    return tc_supported(h->cfg, CNF_MODE_TRAIN) && h->tc_state != nullptr && h->cfg.trace_mode == CNF_TRACE_VJP &&
-           !h->tc_bw_off;
+    // VecJac always; JacVec needs one more plane pair (QB[L + 1]), so L <= CNF_MAX_LAYERS - 1
+    return tc_supported(h->cfg, CNF_MODE_TRAIN) && h->tc_state != nullptr && !h->tc_bw_off &&
+           (h->cfg.trace_mode == CNF_TRACE_VJP || h->cfg.n_layers < CNF_MAX_LAYERS);
 }
 
 static int tc_ensure_bw(cnf_handle* h, TcState* s) {
@@ -203,6 +204,8 @@ static int tc_ensure_bw(cnf_handle* h, TcState* s) {
     }
     if ((rc = tc_alloc_f32(h, s->Y, s->Mc, pad_to(c.D, TC_BK)))) return rc;
     if ((rc = tc_alloc_f32(h, s->YB, s->Mc, pad_to(c.D, TC_BK)))) return rc;
+    // JacVec: sbar_l lives in QB[l + 1] (width of layer l), so sbar_L needs one more pair
+    if (c.trace_mode == CNF_TRACE_JVP && (rc = tc_alloc_plane(h, s->QB[L + 1], s->Mc, pad_to(c.dims[L], TC_BK), TC_BM))) return rc;
     static bool attr_dev[64] = {};   // per device
     bool& attr = attr_dev[h->device & 63];
     if (!attr) {
@@ -244,6 +247,84 @@ static void tc_launch_wgrad(cnf_handle* h, TcState* s, const TcPlane& A1, const 
     h->launches++;
 }
 
+// JacVec (reference src/icnf.jl:384-420 under the outer gradient): the Hutchinson term comes from the forward-mode chain
+//   tau_0 = [eps; 0], s_l = W_l tau_{l-1}, tau_l = s_l .* d_l (d_l = 1 - h_l^2);  ldot = -eps . tau_L, ndot = |tau_L|.
+// Reverse of one evaluation (cotangents abar of zdot, c_l / c_E / c_n of the quadrature rows, all scaled by dt a_7i):
+//   ybar = abar + beta y/|y|,  taubar_L = -alpha eps + gamma tau_L/|tau_L|
+//   l = L..1:  sbar_l = taubar_l .* d_l,  dbar_l = taubar_l .* s_l,  dW_l += sbar_l tau_{l-1}^T,  taubar_{l-1} = W_l^T sbar_l
+//   l = L..1:  abar_l = (hbar_l - 2 h_l dbar_l) .* d_l,  dW_l += abar_l h_{l-1}^T,  db_l += abar_l,  hbar_{l-1} = W_l^T abar_l
+// The same layer-GEMM kernels as the VecJac sweep with the roles of the two weight orientations exchanged: the tangent
+// chain runs on the forward planes (epilogue TCB_BWD_HIDDEN keeps s_l in fp32 and writes tau_l), its adjoint on the
+// transposed planes (TCB_GBAR_HIDDEN: dbar_l in place of s_l, sbar_l planes); only the last layer needs its own
+// epilogue (TCB_JVP_LAST).  Planes: tau_l in G[l] (G[0] = seed), sbar_l in QB[l + 1], abar_l in PB[l], s_l / dbar_l in Q[l].
+static int tc_vjp_stage_jvp(cnf_handle* h, TcState* s, const CnfBufs& bf, const float* src, TcEpi base, long long row0, int mc,
+                            float* grad) {
+    const cnf_config& c = h->cfg;
+    const int L = c.n_layers;
+    k_tc_prep<1><<<(mc + 255) / 256, 256, 0, h->stream>>>(h->d_ctrl, bf, src, c.D, bf.ys, c.C, row0, mc, s->H[0].p[0],
+                                                      s->H[0].p[1], s->H[0].ld, -1, nullptr, nullptr, 0);
+    k_tc_prep<1><<<(mc + 255) / 256, 256, 0, h->stream>>>(h->d_ctrl, bf, bf.eps, c.D, nullptr, 0, row0, mc, s->G[0].p[0],
+                                                      s->G[0].p[1], s->G[0].ld, 0, nullptr, nullptr, 0);
+    h->launches += 2;
+    tc_forward_hidden<1>(h, s, base, mc);
+    {   // y, ybar (the g_L planes this kind also writes are not used here)
+        TcEpi ep = base;
+        ep.kind = TCB_FWD_LAST;
+        ep.bias = h->d_theta + h->b_off[L - 1];
+        ep.N = c.D;
+        for (int q = 0; q < 2; ++q) ep.out[q] = s->G[L].p[q];
+        ep.ld_out = s->G[L].ld;
+        ep.f32a = s->Y.p; ep.f32b = s->YB.p; ep.ld_f = s->Y.ld;
+        tc_launch_gemm<1, true>(h, s, s->H[L - 1], s->wf[L - 1], mc, ep);
+    }
+    for (int l = 1; l <= L; ++l) {   // tangent chain: s_l = tau_{l-1} W_l^T
+        TcEpi ep = base;
+        if (l < L) {
+            ep.kind = TCB_BWD_HIDDEN;    // s_l kept in fp32 (Q[l]), tau_l = s_l (1 - h_l^2) planes (G[l])
+            ep.N = c.dims[l];
+            ep.aux_p = &s->H[l];
+            for (int q = 0; q < 2; ++q) { ep.hp[q] = s->H[l].p[q]; ep.out[q] = s->G[l].p[q]; }
+            ep.ld_h = s->H[l].ld; ep.ld_out = s->G[l].ld;
+            ep.f32a = s->Q[l].p; ep.ld_f = s->Q[l].ld;
+        } else {
+            ep.kind = TCB_JVP_LAST;
+            ep.N = c.D;
+            for (int q = 0; q < 2; ++q) { ep.out[q] = s->QB[L + 1].p[q]; ep.out2[q] = s->PB[L].p[q]; }
+            ep.ld_out = s->QB[L + 1].ld; ep.ld_out2 = s->PB[L].ld;
+            ep.f32a = s->Y.p; ep.f32b = s->YB.p; ep.ld_f = s->Y.ld;
+        }
+        tc_launch_gemm<1, true>(h, s, s->G[l - 1], s->wf[l - 1], mc, ep);
+    }
+    for (int l = L; l >= 2; --l) {   // adjoint of the tangent chain: taubar_{l-1} = sbar_l W_l
+        TcEpi ep = base;
+        ep.kind = TCB_GBAR_HIDDEN;       // dbar_{l-1} = taubar_{l-1} s_{l-1} (in place of s_{l-1}), sbar_{l-1} = taubar_{l-1} d_{l-1}
+        ep.N = c.dims[l - 1];
+        ep.aux_p = &s->H[l - 1]; ep.aux_f = &s->Q[l - 1];
+        for (int q = 0; q < 2; ++q) { ep.hp[q] = s->H[l - 1].p[q]; ep.out[q] = s->QB[l].p[q]; }
+        ep.ld_h = s->H[l - 1].ld; ep.ld_out = s->QB[l].ld;
+        ep.f32a = s->Q[l - 1].p; ep.ld_f = s->Q[l - 1].ld;
+        tc_launch_gemm<1, true>(h, s, s->QB[l + 1], s->wb[l - 1], mc, ep);
+    }
+    for (int l = L; l >= 1; --l) {   // adjoint of the forward chain: hbar_{l-1} = abar_l W_l; both weight-gradient terms of layer l
+        tc_launch_wgrad(h, s, s->PB[l], s->H[l - 1], &s->QB[l + 1], &s->G[l - 1], mc, c.dims[l], c.dims[l - 1],
+                        grad + h->w_off[l - 1], grad + h->b_off[l - 1]);
+        TcEpi ep = base;
+        if (l > 1) {
+            ep.kind = TCB_HBAR_HIDDEN;
+            ep.N = c.dims[l - 1];
+            ep.aux_p = &s->H[l - 1]; ep.aux_f = &s->Q[l - 1];
+            for (int q = 0; q < 2; ++q) { ep.hp[q] = s->H[l - 1].p[q]; ep.out[q] = s->PB[l - 1].p[q]; }
+            ep.ld_h = s->H[l - 1].ld; ep.ld_out = s->PB[l - 1].ld;
+            ep.f32a = s->Q[l - 1].p; ep.ld_f = s->Q[l - 1].ld;
+        } else {
+            ep.kind = TCB_ZBAR;
+            ep.N = c.D;
+        }
+        tc_launch_gemm<1, true>(h, s, s->PB[l], s->wb[l - 1], mc, ep);
+    }
+    return CNF_OK;
+}
+
 // VJP of TrainMode augmented_f at the stage input src against (abar; c_l, c_E, c_n):
 // ubar += zbar, kb[j<stage] += dt a_{stage,j} zbar, grad += parameter gradient.
 int tc_vjp_stage(cnf_handle* h, const CnfBufs& bf, const float* src, const float* abar, int stage,
@@ -261,6 +342,10 @@ int tc_vjp_stage(cnf_handle* h, const CnfBufs& bf, const float* src, const float
         base.abar = abar; base.ubar = h->d_bw[12]; base.dtp = dtp; base.stage = stage;   // ubar field = zbar scratch
         base.c_l = c_l; base.c_E = c_E; base.c_n = c_n;
         for (int j = 0; j < 5; ++j) base.kb[j] = kb[j];
+        if (c.trace_mode == CNF_TRACE_JVP) {
+            if ((rc = tc_vjp_stage_jvp(h, s, bf, src, base, row0, mc, grad))) return rc;
+            continue;
+        }
         k_tc_prep<1><<<(mc + 255) / 256, 256, 0, h->stream>>>(h->d_ctrl, bf, src, c.D, bf.ys, c.C, row0, mc, s->H[0].p[0],
                                                           s->H[0].p[1], s->H[0].ld, -1, nullptr, nullptr, 0);
         h->launches++;

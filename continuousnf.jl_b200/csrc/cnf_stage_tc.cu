@@ -38,7 +38,10 @@ enum {
     TCB_GBAR_HIDDEN = 11,  // gbar_l: dbar_l = gbar_l q_{l+1} (fp32, in place), qbar_{l+1} = gbar_l (1-h_l^2)
     TCB_GBAR_LAST = 12,    // gbar_L: dbar_L = gbar_L eps, pbar_L = (ybar - 2 y dbar_L)(1-y^2)
     TCB_HBAR_HIDDEN = 13,  // hbar_l: pbar_l = (hbar_l - 2 h_l dbar_l)(1-h_l^2)
-    TCB_ZBAR = 14          // zbar: ubar += zbar, kbar_j += dt a_ij zbar
+    TCB_ZBAR = 14,         // zbar: ubar += zbar, kbar_j += dt a_ij zbar
+    // JacVec reverse sweep (forward-mode tangent chain tau_l = (tau_{l-1} W_l^T) .* d_l; maths in cnf_backward_tc.cu)
+    TCB_JVP_LAST = 15      // s_L -> tau_L = s_L d_L, taubar_L = -alpha eps + gamma tau_L/|tau_L|; sbar_L = taubar_L d_L (planes),
+                           // dbar_L = taubar_L s_L, abar_L = (ybar - 2 y dbar_L) d_L (second plane pair)
 };
 
 struct TcEpi {
@@ -47,6 +50,8 @@ struct TcEpi {
     const float* bias;             // [N]                       (FWD_*)
     __nv_bfloat16* out[2];         // [rows x ld_out] planes    (hidden kinds; FWD_LAST: g_L planes)
     int ld_out;
+    __nv_bfloat16* out2[2];        // second plane pair (TCB_JVP_LAST: abar_L)
+    int ld_out2;
     const __nv_bfloat16* hp[2];    // activations for d = 1-h^2 (BWD_HIDDEN)
     int ld_h;
     const float* eps;              // D x Bs (SoA)
@@ -446,6 +451,53 @@ __device__ __forceinline__ void tc_epilogue_bwd(const TcEpi& ep, TcSmemCtl* ctl,
 #pragma unroll
             for (int j = 0; j < TC_CW; ++j) x[j] = (c0 + j < ep.D) ? fmaf(inv, __uint_as_float(v[j]), -al * e[j]) : 0.0f;
             tc_store_planes16<1>(x, ep.out, rloc * ep.ld_out + c0);
+        }
+        return;
+    }
+    if (KIND == TCB_JVP_LAST) {
+        // acc = s_L = tau_{L-1} W_L^T.  Pass 1: |tau_L|^2 with tau_L = s_L (1 - y^2); pass 2: the three cotangents.
+        float s1 = 0.0f;
+        for (int ch = sub; ch < nchunk; ch += TC_NSUB) {
+            const int c0 = ch * TC_CW;
+            if (c0 >= ep.D) break;
+            uint32_t v[TC_CW];
+            float y[TC_CW];
+            tc_load_f32x16(ep.f32a + rloc * ep.ld_f + c0, y);
+            tc::tmem_ld_32x16(tbase + c0, v);
+            tc::tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < TC_CW; ++j)
+                if (c0 + j < ep.D) {
+                    const float t = __uint_as_float(v[j]) * fmaf(-y[j], y[j], 1.0f);
+                    s1 = fmaf(t, t, s1);
+                }
+        }
+        const float2 r = tc_quad_reduce(ctl, quad, sub, lane, par, s1, 0.0f);
+        const float inv = (live && (ep.flags & CNF_FLAG_NORM_J) && r.x > 0.0f) ? wgt * ep.c_n / sqrtf(r.x) : 0.0f;
+        const float al = live ? wgt * ep.c_l : 0.0f;
+        for (int ch = sub; ch < nchunk; ch += TC_NSUB) {
+            const int c0 = ch * TC_CW;
+            if (c0 >= ep.D) break;
+            uint32_t v[TC_CW];
+            float y[TC_CW], yb[TC_CW], e[TC_CW], sb[TC_CW], pb[TC_CW];
+            tc_load_soa16(ep.eps, ep.Bs, grow, c0, ep.D, e);
+            tc_load_f32x16(ep.f32a + rloc * ep.ld_f + c0, y);
+            tc_load_f32x16(ep.f32b + rloc * ep.ld_f + c0, yb);
+            tc::tmem_ld_32x16(tbase + c0, v);
+            tc::tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < TC_CW; ++j) {
+                sb[j] = 0.0f; pb[j] = 0.0f;
+                if (c0 + j < ep.D) {
+                    const float sl = __uint_as_float(v[j]);
+                    const float dl = fmaf(-y[j], y[j], 1.0f);
+                    const float tb = fmaf(inv, sl * dl, -al * e[j]);     // taubar_L
+                    sb[j] = tb * dl;                                      // sbar_L
+                    pb[j] = fmaf(-2.0f * y[j], tb * sl, yb[j]) * dl;      // abar_L = (ybar - 2 y dbar_L) d_L
+                }
+            }
+            tc_store_planes16<1>(sb, ep.out, rloc * ep.ld_out + c0);
+            tc_store_planes16<1>(pb, ep.out2, rloc * ep.ld_out2 + c0);
         }
         return;
     }
@@ -992,7 +1044,7 @@ static void tc_launch_gemm(cnf_handle* h, TcState* s, const TcPlane& A, const Tc
         break;
         TC_CASE(TC_FWD_HIDDEN) TC_CASE(TC_FWD_LAST) TC_CASE(TC_BWD_HIDDEN) TC_CASE(TC_BWD_LAST) TC_CASE(TC_JVP_LAST)
         TC_CASE(TCB_FWD_LAST) TC_CASE(TCB_BWD_HIDDEN) TC_CASE(TCB_BWD_LAST) TC_CASE(TCB_GBAR_HIDDEN)
-        TC_CASE(TCB_GBAR_LAST) TC_CASE(TCB_HBAR_HIDDEN) TC_CASE(TCB_ZBAR)
+        TC_CASE(TCB_GBAR_LAST) TC_CASE(TCB_HBAR_HIDDEN) TC_CASE(TCB_ZBAR) TC_CASE(TCB_JVP_LAST)
 #undef TC_CASE
         default: break;
     }

@@ -37,7 +37,6 @@ def test_augmented_f(cid, B, trace_mode, mode):
 FLOORS = {}      # test id -> tolerance applied to the relative log-density / loss error
 FLIPS = {}       # test id -> True when the accepted-step counts differed by one
 FLOOR_MAX = 1e-3  # no case may need a floor above this
-FLIP_FRACTION_MAX = 0.25
 
 
 def _logdensity_case(name, cid, B, trace_mode, mode, inp=None, kernel_path=0):
@@ -61,16 +60,17 @@ def _logdensity_case(name, cid, B, trace_mode, mode, inp=None, kernel_path=0):
     tol = max(1e-4, floor)
     FLIPS[name] = st["naccept"] != rst["naccept"]
     err = relerr(lp, rlp)
-    if st["naccept"] == rst["naccept"]:
-        FLOORS[name] = tol
-        print(f"{name}: max rel logp err {err:.2e}, tolerance applied {tol:.2e} (floor {floor:.2e}), naccept {st['naccept']}")
-        assert tol <= FLOOR_MAX, (name, tol)
-        assert err < tol
-        assert relnorm(np.asarray(z).T, rz) < tol
-        assert np.allclose(np.stack(regs, 1), rregs, rtol=1e-4, atol=1e-5)
-    else:  # a borderline accept/reject flip: both are valid solves, compare at solver tolerance
-        print(f"{name}: accepted steps {st['naccept']} vs oracle {rst['naccept']}: max rel logp err {err:.2e} (bound 5e-3)")
-        assert err < 5e-3
+    # the SAME tolerance whether or not the accepted-step counts agree: north_star asks for 1e-4 AND steps +-1.
+    # (Where the counts differ it is by one step fewer on the tensor-core paths, systematically: their f has less
+    # rounding noise than an FP32 FMA chain, and on these problems the abstol = 1e-6 rows of the error norm turn that
+    # noise into the step-size sequence — DESIGN.md §6.  Both solves are far more accurate than the solver tolerance.)
+    FLOORS[name] = tol
+    print(f"{name}: max rel logp err {err:.2e}, tolerance applied {tol:.2e} (floor {floor:.2e}), naccept {st['naccept']} "
+          f"vs oracle {rst['naccept']}")
+    assert tol <= FLOOR_MAX, (name, tol)
+    assert err < tol
+    assert relnorm(np.asarray(z).T, rz) < tol
+    assert np.allclose(np.stack(regs, 1), rregs, rtol=1e-4, atol=1e-5)
     return st
 
 
@@ -106,8 +106,6 @@ def test_logdensity_c4_hutchinson_large():
 @pytest.mark.parametrize("cid,B", [("C0", 64), ("C1", 1024), ("C3", 256), ("C4", 1024), ("C5", 64)])
 @pytest.mark.parametrize("trace_mode", [0, 1])
 def test_loss_grad(cid, B, trace_mode):
-    if cid == "C5" and trace_mode == 1:
-        pytest.skip("JacVec training at width 1024: the tensor reverse sweep covers VecJac; the generic one does not fit")
     inp = wl.make_inputs(cid, B=B)
     c = wl.CONFIGS[cid]
     icnf = make_icnf(cid, trace_mode=trace_mode)
@@ -124,12 +122,11 @@ def test_loss_grad(cid, B, trace_mode):
     same = pst["naccept"] == rst["naccept"]
     fl_l = 4 * abs(pval - rval) / abs(rval) if same else 0.0
     fl_g = 4 * relnorm(pg, rg) if same else 0.0
-    tol_l, tol_g = (max(1e-4, fl_l), max(1e-3, fl_g)) if st["naccept"] == rst["naccept"] else (5e-3, 5e-2)
+    tol_l, tol_g = max(1e-4, fl_l), max(1e-3, fl_g)     # the same whether or not the step counts agree (see _logdensity_case)
     name = f"loss_grad[{cid},B={B},tm={trace_mode}]"
     FLIPS[name] = st["naccept"] != rst["naccept"]
-    if not FLIPS[name]:
-        FLOORS[name] = tol_l
-        assert tol_l <= FLOOR_MAX and tol_g <= 10 * FLOOR_MAX, (name, tol_l, tol_g)
+    FLOORS[name] = tol_l
+    assert tol_l <= FLOOR_MAX and tol_g <= 10 * FLOOR_MAX, (name, tol_l, tol_g)
     print(f"{name}: loss rel err {abs(val - rval) / abs(rval):.2e} (tol {tol_l:.1e}), grad rel err {relnorm(g, rg):.2e} "
           f"(tol {tol_g:.1e}), naccept {st['naccept']} vs {rst['naccept']}")
     assert abs(val - rval) / abs(rval) < tol_l
@@ -137,7 +134,7 @@ def test_loss_grad(cid, B, trace_mode):
     assert relnorm(np.asarray(gx).T, rgx) < tol_g
 
 
-@pytest.mark.parametrize("cid,B,tm", [("C2", 1024, 1), ("C2", 512, 0), ("C1", 256, 0), ("C4", 128, 0)])
+@pytest.mark.parametrize("cid,B,tm", [("C2", 1024, 1), ("C2", 512, 0), ("C1", 256, 0), ("C4", 128, 0), ("C4", 384, 1)])
 def test_loss_grad_testmode(cid, B, tm):
     """gradient of loss(icnf, TestMode(), ...) = -mean(logp) w.r.t. ps and xs (reference
     test/call_tests.jl:239-251 differentiates it): exact-trace reverse sweep vs the oracle's"""
@@ -156,7 +153,9 @@ def test_loss_grad_testmode(cid, B, tm):
     same = pst["naccept"] == rst["naccept"]
     fl_l = 4 * abs(pval - rval) / abs(rval) if same else 0.0
     fl_g = 4 * relnorm(pg, rg) if same else 0.0
-    tol_l, tol_g = (max(1e-4, fl_l), max(1e-3, fl_g)) if st["naccept"] == rst["naccept"] else (5e-3, 5e-2)
+    tol_l, tol_g = max(1e-4, fl_l), max(1e-3, fl_g)
+    print(f"loss_grad_testmode[{cid},B={B},tm={tm}]: loss rel err {abs(val - rval) / abs(rval):.2e}, grad rel err {relnorm(g, rg):.2e}, "
+          f"naccept {st['naccept']} vs {rst['naccept']}, path {st['kernel_path']}")
     assert abs(val - rval) / abs(rval) < tol_l
     assert relnorm(g, rg) < tol_g
     assert relnorm(np.asarray(gx).T, rgx) < tol_g
@@ -638,8 +637,9 @@ def test_tensor_path_exact_trace_testmode(cid, B, trace_mode):
 
 def test_zz_tolerance_report():
     """runs last in this file: the tolerance every parity case above actually used.  north_star asks for 1e-4 / 1e-4 /
-    1e-3 AND steps +-1; the two documented widenings (conditioning floor on the tspan = (0, 13) configs; solver-level
-    comparison when the step counts differ by one) are bounded here instead of being silent."""
+    1e-3 AND steps +-1.  One documented widening remains (the conditioning floor of the tspan = (0, 13) configs) and is
+    bounded here; cases whose accepted-step count differs by one are held to the same tolerance as the others and are
+    listed."""
     if not FLIPS:
         pytest.skip("no parity case ran in this session")
     widened = {k: v for k, v in FLOORS.items() if v > 1e-4}
@@ -647,4 +647,3 @@ def test_zz_tolerance_report():
     print(f"{len(FLIPS)} parity cases; tolerance floor above 1e-4 in {len(widened)}: {widened}")
     print(f"accepted-step count differed by one in {len(flips)}: {flips}")
     assert all(v <= FLOOR_MAX for v in FLOORS.values())
-    assert len(flips) <= FLIP_FRACTION_MAX * len(FLIPS), flips
