@@ -445,6 +445,7 @@ static int solve_device(cnf_handle* h, const CnfBufs& bf, int mode, int R, long 
     ic.R = R;
     ic.D = c.D;
     ic.nf = 1;
+    ic.stiff_max = -1.0f;   // stays -1 on kernel paths that do not accumulate the estimate (narrow register kernels)
     if (c.dt0 > 0) ic.dt = ic.tdir * c.dt0;
     h->h_ctrl[0] = ic;
     CNF_CUDA(cudaMemcpyAsync(h->d_ctrl, &h->h_ctrl[0], sizeof(CnfCtrl), cudaMemcpyHostToDevice, h->stream));
@@ -529,6 +530,8 @@ static void fill_stats(cnf_handle* h, const CnfCtrl& c, cnf_stats* st) {
     st->kernel_path = h->path_used;
     st->t_final = c.t;
     st->dt_last = c.dt_last;
+    st->stiff_max = c.stiff_max;
+    st->stiff_run = c.stiff_run;
     float ms = 0.0f;
     if (cudaEventElapsedTime(&ms, h->ev0, h->ev3) == cudaSuccess) st->ms_total = ms;
     if (cudaEventElapsedTime(&ms, h->ev1, h->ev2) == cudaSuccess) st->ms_solve = ms;

@@ -21,6 +21,10 @@ struct CnfCtrl {
     float t, dt, t0, t1, tdir, dtmax, dtmin, reltol, abstol, dt_last, dt0init;
     int done, retcode, k1idx, use_tape, R, D;
     int accepted;        // the attempt the controller has just judged was accepted (k_tape_stages)
+    // stiffness estimate of the default algorithm's auto-switch (reported only)
+    double stiffu, stiffd;   // sum (k7 - k6)^2, sum (u_new - g6)^2 of the current attempt
+    float stiff_max;
+    int stiff_run, stiff_cur;
 };
 
 // Network description passed by value to kernels.

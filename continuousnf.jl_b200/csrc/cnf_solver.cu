@@ -90,7 +90,7 @@ __device__ __forceinline__ void d_errnorm(CnfCtrl* c, const CnfBufs& bf) {
     const float* k1 = bf.K[c->k1idx];
     const float* k7 = bf.K[6 - c->k1idx];
     const float dt = c->dt, reltol = c->reltol, abstol = c->abstol;
-    double acc = 0.0;
+    double acc = 0.0, su = 0.0, sd = 0.0;
     const long long n = (long long)R * bf.Bs;
     for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n;
          e += (long long)gridDim.x * blockDim.x) {
@@ -99,6 +99,14 @@ __device__ __forceinline__ void d_errnorm(CnfCtrl* c, const CnfBufs& bf) {
         float a = c_BT[0] * k1[e];
         for (int j = 1; j < 6; ++j) a = fmaf(c_BT[j], bf.K[j][e], a);
         a = fmaf(c_BT[6], k7[e], a);
+        {   // stiffness estimate (A.1): k7 - k6 and u_new - g6 = dt (sum_j (a_7j - a_6j) k_j + a_76 k_6)
+            float gd = (c_A[6][0] - c_A[5][0]) * k1[e];
+            for (int j = 1; j < 5; ++j) gd = fmaf(c_A[6][j] - c_A[5][j], bf.K[j][e], gd);
+            gd = dt * fmaf(c_A[6][5], bf.K[5][e], gd);
+            const float kd = k7[e] - bf.K[5][e];
+            su += (double)kd * (double)kd;
+            sd += (double)gd * (double)gd;
+        }
         float ut = dt * a;
         float sc = fmaf(fmaxf(fabsf(u[e]), fabsf(un[e])), reltol, abstol);
         float r = ut / sc;
@@ -106,7 +114,9 @@ __device__ __forceinline__ void d_errnorm(CnfCtrl* c, const CnfBufs& bf) {
         acc += (double)r * (double)r;
     }
     acc = cnf_block_sum(acc, sh);
-    if (threadIdx.x == 0) atomicAdd(&c->errsum, acc);
+    su = cnf_block_sum(su, sh);
+    sd = cnf_block_sum(sd, sh);
+    if (threadIdx.x == 0) { atomicAdd(&c->errsum, acc); atomicAdd(&c->stiffu, su); atomicAdd(&c->stiffd, sd); }
 }
 __global__ void k_errnorm(CnfCtrl* c, CnfBufs bf) { d_errnorm(c, bf); }
 void launch_errnorm(cnf_handle* h, const CnfBufs& bf) {
@@ -135,6 +145,8 @@ __device__ __forceinline__ void d_controller(CnfCtrl* c, float* dts) {
     if (c->done) return;
     const double es = c->errsum;
     c->errsum = 0.0;
+    const double stu = c->stiffu, std_ = c->stiffd;
+    c->stiffu = 0.0; c->stiffd = 0.0;
     c->nf += 6;
     const float EEst = (float)sqrt(es / c->nglobal);
     if (EEst != EEst) { c->retcode = CNF_RET_UNSTABLE; c->done = 1; return; }
@@ -147,6 +159,12 @@ __device__ __forceinline__ void d_controller(CnfCtrl* c, float* dts) {
         q = fmax(1.0 / CNF_QMAX, fmin(1.0 / CNF_QMIN, q / CNF_GAMMA));
     }
     if (EEst <= 1.0f) {
+        if (std_ > 0.0) {   // kernel paths that accumulate the two norms (k_errnorm)
+            const float stiff = (float)(fabs((double)c->dt) * sqrt(stu / std_) / CNF_TSIT5_STABILITY);
+            c->stiff_max = fmaxf(c->stiff_max, stiff);
+            c->stiff_cur = stiff > CNF_STIFFTOL ? c->stiff_cur + 1 : 0;
+            c->stiff_run = max(c->stiff_run, c->stiff_cur);
+        }
         if (c->naccept < CNF_MAX_SLOTS) dts[c->naccept] = c->dt;
         float tn = c->t + c->dt;
         if (fabsf(tn - c->t1) < 100.0f * 1.1920929e-7f * fmaxf(fabsf(c->t), fabsf(c->t1))) tn = c->t1;

@@ -50,7 +50,8 @@ mutable struct CnfStats
     t_final::Float32; dt_last::Float32
     ms_total::Float64; ms_solve::Float64; gpu_launches::Int64
     ms_stage::Float64; n_stage::Int64
-    CnfStats() = new(0, 0, 0, 0, 0, 0.0f0, 0.0f0, 0.0, 0.0, 0, 0.0, 0)
+    stiff_max::Float32; stiff_run::Int32
+    CnfStats() = new(0, 0, 0, 0, 0, 0.0f0, 0.0f0, 0.0, 0.0, 0, 0.0, 0, -1.0f0, 0)
 end
 
 const B200ICNF{CM} = CNF.ICNF{

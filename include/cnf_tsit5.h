@@ -52,6 +52,12 @@
 #define CNF_QMAX 10.0
 #define CNF_QOLDINIT 1e-4
 
+/* auto-switch of the reference's default algorithm, reported only: Tsit5's stability size and the
+ * non-stiff tolerance of OrdinaryDiffEq's AutoSwitch; 10 consecutive stiff steps would switch to a stiff method */
+#define CNF_TSIT5_STABILITY 3.5068
+#define CNF_STIFFTOL 0.9f
+#define CNF_MAXSTIFFSTEP 10
+
 /* solver defaults when sol_kwargs is empty, SURVEY.md A.4 */
 #define CNF_DEFAULT_RELTOL 1e-3f
 #define CNF_DEFAULT_ABSTOL 1e-6f

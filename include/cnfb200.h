@@ -89,6 +89,14 @@ typedef struct cnf_stats {
     int64_t gpu_launches;         /* kernels launched by this call */
     double ms_stage;              /* summed device time of the RK stage kernels (option time_stages) */
     int64_t n_stage;              /* number of stage-kernel launches timed */
+    /* Reported, never acted on: the reference calls solve() without `alg` (src/base_icnf.jl:141), so its
+     * default composite algorithm starts on Tsit5 and would leave it after 10 consecutive steps whose stiffness estimate
+     * |dt| * ||k7 - k6|| / ||u_new - g6|| / 3.5068 (Tsit5's stability size) exceeds 9/10.  stiff_max = the largest
+     * estimate over the accepted steps (-1: not computed on this kernel path), stiff_run = the longest run of
+     * consecutive accepted steps above 9/10.  stiff_run >= 10 means the real reference would have switched solver and
+     * this Tsit5-only path is not comparable on that problem.  Local shard only when the batch is sharded. */
+    float stiff_max;
+    int32_t stiff_run;
 } cnf_stats;
 
 typedef struct cnf_handle cnf_handle;

@@ -299,6 +299,8 @@ typedef struct {
     int64_t naccept, nreject, nf;
     int32_t retcode;
     float t_final, dt_last;
+    float stiff_max;   /* largest stiffness estimate of the default algorithm's auto-switch (reported only) */
+    int32_t stiff_run; /* longest run of consecutive accepted steps above the switch tolerance */
 } ostats;
 
 typedef struct { /* accepted-step tape for the discrete adjoint */
@@ -418,6 +420,8 @@ static void tsit5_solve(const omodel* m, int mode, float* u, const float* ys, co
 
     g_last_ndts = 0;
     float t = t0;
+    int32_t stiff_cur = 0;
+    st->stiff_max = -1.0f;
     double qold = CNF_QOLDINIT;
     int64_t iter = 0;
     st->retcode = CNF_OK;
@@ -457,6 +461,26 @@ static void tsit5_solve(const omodel* m, int mode, float* u, const float* ys, co
             q = fmax(1.0 / CNF_QMAX, fmin(1.0 / CNF_QMIN, q / CNF_GAMMA));
         }
         if (EEst <= 1.0f) {
+            /* A.1, reported only: OrdinaryDiffEq's composite default would test |dt| * eigen_est / 3.5068 > 9/10 with
+             * eigen_est = ||k7 - k6|| / ||u_new - g6|| (RMS norms; g6 = the 6th stage input) after every step */
+            {
+                double su = 0.0, sd = 0.0;
+#pragma omp parallel for schedule(static) reduction(+ : su, sd)
+                for (int64_t e = 0; e < nel; ++e) {
+                    float gd = (A_[6][0] - A_[5][0]) * k[0][e];
+                    for (int j = 1; j < 5; ++j) gd = fmaf(A_[6][j] - A_[5][j], k[j][e], gd);
+                    gd = dt * fmaf(A_[6][5], k[5][e], gd);
+                    float kd = k[6][e] - k[5][e];
+                    su += (double)kd * (double)kd;
+                    sd += (double)gd * (double)gd;
+                }
+                if (sd > 0.0) {
+                    float stiff = (float)(fabs((double)dt) * sqrt(su / sd) / CNF_TSIT5_STABILITY);
+                    if (stiff > st->stiff_max) st->stiff_max = stiff;
+                    stiff_cur = stiff > CNF_STIFFTOL ? stiff_cur + 1 : 0;
+                    if (stiff_cur > st->stiff_run) st->stiff_run = stiff_cur;
+                }
+            }
             if (tape) tape_push(tape, u, (size_t)nel, dt);
             if (st->naccept < 4096) g_last_dts[st->naccept] = dt;
             g_last_ndts = st->naccept + 1;
@@ -531,6 +555,8 @@ static void copy_stats(cnf_stats* out, const ostats* st) {
     out->retcode = st->retcode;
     out->t_final = st->t_final;
     out->dt_last = st->dt_last;
+    out->stiff_max = st->stiff_max;
+    out->stiff_run = st->stiff_run;
 }
 
 /* inference(icnf, mode, xs[, ys], ps, st)  (src/base_icnf.jl:407-426) */

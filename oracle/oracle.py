@@ -40,6 +40,7 @@ class Stats(C.Structure):
         ("t_final", C.c_float), ("dt_last", C.c_float),
         ("ms_total", C.c_double), ("ms_solve", C.c_double), ("gpu_launches", C.c_int64),
         ("ms_stage", C.c_double), ("n_stage", C.c_int64),
+        ("stiff_max", C.c_float), ("stiff_run", C.c_int32),
     ]
 
     def as_dict(self):

@@ -30,7 +30,7 @@ def test_library_exports_every_declared_symbol():
 def test_struct_sizes_match_header():
     # cnf_config: 4+9 int32, trace_mode, flags, 5 floats, (pad) int64, 3 floats, 2 int32
     assert C.sizeof(cnf._cabi.CnfConfig) == 112
-    assert C.sizeof(cnf._cabi.CnfStats) == 80
+    assert C.sizeof(cnf._cabi.CnfStats) == 88
 
 
 def test_no_cpu_fallback_without_gpu():
