@@ -47,8 +47,10 @@ class DIJacVecMatrixMode(ComputeMode):
 
 
 class DIVecJacVectorMode(ComputeMode):
-    """VectorMode: every sample its own adaptive solve.  Built for TestMode on
-    the narrow 3-layer shapes; anything else raises inside the library."""
+    """VectorMode: every sample its own adaptive solve (own dt, own error norm).  TestMode on
+    the narrow 3-layer shapes runs as one register-resident launch (kernel_path 4); every other net, width and mode
+    (TrainMode Hutchinson, conditional flows, the tensor-core paths) runs the MatrixMode stage kernels under a per-sample
+    controller (kernel_path 8).  The reverse sweep is MatrixMode-only."""
     trace_mode = _cabi.TRACE_VJP
     vector = True
 

@@ -135,6 +135,7 @@ extern "C" int32_t cnfb200_destroy(cnf_handle* h) {
     cnf_nccl_destroy(h);
     tc_free(h);
     cudaFree(h->d_io);
+    cudaFree(h->d_vg);
     cudaFree(h->d_theta); cudaFree(h->d_wt); cudaFree(h->d_grad);
     cudaFree(h->d_ctrl); cudaFree(h->d_dts); cudaFree(h->d_lossacc); cudaFree(h->d_slots); cudaFree(h->d_ktape);
     if (h->h_ctrl) cudaFreeHost(h->h_ctrl);
@@ -325,6 +326,7 @@ static int ensure_io(cnf_handle* h, long long nfloats) {
     if (nfloats <= h->cap_io) return CNF_OK;
     CNF_CUDA(cudaStreamSynchronize(h->stream));
     cudaFree(h->d_io);
+    cudaFree(h->d_vg);
     h->d_io = nullptr;
     CNF_CUDA(cudaMalloc(&h->d_io, (size_t)nfloats * sizeof(float)));
     h->cap_io = nfloats;
@@ -666,8 +668,10 @@ static int run_flow(cnf_handle* h, int mode, const float* x, int rows_x, const f
     h->path_used = 1;
     CnfCtrl fin;
     if (h->vector_mode) {   // N4: every sample its own adaptive solve (no cross-sample coupling, no allreduce)
-        if (mode != CNF_MODE_TEST) { h->err = "vector mode: TestMode only"; return CNF_ERR_UNSUPPORTED; }
-        if ((rc = vector_solve(h, bf, t0, t1, &fin))) return rc;
+        if (h->nranks > 1) Bglobal = B;   // no cross-sample coupling: nothing is exchanged between ranks
+        if (vector_narrow_ok(h, mode)) rc = vector_solve(h, bf, t0, t1, &fin);            // one launch, registers
+        else rc = vector_solve_generic(h, bf, mode, R, t0, t1, &fin);                      // any net / mode / width
+        if (rc) return rc;
     } else if ((rc = solve_device(h, bf, mode, R, Bglobal, t0, t1, false, &fin))) return rc;
     // epilogue writes in the caller's layout; host destinations go through the staging area
     const int nreg = mode == CNF_MODE_TRAIN ? 3 : 1;
@@ -786,6 +790,10 @@ extern "C" int32_t cnfb200_loss_grad_mode(cnf_handle* h, int32_t mode, const flo
     int rc = check_call(h, mode, B);
     if (rc) return rc;
     if (!xs || !loss) { h->err = "null xs/loss"; return CNF_ERR_BADARG; }
+    if (h->vector_mode && (grad_theta || grad_x)) {
+        h->err = "VectorMode: the reverse sweep is built for MatrixMode only (use loss without gradients, or a MatrixMode flow)";
+        return CNF_ERR_UNSUPPORTED;
+    }
     CNF_CUDA(cudaSetDevice(h->device));
     const cnf_config& c = h->cfg;
     const int R = c.D + (mode == CNF_MODE_TRAIN ? 3 : 1);

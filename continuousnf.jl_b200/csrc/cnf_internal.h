@@ -34,7 +34,9 @@ struct cnf_handle {
     float* d_eps = nullptr;
     // N1: on-device eps / z0 (cnf_rng.cu)
     bool tile_off = false;       // option tile_solve = 0: never use the single-CTA whole-solve kernels (cnf_tile.cu)
-    bool vector_mode = false;    // N4: per-sample step control (cnf_vector.cu)
+    bool vector_mode = false;    // N4: per-sample step control (cnf_vector.cu, cnf_vector_generic.cu)
+    void* d_vg = nullptr;        // per-sample controller arrays of the generic VectorMode driver
+    long long vg_cap = 0;
     bool rng_on = false;
     unsigned long long rng_seed = 0, rng_offset = 0;
     float steer_rate = 0.0f;     // cnfb200_set_steer: fit_epochs re-draws t1 per mini-batch (src/base_icnf.jl:108-121)
@@ -103,6 +105,8 @@ bool tile_solve_ok(cnf_handle* h, int mode, long long B);
 int tile_solve(cnf_handle* h, const CnfBufs& bf, int mode, bool use_tape, long long maxiters, CnfCtrl* out);
 bool tile_sweep(cnf_handle* h, const CnfBufs& bf, int mode, long long naccept, long long Bglobal);
 int vector_solve(cnf_handle* h, const CnfBufs& bf, float t0, float t1, CnfCtrl* out);
+bool vector_narrow_ok(const cnf_handle* h, int mode);   // the one-launch register kernel serves this shape / mode
+int vector_solve_generic(cnf_handle* h, const CnfBufs& bf, int mode, int R, float t0, float t1, CnfCtrl* out);
 void launch_tape_stages(cnf_handle* h, const CnfBufs& bf);
 void launch_philox_normal(cnf_handle* h, float* out, long long Bs, long long B, int rows, uint32_t draw);
 void launch_pack_rows(cnf_handle* h, const float* src, int rows, long long B, float* dst, long long Bs);

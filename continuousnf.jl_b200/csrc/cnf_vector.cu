@@ -202,6 +202,10 @@ static void vector_launch(cnf_handle* h, const VecParams& vp, const float* u0, f
     h->launches++;
 }
 
+bool vector_narrow_ok(const cnf_handle* h, int mode) {
+    return mode == CNF_MODE_TEST && h->cfg.kernel_path != 1 && narrow_find(h->cfg) != nullptr && h->narrow_w != nullptr;
+}
+
 // slot 0 holds [x; 0] (R x Bs); on return slot 0 holds the final state of every sample and `out`
 // a control block the epilogue kernels can read (naccept = 0 -> slot 0)
 int vector_solve(cnf_handle* h, const CnfBufs& bf, float t0, float t1, CnfCtrl* out) {

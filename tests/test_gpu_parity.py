@@ -500,7 +500,7 @@ def test_n4_vector_mode_matches_per_sample_oracle_solves(mode_cls):
     assert np.max(np.abs(np.asarray(lpm) - lp)) < 5e-2
 
 
-def test_n4_vector_mode_generate_roundtrip_and_unsupported_shapes():
+def test_n4_vector_mode_generate_roundtrip():
     cid, B = "C2", 500
     inp = wl.make_inputs(cid, B=B)
     icnf = _vector_icnf(cid, cnf.DIJacVecVectorMode)
@@ -508,12 +508,7 @@ def test_n4_vector_mode_generate_roundtrip_and_unsupported_shapes():
     lp, regs, z = cnf.inference(icnf, m, inp["xs"].T, *args_of(inp), return_z=True)
     xr = np.asarray(cnf.generate(icnf, m, *args_of(inp), B, z0=np.asarray(z))).T
     assert np.max(np.abs(xr - inp["xs"])) < 2e-2
-    with pytest.raises(cnf._cabi.CnfError):      # TrainMode has no vector kernel
-        cnf.inference(icnf, cnf.TrainMode(), inp["xs"].T, *args_of(inp))
-    wide = _vector_icnf("C3", cnf.DIJacVecVectorMode)
-    i3 = wl.make_inputs("C3", B=8)
-    with pytest.raises(cnf._cabi.CnfError):      # not a narrow shape
-        cnf.inference(wide, m, i3["xs"].T, *args_of(i3))
+    # (TrainMode and the shapes outside the narrow list run under the per-sample controller: test_n4_vector_mode_any_net_and_mode)
 
 
 def _planar_pair(nvars, C, B, trace_mode, seed=7):
@@ -633,6 +628,57 @@ def test_tensor_path_exact_trace_testmode(cid, B, trace_mode):
     assert abs(out[0][1] - rst["naccept"]) <= 1 and abs(out[0][1] - out[1][1]) <= 1
     if out[0][1] == rst["naccept"]:
         assert relerr(out[0][0], rlp) < 1e-4
+
+
+def _vector_icnf_any(cid, tm):
+    c = wl.CONFIGS[cid]
+    dims = c["dims"]
+    nn = cnf.Chain(*[cnf.Dense(dims[i], dims[i + 1], "tanh") for i in range(len(dims) - 1)])
+    cm = cnf.DIJacVecVectorMode() if tm else cnf.DIVecJacVectorMode()
+    tag = {"RNODE": cnf.RNODE, "ICNF": cnf.FFJORD, "CondRNODE": cnf.CondRNODE}[c["tag"]]
+    sk = {k: c[k] for k in ("reltol", "abstol") if c[k]}
+    return cnf.construct(tag, nn, c["nvars"], c["naug"], compute_mode=cm, tspan=c["tspan"], sol_kwargs=sk,
+                         lambda1=c["lambda1"], lambda2=c["lambda2"], lambda3=c["lambda3"],
+                         resource=cnf.B200Libs(0), rng=np.random.default_rng(1))
+
+
+@pytest.mark.parametrize("cid,B,tm,mode,path", [("C1", 48, 0, 1, 8), ("C0", 24, 1, 1, 8), ("C4", 40, 0, 1, 8), ("C4", 24, 1, 0, 8),
+                                                 ("C3", 12, 0, 1, 8), ("C2", 64, 0, 1, 8)])
+def test_n4_vector_mode_any_net_and_mode(cid, B, tm, mode, path):
+    """N4, the rest: VectorMode for TrainMode (Hutchinson), conditional flows, 1/2/3-layer nets and the tensor-core
+    widths — the MatrixMode stage kernels under a per-sample controller.  Oracle: the CPU solve called once per column
+    with B = 1 (its own dt, error norm and step count)."""
+    inp = wl.make_inputs(cid, B=B)
+    c = wl.CONFIGS[cid]
+    icnf = _vector_icnf_any(cid, tm)
+    m = cnf.TrainMode() if mode else cnf.TestMode()
+    lp, regs, z = cnf.inference(icnf, m, inp["xs"].T, *args_of(inp), eps=inp["eps"].T, return_z=True)
+    st = cnf.last_stats(icnf)
+    lp, z, regs = np.asarray(lp), np.asarray(z).T, np.stack([np.asarray(r) for r in regs], 1)
+    cfg = oracle_cfg(cid, trace_mode=tm)
+    rlp, rz, rregs, nacc = np.empty(B, np.float32), np.empty_like(z), np.empty_like(regs), []
+    for b in range(B):
+        ys = inp["ys"][b:b + 1] if inp["ys"] is not None else None
+        out = O.logdensity(cfg, inp["theta"], mode, inp["xs"][b:b + 1], ys, inp["eps"][b:b + 1], *c["tspan"])
+        rlp[b], rregs[b], rz[b] = out[0][0], out[1][0], out[2][0]
+        nacc.append(out[-1]["naccept"])
+    err = np.max(np.abs(lp - rlp) / np.maximum(1.0, np.abs(rlp)))
+    print(f"vector[{cid},B={B},tm={tm},mode={mode}]: max err {err:.2e}, naccept max {st['naccept']} vs oracle {max(nacc)} "
+          f"(min {min(nacc)}), path {st['kernel_path']}")
+    tol = 1e-4 if cid not in ("C0", "C1") else 1e-3      # tspan (0, 13): rounding is amplified along the flow
+    assert err < tol
+    assert np.max(np.abs(z - rz)) < 10 * tol
+    assert np.allclose(regs, rregs, rtol=10 * tol, atol=1e-4)
+    assert abs(st["naccept"] - max(nacc)) <= 1, (st, max(nacc))
+    assert st["kernel_path"] == path
+    assert st["retcode"] == 0
+
+
+def test_n4_vector_mode_gradient_is_refused():
+    inp = wl.make_inputs("C4", B=32)
+    icnf = _vector_icnf_any("C4", 0)
+    with pytest.raises(cnf._cabi.CnfError):
+        cnf.loss_and_grad(icnf, cnf.TrainMode(), inp["xs"].T, *args_of(inp), eps=inp["eps"].T)
 
 
 def test_zz_tolerance_report():
