@@ -8,7 +8,7 @@ from . import _cabi, adapters, parallel, workloads  # noqa: F401
 from .adapters import CondICNFDist, CondICNFModel, ICNFDist, ICNFModel, Lion, fit, transform  # noqa: F401
 from .api import (  # noqa: F401
     B200Libs, Chain, CondFFJORD, CondPlanar, CondRNODE, Dense, Planar, PlanarLayer, DIJacVecMatrixMode, DIJacVecVectorMode,
-    DIVecJacMatrixMode, DIVecJacVectorMode, FFJORD, ICNF, RNODE, TestMode, TrainMode, augmented_f,
+    DIVecJacMatrixMode, DIVecJacVectorMode, FFJORD, ICNF, RNODE, TestMode, TrainMode, augmented_f, augmented_f_static,
     construct, generate, inference, last_stats, loss, loss_and_grad, param_offsets, set_option, setup,
     steer_tspan, seed_device_rng, last_eps, fit_epochs, steer_sequence,
 )

@@ -11,6 +11,7 @@ MAX_LAYERS = 8
 MODE_TEST, MODE_TRAIN = 0, 1
 TRACE_VJP, TRACE_JVP = 0, 1
 FLAG_COND, FLAG_AUGMENTED, FLAG_NORM_Z, FLAG_NORM_J, FLAG_NORM_Z_AUG, FLAG_LAST_LINEAR = 1, 2, 4, 8, 16, 32
+STATIC_SCRATCH_BYTES = 16 << 20   # CNFB200_STATIC_SCRATCH_BYTES
 RETCODES = {0: "Success", 1: "MaxIters", 2: "DtLessThanMin", 3: "Unstable"}
 
 EXPORTS = [
@@ -18,6 +19,7 @@ EXPORTS = [
     "cnfb200_set_params", "cnfb200_comm_unique_id", "cnfb200_comm_init", "cnfb200_comm_p2p", "cnfb200_augmented_f",
     "cnfb200_logdensity", "cnfb200_loss_grad", "cnfb200_loss_grad_mode", "cnfb200_generate", "cnfb200_measure_fp32_peak",
     "cnfb200_seed_rng", "cnfb200_last_eps", "cnfb200_fit_epochs", "cnfb200_host_alloc", "cnfb200_host_free", "cnfb200_set_steer",
+    "cnfb200_augmented_f_static",
 ]
 
 
@@ -77,6 +79,8 @@ def load():
     lib.cnfb200_comm_p2p.restype = C.c_int32
     lib.cnfb200_augmented_f.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
                                         C.c_int64, C.c_void_p]
+    lib.cnfb200_augmented_f_static.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
+                                               C.c_int64, C.c_void_p]
     lib.cnfb200_logdensity.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
                                        C.c_int64, C.c_float, C.c_float, C.c_void_p, C.c_void_p,
                                        C.c_void_p, C.POINTER(CnfStats)]

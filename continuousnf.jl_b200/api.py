@@ -605,6 +605,28 @@ def augmented_f(icnf, mode, u, *args, eps=None):
     return _rows_view(du)
 
 
+def augmented_f_static(icnf, mode, u, *args, eps=None, out):
+    """cnfb200_augmented_f_static: the same evaluation with no device allocation inside the call (no reference
+    counterpart; csrc/cnf_noalloc.cu).  u, ys, eps and `out` are CUDA torch tensors that already hold the
+    sample-major memory the ABI reads: shape (B, rows), float32, contiguous.  Nothing is copied or allocated here
+    either; `out` (B, R) is filled and returned.  (2D + C + R) * round_up(B, 256) floats must fit
+    _cabi.STATIC_SCRATCH_BYTES."""
+    ys, ps, st = _split(args, icnf.cond, "augmented_f_static")
+    lib = _cabi.load()
+    h = _upload_params(icnf, ps)
+    R = icnf.D + (3 if isinstance(mode, TrainMode) else 1)
+    for name, t, rows in (("u", u, R), ("ys", ys if icnf.cond else None, icnf._cfg.C), ("eps", eps, icnf.D), ("out", out, R)):
+        if t is None:
+            continue
+        if not (_is_torch(t) and t.device.type == "cuda" and t.is_contiguous() and t.dtype.is_floating_point
+                and t.element_size() == 4 and t.ndim == 2 and t.shape[1] == rows and t.shape[0] == u.shape[0]):
+            raise ValueError(f"{name}: expected a contiguous float32 CUDA tensor of shape (B, {rows})")
+    rc = lib.cnfb200_augmented_f_static(h, mode.code, u.data_ptr(), ys.data_ptr() if icnf.cond else None,
+                                        eps.data_ptr() if eps is not None else None, int(u.shape[0]), out.data_ptr())
+    icnf._check(rc, "cnfb200_augmented_f_static")
+    return out
+
+
 def set_option(icnf, key, value):
     """runtime options of the handle: 'time_stages', 'kernel_path'"""
     icnf._check(_cabi.load().cnfb200_set_option(icnf.handle(), key.encode(), int(value)), "cnfb200_set_option")

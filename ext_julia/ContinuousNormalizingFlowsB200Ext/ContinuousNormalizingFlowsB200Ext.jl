@@ -260,6 +260,18 @@ function augmented_f(icnf::B200ICNF, mode::CNF.Mode, u::AbstractMatrix, ys, ϵ, 
     du
 end
 
+# the same evaluation without any device allocation inside the call (no reference counterpart; csrc/cnf_noalloc.cu):
+# u, ys, ϵ, du are DEVICE pointers (e.g. `pointer(::CuArray)` reinterpreted), (2D + C + R) * round_up(B, 256) floats
+# must fit CNFB200_STATIC_SCRATCH_BYTES = 16 MiB
+function augmented_f_static!(du::Ptr{Float32}, icnf::B200ICNF, mode::CNF.Mode, u::Ptr{Float32}, ys::Ptr{Float32},
+        ϵ::Ptr{Float32}, B::Integer, ps)
+    h = handle(icnf); set_params!(icnf, h, ps)
+    check(icnf, h, ccall((:cnfb200_augmented_f_static, lib(icnf)), Int32,
+        (Ptr{Cvoid}, Int32, Ptr{Float32}, Ptr{Float32}, Ptr{Float32}, Int64, Ptr{Float32}),
+        h, mode isa CNF.TrainMode ? 1 : 0, u, ys, ϵ, B, du), "cnfb200_augmented_f_static")
+    du
+end
+
 # ---- inference(icnf, mode, xs[, ys], ps, st): replaces base_icnf.jl:407-426 for RESOURCE <: B200Libs --------------------
 function _inference(icnf::B200ICNF, mode::CNF.Mode, xs::AbstractMatrix, ys, ps)
     h = handle(icnf); set_params!(icnf, h, ps)

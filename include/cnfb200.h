@@ -132,6 +132,19 @@ CNF_API int32_t cnfb200_comm_p2p(const cnf_handle* h);
 CNF_API int32_t cnfb200_augmented_f(cnf_handle* h, int32_t mode, const float* u, const float* ys,
                             const float* eps, int64_t B, float* du);
 
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same result as
+ * cnfb200_augmented_f on the generic FP32 kernels, but the call allocates nothing: its SoA work planes live in one
+ * file-scope device array of CNFB200_STATIC_SCRATCH_BYTES that every GPU loading the library holds until exit
+ * (csrc/cnf_noalloc.cu).  u, ys, eps and du must be DEVICE pointers (eps is required in TrainMode);
+ * (2 D + C + R) * round_up(B, 256) floats must fit the array, larger batches return CNF_ERR_BADARG with the limit in
+ * cnfb200_last_error.  All handles on a device share the array and it keeps the last call's contents (every plane a
+ * call reads is rewritten first); the call returns after its work is done, but calls that overlap on the GPU (two
+ * handles from two host threads) race. */
+#define CNFB200_STATIC_SCRATCH_BYTES (16u << 20)
+CNF_API int32_t cnfb200_augmented_f_static(cnf_handle* h, int32_t mode, const float* u, const float* ys,
+                                   const float* eps, int64_t B, float* du);
+
 /* replaces inference(icnf, mode, xs[, ys], ps, st) = inference_prob + inference_sol
  * (src/base_icnf.jl:266-309, 167-189, 407-426).  xs: nvars x B; ys: C x B or NULL;
  * eps: D x B (may be NULL in TestMode, where it is unused);
