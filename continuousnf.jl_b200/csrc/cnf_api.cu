@@ -119,6 +119,7 @@ static void free_workspaces(cnf_handle* h) {
     free_ktape(h);
     for (int j = 0; j < 16; ++j) { cudaFree(h->d_bw[j]); h->d_bw[j] = nullptr; }
     h->cap_bw = 0;
+    h->cap_bw13 = 0;
     h->cap_B = 0;
     h->cap_R = 0;
 }
@@ -293,6 +294,16 @@ static int ensure_slots(cnf_handle* h, size_t want, size_t need = 0) {
         if (tight || cudaMalloc(&p, bytes) != cudaSuccess) {
             cudaGetLastError();
             if (h->slots.size() >= need) break;
+            if (!h->ktape.empty()) {
+                // the stage tape is optional (the reverse sweep recomputes untaped steps): its last entry goes back to
+                // the device before a solve is given up.  Kernels in flight may still write it: wait for them first.
+                CNF_CUDA(cudaStreamSynchronize(h->stream));
+                float* last = h->ktape.back();
+                h->ktape.pop_back();
+                CNF_CUDA(cudaMemsetAsync(h->d_ktape + h->ktape.size(), 0, sizeof(float*), h->stream));
+                cudaFree(last);
+                continue;
+            }
             h->err = "state slots of the step tape do not fit the device memory (shard the batch over more GPUs)";
             return CNF_ERR_OOM;
         }
@@ -755,11 +766,13 @@ static int ensure_bw(cnf_handle* h, long long Bs) {
     const long long need = (long long)h->cfg.D * Bs;
     if (need <= h->cap_bw) return CNF_OK;
     CNF_CUDA(cudaStreamSynchronize(h->stream));
-    for (int j = 0; j < 15; ++j) {   // [12]: zbar scratch of the tensor-path reverse sweep; [13], [14]: one-hot eps / zero cotangent (exact trace)
+    for (int j = 0; j < 13; ++j) {   // [12]: zbar scratch of the tensor-path reverse sweep; [13], [14]: allocated by the exact-trace tensor sweep only
         cudaFree(h->d_bw[j]);
         h->d_bw[j] = nullptr;
         CNF_CUDA(cudaMalloc(&h->d_bw[j], (size_t)need * sizeof(float)));
     }
+    for (int j = 13; j < 15; ++j) { cudaFree(h->d_bw[j]); h->d_bw[j] = nullptr; }
+    h->cap_bw13 = 0;
     h->cap_bw = need;
     return CNF_OK;
 }

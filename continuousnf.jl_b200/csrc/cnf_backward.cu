@@ -354,7 +354,17 @@ static int backward_sweep(cnf_handle* h, const CnfBufs& bf, int mode, long long 
     // TestMode (exact trace) on wide nets: the D unit-vector VJPs on the tensor-core sweep as well (eps = e_unit in
     // d_bw[13], zero zdot cotangent in d_bw[14] for unit > 0)
     const bool tct = !train && tc_supported(c, CNF_MODE_TEST) && tc_bw_supported(h);
-    if (tct) CNF_CUDA(cudaMemsetAsync(w[14], 0, (size_t)nz * sizeof(float), h->stream));
+    if (tct) {
+        if (h->cap_bw13 < nz) {
+            for (int j = 13; j < 15; ++j) {
+                cudaFree(w[j]);
+                w[j] = nullptr;
+                CNF_CUDA(cudaMalloc(&w[j], (size_t)nz * sizeof(float)));
+            }
+            h->cap_bw13 = nz;
+        }
+        CNF_CUDA(cudaMemsetAsync(w[14], 0, (size_t)nz * sizeof(float), h->stream));
+    }
     for (long long n = naccept - 1; n >= 0; --n) {
         const float* un = h->slots[n];
         const float* dtp = h->d_dts + n;

@@ -55,6 +55,7 @@ struct cnf_handle {
     // backward workspaces
     float* d_bw[16] = {};
     long long cap_bw = 0;
+    long long cap_bw13 = 0;     // d_bw[13], d_bw[14]: one-hot eps / zero cotangent of the exact-trace tensor sweep (allocated on first use)
     // communicator (NCCL via dlopen)
     void* nccl_comm = nullptr;
     int nranks = 1, rank = 0;

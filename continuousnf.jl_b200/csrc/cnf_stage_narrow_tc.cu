@@ -7,18 +7,22 @@
 //   1. SIMT: stage input u + dt*sum a_ij k_j, layer 1 and the D one-hot tangents in registers,
 //      written as IEEE-half hi/lo planes straight into shared memory in the canonical K-major
 //      SWIZZLE_128B operand layout (no TMA: the operand never exists in global memory);
-//   2. the issuer thread launches (1+D) x 4 x 3 tcgen05.mma (M = 128, N = 64, K = 16; hi*hi + lo*hi + hi*lo
-//      = FP32-level products, as in cnf_stage_tc.cu) against the resident W2 planes; accumulators in TMEM;
-//   3. SIMT epilogue from TMEM: bias + tanh, tangent scaling, layer 3 (only the diagonal of the
-//      D x D Jacobian product is needed for the trace); the two halves of a sample meet through
-//      shared memory; output rows; at the 7th stage also the new state and the embedded-error
-//      partial sum.
+//   2. the issuer thread launches 2 x 4 x 3 tcgen05.mma (M = 128, K = 16; hi*hi + lo*hi + hi*lo = FP32-level
+//      products, as in cnf_stage_tc.cu): h1 against the resident W2 planes (N = 64) and dn = h1^2 - 1 against
+//      the resident TANGENT planes (N = 64 D); accumulators in TMEM.  The tangents tau1_v = W1[:, v] .* (1 - h1^2)
+//      are never formed: the per-unit factors on both sides of layer 2 are folded into the weights on the host,
+//      T_v[o][k] = W3[v][o] W2[o][k] C W1[k][v], so ONE operand vector (dn) serves all D tangents, the D products
+//      are one MMA stacked along N, and the epilogue needs one FMA per tangent column;
+//   3. SIMT epilogue from TMEM: bias + tanh, the trace dot products (only the diagonal of the D x D Jacobian
+//      product is needed), layer 3; the two halves of a sample meet through shared memory; output rows; at the
+//      7th stage also the new state and the embedded-error partial sum.
 // Two such groups per CTA (one persistent CTA per SM, 16 worker warps) alternate, so the tensor pipe works
 // on one tile while the other group's SIMT phases run; a 17th warp issues the MMAs of both groups as
 // soon as a tile's 256 writers have arrived on its mbarrier.  The SIMT phases use the packed f32x2
 // instructions (FFMA2/FMUL2/FADD2): ~2.4 k instructions per sample instead of 17.7 k.
 #include "cnf_internal.h"
 #include "cnf_tc_ptx.cuh"
+#include <cmath>
 
 #define NTC_H 64            // hidden width (one 128-byte swizzle row of halves)
 #define NTC_GROUPS 2
@@ -26,7 +30,8 @@
 #define NTC_WORKERS (NTC_GT * NTC_GROUPS)
 #define NTC_THREADS (NTC_WORKERS + 32)   // + one warp that issues the MMAs of both groups
 #define NTC_PLANE_A (128 * NTC_H * 2)   // 16 KB: one plane of one operand vector
-#define NTC_PLANE_B (NTC_H * NTC_H * 2) // 8 KB: one plane of W2
+#define NTC_PLANE_B (NTC_H * NTC_H * 2) // 8 KB: one plane of W2 (or of one tangent matrix T_v)
+#define NTC_NVA 2                       // operand vectors written per tile: h1 and dn = h1^2 - 1
 #define NTC_C 2.8853900817779268f       // 2 log2(e): tanh(x) = 1 - 2 / (exp2(C x) + 1)
 
 // small weights per PAIR of hidden units (o, o+1) — the SIMT phases run on packed f32x2 instructions
@@ -38,20 +43,20 @@ struct alignas(16) NtcW {
     float4 l3w[NTC_H / 2];
     float2 l1b[NTC_H / 2];
     float2 l3v[NTC_H / 2];
-    float b3[4];
+    float b3[4];   // b3[0..D); b3[3] = 1 / (C S): undoes the factor C and the power-of-two scale S of the tangent planes
 };
 
 struct NtcState {
     NtcW* w_host = nullptr;
     NtcW* d_w = nullptr;
-    __half* d_w2 = nullptr;            // hi plane then lo plane, pre-swizzled K-major SWIZZLE_128B
+    __half* d_w2 = nullptr;            // W2 hi, W2 lo, T_1..T_D hi, T_1..T_D lo: 8 KB planes, pre-swizzled K-major SWIZZLE_128B
     int D = 0;
     int sms = 148;
 };
 
 template <int D>
 constexpr int ntc_smem_bytes() {
-    return 1024 + 2 * NTC_PLANE_B + NTC_GROUPS * (1 + D) * 2 * NTC_PLANE_A + (int)sizeof(NtcW) + NTC_GROUPS * 128 * 16 + 64;
+    return 1024 + (1 + D) * 2 * NTC_PLANE_B + NTC_GROUPS * NTC_NVA * 2 * NTC_PLANE_A + (int)sizeof(NtcW) + NTC_GROUPS * 128 * 16 + 64;
 }
 
 // byte offset of the 16-byte chunk `ch` (8 halves along K) of row `r` inside a SWIZZLE_128B K-major tile
@@ -125,13 +130,14 @@ k_stage_narrow_tc(const NtcW* __restrict__ wsmall, const __half* __restrict__ w2
                   CnfBufs bf, int stage, int check_done, int ntiles) {
     if (check_done && c->done) return;
     constexpr int R = D + 1;
-    constexpr int NV = 1 + D;                       // operand vectors: h1, tau1_1..tau1_D
+    constexpr int NV = 1 + D;                       // accumulator vectors: layer-2 pre-activation, D folded tangents
+    constexpr int NB_BYTES = (1 + D) * 2 * NTC_PLANE_B;
     extern __shared__ uint8_t ntc_raw[];
     const uint32_t sbase = (tc::smem_u32(ntc_raw) + 1023u) & ~1023u;
     uint8_t* sgen = ntc_raw + (sbase - tc::smem_u32(ntc_raw));
-    const uint32_t sB = sbase;                                       // W2 hi, lo planes
-    const uint32_t sA = sbase + 2 * NTC_PLANE_B;                     // [group][vector][plane]
-    uint8_t* after = sgen + 2 * NTC_PLANE_B + NTC_GROUPS * NV * 2 * NTC_PLANE_A;
+    const uint32_t sB = sbase;                                       // W2 hi, lo; T hi (D planes), T lo (D planes)
+    const uint32_t sA = sbase + NB_BYTES;                            // [group][vector h1 / dn][plane]
+    uint8_t* after = sgen + NB_BYTES + NTC_GROUPS * NTC_NVA * 2 * NTC_PLANE_A;
     const NtcW* sw = reinterpret_cast<const NtcW*>(after);
     float4* xch = reinterpret_cast<float4*>(after + sizeof(NtcW));   // [group][row]: partial sums of the upper half
     uint64_t* bars = reinterpret_cast<uint64_t*>(after + sizeof(NtcW) + NTC_GROUPS * 128 * 16);
@@ -148,7 +154,7 @@ k_stage_narrow_tc(const NtcW* __restrict__ wsmall, const __half* __restrict__ w2
     {
         const uint4* src = reinterpret_cast<const uint4*>(w2planes);
         uint4* dst = reinterpret_cast<uint4*>(sgen);
-        for (int i = tid; i < 2 * NTC_PLANE_B / 16; i += NTC_THREADS) dst[i] = src[i];
+        for (int i = tid; i < NB_BYTES / 16; i += NTC_THREADS) dst[i] = src[i];
         const uint4* src2 = reinterpret_cast<const uint4*>(wsmall);
         uint4* dst2 = reinterpret_cast<uint4*>(after);
         for (int i = tid; i < (int)sizeof(NtcW) / 16; i += NTC_THREADS) dst2[i] = src2[i];
@@ -164,7 +170,7 @@ k_stage_narrow_tc(const NtcW* __restrict__ wsmall, const __half* __restrict__ w2
     tc::tc_fence_after();
     const uint32_t tmem = *tmem_slot + (uint32_t)g * 256u;          // this group's accumulators: NV x 64 columns
     const uint32_t tlane = tmem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)hw * 32u;
-    const uint32_t myA = sA + (uint32_t)g * (NV * 2 * NTC_PLANE_A);
+    const uint32_t myA = sA + (uint32_t)g * (NTC_NVA * 2 * NTC_PLANE_A);
     const int barB = 1 + g;
 
     double acc = 0.0;
@@ -174,6 +180,7 @@ k_stage_narrow_tc(const NtcW* __restrict__ wsmall, const __half* __restrict__ w2
         // 3 MMAs per k-step (hi*hi + lo*hi + hi*lo), one commit per tile
         if ((tid & 31) == 0) {
             const uint32_t idesc = tc::umma_idesc_f16(128, NTC_H, 0);
+            const uint32_t idesc_t = tc::umma_idesc_f16(128, NTC_H * D, 0);   // the D tangent products stacked along N
             const uint64_t dhi = (uint64_t)(tc::umma_desc_sw128(0) >> 32) << 32;
             const uint32_t blo0 = (uint32_t)tc::umma_desc_sw128(sB);
             int left[NTC_GROUPS];
@@ -190,19 +197,23 @@ k_stage_narrow_tc(const NtcW* __restrict__ wsmall, const __half* __restrict__ w2
                 for (int q = 0; q < NTC_GROUPS; ++q) {
                     if (left[q] > 0 && tc::mbar_try_wait(&full[q], ph[q])) {
                         tc::tc_fence_after();
-                        const uint32_t alo0 = (uint32_t)tc::umma_desc_sw128(sA + (uint32_t)q * (NV * 2 * NTC_PLANE_A));
+                        const uint32_t alo0 = (uint32_t)tc::umma_desc_sw128(sA + (uint32_t)q * (NTC_NVA * 2 * NTC_PLANE_A));
                         const uint32_t tq = *tmem_slot + (uint32_t)q * 256u;
 #pragma unroll
-                        for (int v = 0; v < NV; ++v) {
+                        for (int v = 0; v < NTC_NVA; ++v) {
+                            // v = 0: h1 x W2 -> columns [0, 64); v = 1: dn x [T_1; ..; T_D] -> columns [64, 64 + 64 D)
+                            const uint32_t bhi0 = v == 0 ? 0u : 2u * NTC_PLANE_B;
+                            const uint32_t blo0b = v == 0 ? (uint32_t)NTC_PLANE_B : (2u + D) * NTC_PLANE_B;
+                            const uint32_t id = v == 0 ? idesc : idesc_t;
 #pragma unroll
                             for (int kk = 0; kk < NTC_H / 16; ++kk) {
                                 const uint64_t ahi = dhi | (alo0 + (uint32_t)(((v * 2) * NTC_PLANE_A + kk * 32) >> 4));
                                 const uint64_t alo = dhi | (alo0 + (uint32_t)(((v * 2 + 1) * NTC_PLANE_A + kk * 32) >> 4));
-                                const uint64_t bhi = dhi | (blo0 + (uint32_t)((kk * 32) >> 4));
-                                const uint64_t blo = dhi | (blo0 + (uint32_t)((NTC_PLANE_B + kk * 32) >> 4));
-                                tc::umma_bf16(tq + v * NTC_H, ahi, bhi, idesc, kk != 0);
-                                tc::umma_bf16(tq + v * NTC_H, alo, bhi, idesc, 1);
-                                tc::umma_bf16(tq + v * NTC_H, ahi, blo, idesc, 1);
+                                const uint64_t bhi = dhi | (blo0 + (uint32_t)((bhi0 + kk * 32) >> 4));
+                                const uint64_t blo = dhi | (blo0 + (uint32_t)((blo0b + kk * 32) >> 4));
+                                tc::umma_bf16(tq + v * NTC_H, ahi, bhi, id, kk != 0);
+                                tc::umma_bf16(tq + v * NTC_H, alo, bhi, id, 1);
+                                tc::umma_bf16(tq + v * NTC_H, ahi, blo, id, 1);
                             }
                         }
                         tc::umma_commit(&bars[q]);
@@ -274,26 +285,23 @@ k_stage_narrow_tc(const NtcW* __restrict__ wsmall, const __half* __restrict__ w2
                 if (rr < D) z[rr < D ? rr : 0] = v;
             }
         }
-        // ---- layer 1 and the D one-hot tangents (scaled by -C: dn = h^2 - 1) of this thread's 32 hidden units,
-        // two units per instruction -> hi/lo operand planes in shared memory
+        // ---- layer 1 of this thread's 32 hidden units, two units per instruction: h1 and dn = h1^2 - 1 (the operand of
+        // every tangent product, see the header) -> hi/lo operand planes in shared memory
         const float2 z0 = make_float2(z[0], z[0]), z1 = make_float2(z[D > 1 ? 1 : 0], z[D > 1 ? 1 : 0]);
 #pragma unroll
         for (int cq = 0; cq < 4; ++cq) {
             const int cb = hw * 4 + cq;
-            float2 x[NV][4];
+            float2 x[NTC_NVA][4];
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
                 const float4 w = sw->l1w[cb * 4 + q];
                 float2 a = ntc_fma2(make_float2(w.x, w.y), z0, sw->l1b[cb * 4 + q]);
                 if (D > 1) a = ntc_fma2(make_float2(w.z, w.w), z1, a);
-                float2 dn;
-                ntc_tanh2(a, x[0][q], dn);
-                x[1][q] = ntc_mul2(make_float2(w.x, w.y), dn);
-                if (D > 1) x[D > 1 ? 2 : 1][q] = ntc_mul2(make_float2(w.z, w.w), dn);
+                ntc_tanh2(a, x[0][q], x[1][q]);
             }
             const uint32_t off = ntc_swz(r, cb);
 #pragma unroll
-            for (int v = 0; v < NV; ++v) {
+            for (int v = 0; v < NTC_NVA; ++v) {
                 uint32_t hi[4], lo[4];
 #pragma unroll
                 for (int q = 0; q < 4; ++q) ntc_split2(x[v][q], hi[q], lo[q]);
@@ -306,33 +314,36 @@ k_stage_narrow_tc(const NtcW* __restrict__ wsmall, const __half* __restrict__ w2
         tc::mbar_arrive(&full[g]);   // the issuer warp starts this tile's MMAs after all 256 arrivals
         // ---- next tile's operands: in flight during the MMA wait and the epilogue
         if (tile + tstride < ntiles) load_raw(tile + tstride);
-        // ---- epilogue on this thread's 32 columns: tanh, tangent scaling, layer 3 (diagonal of the
-        // Jacobian product only; the tangents carry the factor C until the end)
-        // (both the tangents and dn carry a minus sign: their product does not)
+        // ---- epilogue on this thread's 32 columns: tanh, layer 3, and the trace dot products: accumulator column o
+        // of tangent v already holds W3[v][o] (W2 diag(C W1[:, v]) dn1)[o], so the diagonal of the Jacobian product is
+        // its dot product with dn2 (both dn carry a minus sign: their product does not; the factor C leaves at the end)
         float2 p3a = make_float2(0.0f, 0.0f), p3b = p3a, r3a = p3a, r3b = p3a;   // even / odd hidden units
         ntc_wait_sleep(&bars[g], it & 1);
         __syncwarp();
         tc::tc_fence_after();
+        uint32_t va[2][NV][8];       // chunk ch + 1 is in flight while chunk ch is consumed
+#pragma unroll
+        for (int v = 0; v < NV; ++v) tc::tmem_ld_32x8(tlane + v * NTC_H, va[0][v]);
 #pragma unroll
         for (int ch = 0; ch < 4; ++ch) {
-            uint32_t va[NV][8];
-#pragma unroll
-            for (int v = 0; v < NV; ++v) tc::tmem_ld_32x8(tlane + v * NTC_H + ch * 8, va[v]);
+            const int cur = ch & 1;
             tc::tmem_ld_wait();
+            if (ch + 1 < 4) {
+#pragma unroll
+                for (int v = 0; v < NV; ++v) tc::tmem_ld_32x8(tlane + v * NTC_H + (ch + 1) * 8, va[cur ^ 1][v]);
+            }
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
                 const float4 w = sw->l3w[hw * 16 + ch * 4 + q];
                 float2 h, dn;
-                ntc_tanh2(ntc_fma2(make_float2(__uint_as_float(va[0][2 * q]), __uint_as_float(va[0][2 * q + 1])),
+                ntc_tanh2(ntc_fma2(make_float2(__uint_as_float(va[cur][0][2 * q]), __uint_as_float(va[cur][0][2 * q + 1])),
                                    make_float2(NTC_C, NTC_C), make_float2(w.x, w.y)), h, dn);
                 p3a = ntc_fma2(make_float2(w.z, w.w), h, p3a);
-                r3a = ntc_fma2(make_float2(w.z, w.w),
-                               ntc_mul2(make_float2(__uint_as_float(va[1][2 * q]), __uint_as_float(va[1][2 * q + 1])), dn), r3a);
+                r3a = ntc_fma2(make_float2(__uint_as_float(va[cur][1][2 * q]), __uint_as_float(va[cur][1][2 * q + 1])), dn, r3a);
                 if (D > 1) {
-                    const float2 w1 = sw->l3v[hw * 16 + ch * 4 + q];
-                    p3b = ntc_fma2(w1, h, p3b);
-                    r3b = ntc_fma2(w1, ntc_mul2(make_float2(__uint_as_float(va[D > 1 ? 2 : 1][2 * q]),
-                                                            __uint_as_float(va[D > 1 ? 2 : 1][2 * q + 1])), dn), r3b);
+                    p3b = ntc_fma2(sw->l3v[hw * 16 + ch * 4 + q], h, p3b);
+                    r3b = ntc_fma2(make_float2(__uint_as_float(va[cur][D > 1 ? 2 : 1][2 * q]),
+                                               __uint_as_float(va[cur][D > 1 ? 2 : 1][2 * q + 1])), dn, r3b);
                 }
             }
         }
@@ -354,7 +365,7 @@ k_stage_narrow_tc(const NtcW* __restrict__ wsmall, const __half* __restrict__ w2
 #pragma unroll
         for (int j = 0; j < D; ++j) {
             y[j] = cnf_tanh_fastpath(p3[j] + sw->b3[j]);
-            tr -= fmaf(-y[j], y[j], 1.0f) * (r3[j] * (1.0f / NTC_C));
+            tr -= fmaf(-y[j], y[j], 1.0f) * (r3[j] * sw->b3[3]);
         }
 #pragma unroll
         for (int j = 0; j < D; ++j) kout[(long long)j * Bs + b] = y[j];
@@ -400,15 +411,32 @@ static void ntc_pack(const cnf_handle* h, const float* theta, NtcW* out, __half*
         out->l3v[p] = D > 1 ? make_float2(W3[o * D + 1], W3[(o + 1) * D + 1]) : make_float2(0.0f, 0.0f);
     }
     for (int j = 0; j < D; ++j) out->b3[j] = theta[h->b_off[2] + j];
-    // B operand: row n = output unit, K = input unit; K-major SWIZZLE_128B (same layout as ntc_swz)
+    // B operands: row n = output unit, K = input unit; K-major SWIZZLE_128B (same layout as ntc_swz).  Plane order:
+    // W2 hi, W2 lo, T_1..T_D hi, T_1..T_D lo with T_v[n][k] = W3[v][n] W2[n][k] C W1[k][v] (the D hi planes are
+    // contiguous, so they are ONE operand of 64 D rows: SBO = 1024 bytes per 8 rows runs across the plane boundary)
+    // The products are small (three weights): scaled by a power of two S so that the largest is in [4096, 8192) and the
+    // lo words stay clear of the half subnormals (absolute resolution 6e-8 would cost 3-4 bits of T otherwise)
+    const size_t PH = NTC_PLANE_B / 2;   // halves per plane
+    double tmax = 0.0;
+    for (int n = 0; n < NTC_H; ++n)
+        for (int k = 0; k < NTC_H; ++k)
+            for (int v = 0; v < D; ++v)
+                tmax = fmax(tmax, fabs((double)W3[n * D + v] * (double)W2[k * NTC_H + n] * ((double)NTC_C * (double)W1[v * NTC_H + k])));
+    const double S = (tmax > 0.0 && std::isfinite(tmax)) ? exp2(floor(log2(8192.0 / tmax))) : 1.0;
+    out->b3[3] = (float)(1.0 / ((double)NTC_C * S));
     for (int n = 0; n < NTC_H; ++n)
         for (int k = 0; k < NTC_H; ++k) {
+            const size_t off = (size_t)(n >> 3) * 512 + (n & 7) * 64 + (((k >> 3) ^ (n & 7)) << 3) + (k & 7);   // in halves
             const float w = W2[k * NTC_H + n];
             const __half hi = __float2half_rn(w);
-            const __half lo = __float2half_rn(w - __half2float(hi));
-            const size_t off = (size_t)(n >> 3) * 512 + (n & 7) * 64 + (((k >> 3) ^ (n & 7)) << 3) + (k & 7);   // in halves
             planes[off] = hi;
-            planes[NTC_PLANE_B / 2 + off] = lo;
+            planes[PH + off] = __float2half_rn(w - __half2float(hi));
+            for (int v = 0; v < D; ++v) {
+                const float t = (float)(S * (double)W3[n * D + v] * (double)w * ((double)NTC_C * (double)W1[v * NTC_H + k]));
+                const __half thi = __float2half_rn(t);
+                planes[(2 + v) * PH + off] = thi;
+                planes[(2 + D + v) * PH + off] = __float2half_rn(t - __half2float(thi));
+            }
         }
 }
 
@@ -432,14 +460,15 @@ int ntc_set_params(cnf_handle* h, const float* theta_host) {
         s->w_host = new NtcW();
         h->ntc_state = s;
         CNF_CUDA(cudaMalloc(&s->d_w, sizeof(NtcW)));
-        CNF_CUDA(cudaMalloc(&s->d_w2, 2 * NTC_PLANE_B));
+        CNF_CUDA(cudaMalloc(&s->d_w2, (1 + 2) * 2 * NTC_PLANE_B));   // sized for D = 2
         CNF_CUDA(cudaFuncSetAttribute(k_stage_narrow_tc<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ntc_smem_bytes<1>()));
         CNF_CUDA(cudaFuncSetAttribute(k_stage_narrow_tc<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, ntc_smem_bytes<2>()));
     }
-    std::vector<__half> planes(NTC_PLANE_B);   // 2 planes x NTC_PLANE_B / 2 halves
+    const size_t plane_bytes = (size_t)(1 + s->D) * 2 * NTC_PLANE_B;
+    std::vector<__half> planes(plane_bytes / 2);
     ntc_pack(h, theta_host, s->w_host, planes.data());
     CNF_CUDA(cudaMemcpyAsync(s->d_w, s->w_host, sizeof(NtcW), cudaMemcpyHostToDevice, h->stream));
-    CNF_CUDA(cudaMemcpyAsync(s->d_w2, planes.data(), 2 * NTC_PLANE_B, cudaMemcpyHostToDevice, h->stream));
+    CNF_CUDA(cudaMemcpyAsync(s->d_w2, planes.data(), plane_bytes, cudaMemcpyHostToDevice, h->stream));
     CNF_CUDA(cudaStreamSynchronize(h->stream));
     return CNF_OK;
 }
