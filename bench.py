@@ -63,6 +63,8 @@ def parse():
     p.add_argument("--no-parity", action="store_true")
     p.add_argument("--no-extra", action="store_true", help="default run without the train / strong-scaling blocks")
     p.add_argument("--cpu-sample", type=int, default=0)
+    p.add_argument("--tc-dbg", type=int, default=0, help="debug / timing-experiment bits of the tensor-core kernels (option tc_dbg)")
+    p.add_argument("--stage-sample", type=int, default=7, help="time every N-th stage-kernel launch with CUDA events (1 = all)")
     return p.parse_args()
 
 
@@ -260,7 +262,12 @@ def run_leg(ctx, cid, kind, B, steps, warmup, strong=False, want_cpu=True, want_
     icnf = make_model(cnf, cid, local, args.kernel_path, args.compute_mode == "vector")
     if world > 1:
         cnf.parallel.init_comm(icnf, rank, world)
-    cnf.set_option(icnf, "time_stages", 1)
+    # every N-th stage launch of the timed region is bracketed by CUDA events on the library's stream (N = 7 walks
+    # through all stage indices of the 6-stage attempts): timing every launch costs two event records per launch,
+    # several per cent of a C2 step, and the record would then measure its own instrumentation
+    cnf.set_option(icnf, "time_stages", max(1, args.stage_sample))
+    if args.tc_dbg:
+        cnf.set_option(icnf, "tc_dbg", args.tc_dbg)
     mode = cnf.TrainMode() if kind in ("train", "hutchinson") else cnf.TestMode()
     xs_d = torch.from_numpy(inp["xs"]).to(dev).t()
     ys_d = torch.from_numpy(inp["ys"]).to(dev).t() if inp["ys"] is not None else None
@@ -507,8 +514,9 @@ def make_roofline(ctx, cid, kind, B, st, ms_stage, n_stage, ms_solve, ms_dev, st
     path = st["kernel_path"]
     common = {"traffic": traffic, "traffic_source": "static: dram__bytes_read+write per launch from the committed ncu --set full "
               "capture of this kernel (profiles/traffic.json), not measured in this run" if traffic else None,
-              "stage_ms": stage_ms, "stage_launches": n_stage, "kernel_path": path,
-              "stage_share_of_step": ms_stage / ms_dev if ms_dev else None,
+              "stage_ms": stage_ms, "stage_launches_timed": n_stage, "stage_sampling": f"every {max(1, ctx.args.stage_sample)}-th stage launch of the timed steps",
+              "kernel_path": path,
+              "stage_share_of_step": stage_ms * st["nf"] * steps / ms_dev if ms_dev else None,
               "algorithmic_flops_per_eval": flops_eval,
               "algorithmic_bytes_per_eval": (2 * R + D) * 4 * B,
               "algorithmic_gbs": (2 * R + D) * 4 * B / (stage_ms * 1e-3) / 1e9 if stage_ms > 0 else None}

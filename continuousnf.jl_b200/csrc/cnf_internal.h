@@ -69,7 +69,9 @@ struct cnf_handle {
     bool p2p_ok = false;
     long long launches = 0;
     // optional per-stage-kernel timing (cnfb200_set_option "time_stages")
-    bool time_stages = false;
+    int time_stages = 0;         // 0 off; N: every N-th stage launch is timed
+    unsigned long long stage_seq = 0;
+    bool stage_timed_now = false;
     std::vector<cudaEvent_t> stage_ev;
     size_t stage_ev_used = 0;
     double ms_stage = 0.0;

@@ -69,9 +69,9 @@ __device__ __forceinline__ void ntc_sts128(uint32_t addr, const uint32_t (&v)[4]
 __device__ __forceinline__ void ntc_bar_sync(int id) { asm volatile("bar.sync %0, 256;" ::"r"(id) : "memory"); }
 __device__ __forceinline__ void ntc_bar_arrive(int id) { asm volatile("bar.arrive %0, 256;" ::"r"(id) : "memory"); }
 // wait with back-off: a spinning try_wait loop takes issue slots from the other group's warps on the same scheduler
-__device__ __forceinline__ void ntc_wait_sleep(uint64_t* bar, uint32_t parity) {
+__device__ __forceinline__ void ntc_wait_sleep(uint64_t* bar, uint32_t parity, int nosleep = 0) {
     for (uint32_t it = 0; !tc::mbar_try_wait(bar, parity); ++it) {
-        __nanosleep(64);
+        if (!nosleep) __nanosleep(64);
         if (it > (1u << 24)) { asm volatile("trap;"); }
     }
 }
@@ -127,7 +127,7 @@ __device__ __forceinline__ float ntc_tanh_scaled(float cx) {
 template <int D>
 __global__ void __maxnreg__(96)
 k_stage_narrow_tc(const NtcW* __restrict__ wsmall, const __half* __restrict__ w2planes, CnfCtrl* __restrict__ c,
-                  CnfBufs bf, int stage, int check_done, int ntiles) {
+                  CnfBufs bf, int stage, int check_done, int ntiles, int dbg) {
     if (check_done && c->done) return;
     constexpr int R = D + 1;
     constexpr int NV = 1 + D;                       // accumulator vectors: layer-2 pre-activation, D folded tangents
@@ -142,7 +142,8 @@ k_stage_narrow_tc(const NtcW* __restrict__ wsmall, const __half* __restrict__ w2
     float4* xch = reinterpret_cast<float4*>(after + sizeof(NtcW));   // [group][row]: partial sums of the upper half
     uint64_t* bars = reinterpret_cast<uint64_t*>(after + sizeof(NtcW) + NTC_GROUPS * 128 * 16);
     uint64_t* full = bars + NTC_GROUPS;   // operand planes of a tile written (256 arrivals)
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * NTC_GROUPS);
+    uint64_t* bars0 = bars + 2 * NTC_GROUPS;   // the h1 x W2 product of a tile is complete (bars: the tangent product too)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3 * NTC_GROUPS);
     __shared__ double sh_red[32];
 
     const int tid = threadIdx.x, warp = tid >> 5;
@@ -160,7 +161,7 @@ k_stage_narrow_tc(const NtcW* __restrict__ wsmall, const __half* __restrict__ w2
         for (int i = tid; i < (int)sizeof(NtcW) / 16; i += NTC_THREADS) dst2[i] = src2[i];
     }
     if (tid == 0) {
-        for (int i = 0; i < NTC_GROUPS; ++i) { tc::mbar_init(&bars[i], 1); tc::mbar_init(&full[i], NTC_GT); }
+        for (int i = 0; i < NTC_GROUPS; ++i) { tc::mbar_init(&bars[i], 1); tc::mbar_init(&bars0[i], 1); tc::mbar_init(&full[i], NTC_GT); }
         tc::fence_barrier_init();
     }
     if (warp == 0) tc::tmem_alloc(tmem_slot, 512);
@@ -215,8 +216,10 @@ k_stage_narrow_tc(const NtcW* __restrict__ wsmall, const __half* __restrict__ w2
                                 tc::umma_bf16(tq + v * NTC_H, alo, bhi, id, 1);
                                 tc::umma_bf16(tq + v * NTC_H, ahi, blo, id, 1);
                             }
+                            // two commits: the epilogue's tanh half starts on the layer-2 pre-activations while the
+                            // (twice as long) tangent product is still running
+                            tc::umma_commit(v == 0 ? &bars0[q] : &bars[q]);
                         }
-                        tc::umma_commit(&bars[q]);
                         ph[q] ^= 1;
                         left[q]--;
                         spins = 0;
@@ -318,32 +321,46 @@ k_stage_narrow_tc(const NtcW* __restrict__ wsmall, const __half* __restrict__ w2
         // of tangent v already holds W3[v][o] (W2 diag(C W1[:, v]) dn1)[o], so the diagonal of the Jacobian product is
         // its dot product with dn2 (both dn carry a minus sign: their product does not; the factor C leaves at the end)
         float2 p3a = make_float2(0.0f, 0.0f), p3b = p3a, r3a = p3a, r3b = p3a;   // even / odd hidden units
-        ntc_wait_sleep(&bars[g], it & 1);
+        float2 dn2[16];              // dn of this thread's 32 layer-2 units, kept for the tangent half
+        ntc_wait_sleep(&bars0[g], it & 1, dbg & 32);
         __syncwarp();
         tc::tc_fence_after();
-        uint32_t va[2][NV][8];       // chunk ch + 1 is in flight while chunk ch is consumed
+        {
+            uint32_t va[2][8];       // chunk ch + 1 is in flight while chunk ch is consumed
+            tc::tmem_ld_32x8(tlane, va[0]);
 #pragma unroll
-        for (int v = 0; v < NV; ++v) tc::tmem_ld_32x8(tlane + v * NTC_H, va[0][v]);
+            for (int ch = 0; ch < 4; ++ch) {
+                const int cur = ch & 1;
+                tc::tmem_ld_wait();
+                if (ch + 1 < 4) tc::tmem_ld_32x8(tlane + (ch + 1) * 8, va[cur ^ 1]);
 #pragma unroll
-        for (int ch = 0; ch < 4; ++ch) {
-            const int cur = ch & 1;
-            tc::tmem_ld_wait();
-            if (ch + 1 < 4) {
-#pragma unroll
-                for (int v = 0; v < NV; ++v) tc::tmem_ld_32x8(tlane + v * NTC_H + (ch + 1) * 8, va[cur ^ 1][v]);
+                for (int q = 0; q < 4; ++q) {
+                    const float4 w = sw->l3w[hw * 16 + ch * 4 + q];
+                    float2 h;
+                    ntc_tanh2(ntc_fma2(make_float2(__uint_as_float(va[cur][2 * q]), __uint_as_float(va[cur][2 * q + 1])),
+                                       make_float2(NTC_C, NTC_C), make_float2(w.x, w.y)), h, dn2[ch * 4 + q]);
+                    p3a = ntc_fma2(make_float2(w.z, w.w), h, p3a);
+                    if (D > 1) p3b = ntc_fma2(sw->l3v[hw * 16 + ch * 4 + q], h, p3b);
+                }
             }
+        }
+        ntc_wait_sleep(&bars[g], it & 1, dbg & 32);
+        __syncwarp();
+        tc::tc_fence_after();
+        {
+            // (single-buffered: by now the tangent product has long finished, and 16 more registers would spill)
+            uint32_t va[D][8];
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const float4 w = sw->l3w[hw * 16 + ch * 4 + q];
-                float2 h, dn;
-                ntc_tanh2(ntc_fma2(make_float2(__uint_as_float(va[cur][0][2 * q]), __uint_as_float(va[cur][0][2 * q + 1])),
-                                   make_float2(NTC_C, NTC_C), make_float2(w.x, w.y)), h, dn);
-                p3a = ntc_fma2(make_float2(w.z, w.w), h, p3a);
-                r3a = ntc_fma2(make_float2(__uint_as_float(va[cur][1][2 * q]), __uint_as_float(va[cur][1][2 * q + 1])), dn, r3a);
-                if (D > 1) {
-                    p3b = ntc_fma2(sw->l3v[hw * 16 + ch * 4 + q], h, p3b);
-                    r3b = ntc_fma2(make_float2(__uint_as_float(va[cur][D > 1 ? 2 : 1][2 * q]),
-                                               __uint_as_float(va[cur][D > 1 ? 2 : 1][2 * q + 1])), dn, r3b);
+            for (int ch = 0; ch < 4; ++ch) {
+#pragma unroll
+                for (int v = 0; v < D; ++v) tc::tmem_ld_32x8(tlane + (1 + v) * NTC_H + ch * 8, va[v]);
+                tc::tmem_ld_wait();
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    r3a = ntc_fma2(make_float2(__uint_as_float(va[0][2 * q]), __uint_as_float(va[0][2 * q + 1])), dn2[ch * 4 + q], r3a);
+                    if (D > 1)
+                        r3b = ntc_fma2(make_float2(__uint_as_float(va[D > 1 ? 1 : 0][2 * q]),
+                                                   __uint_as_float(va[D > 1 ? 1 : 0][2 * q + 1])), dn2[ch * 4 + q], r3b);
                 }
             }
         }
@@ -489,10 +506,10 @@ int launch_stage_narrow_tc(cnf_handle* h, const CnfBufs& bf, int stage, int chec
     if (grid > s->sms) grid = s->sms;
     if (s->D == 1)
         k_stage_narrow_tc<1><<<grid, NTC_THREADS, ntc_smem_bytes<1>(), h->stream>>>(s->d_w, s->d_w2, h->d_ctrl, bf, stage,
-                                                                                   check_done, ntiles);
+                                                                                   check_done, ntiles, h->tc_dbg);
     else
         k_stage_narrow_tc<2><<<grid, NTC_THREADS, ntc_smem_bytes<2>(), h->stream>>>(s->d_w, s->d_w2, h->d_ctrl, bf, stage,
-                                                                                   check_done, ntiles);
+                                                                                   check_done, ntiles, h->tc_dbg);
     h->launches++;
     return CNF_OK;
 }

@@ -106,7 +106,8 @@ CNF_API const char* cnfb200_version(void);
 /* replaces construct(...) bookkeeping on the device side (src/base_icnf.jl:1-77) */
 CNF_API int32_t cnfb200_create(const cnf_config* cfg, cnf_handle** out);
 CNF_API int32_t cnfb200_destroy(cnf_handle* h);
-/* runtime options: "time_stages" (0/1: CUDA-event timing of every stage kernel -> cnf_stats.ms_stage),
+/* runtime options: "time_stages" (0 off; N >= 1: CUDA-event timing of every N-th stage-kernel launch ->
+ * cnf_stats.ms_stage / n_stage; N = 1 times all of them, at the cost of two event records per launch),
  * "kernel_path" (0 auto, 1 generic, 2 narrow, 3 tcgen05) */
 CNF_API int32_t cnfb200_set_option(cnf_handle* h, const char* key, int64_t value);
 CNF_API const char* cnfb200_last_error(const cnf_handle* h);
