@@ -64,7 +64,7 @@ def parse():
     p.add_argument("--no-extra", action="store_true", help="default run without the train / strong-scaling blocks")
     p.add_argument("--cpu-sample", type=int, default=0)
     p.add_argument("--tc-dbg", type=int, default=0, help="debug / timing-experiment bits of the tensor-core kernels (option tc_dbg)")
-    p.add_argument("--stage-sample", type=int, default=7, help="time every N-th stage-kernel launch with CUDA events (1 = all)")
+    p.add_argument("--stage-sample", type=int, default=13, help="time every N-th stage-kernel launch with CUDA events (1 = all)")
     return p.parse_args()
 
 
@@ -76,26 +76,65 @@ class ClockSampler:
 
     def __init__(self, index):
         self.rows, self.proc, self.index = [], None, index
+        self.nvml, self.t, self.stop_flag = None, None, False
 
     def start(self):
+        # in-process NVML (one cheap library call per sample) when the binding is there: eight ranks that each run
+        # `nvidia-smi -lms 50` put 160 driver queries per second beside the timed host<->device copies
+        try:
+            import pynvml
+            import torch
+            pynvml.nvmlInit()
+            try:
+                uuid = str(torch.cuda.get_device_properties(self.index).uuid)
+                hnd = pynvml.nvmlDeviceGetHandleByUUID(uuid if uuid.startswith("GPU-") else "GPU-" + uuid)
+            except Exception:
+                hnd = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            self.nvml = (pynvml, hnd)
+            self.t = threading.Thread(target=self._poll, daemon=True)
+            self.t.start()
+            return
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "50",
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
                  "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
         except OSError:
             self.proc = None
 
+    def _poll(self):
+        nv, hnd = self.nvml
+        bits = [("hw_slowdown", nv.nvmlClocksEventReasonHwSlowdown), ("hw_thermal_slowdown", nv.nvmlClocksEventReasonHwThermalSlowdown),
+                ("sw_thermal_slowdown", nv.nvmlClocksEventReasonSwThermalSlowdown), ("sw_power_cap", nv.nvmlClocksEventReasonSwPowerCap)]
+        try:
+            mx = nv.nvmlDeviceGetMaxClockInfo(hnd, nv.NVML_CLOCK_SM)
+        except Exception:
+            mx = 0
+        while not self.stop_flag:
+            try:
+                sm = nv.nvmlDeviceGetClockInfo(hnd, nv.NVML_CLOCK_SM)
+                mask = nv.nvmlDeviceGetCurrentClocksEventReasons(hnd)
+                self.rows.append([str(sm), str(mx), "0"] + ["Active" if mask & b else "Not Active" for _, b in bits])
+            except Exception:
+                pass
+            time.sleep(0.025)
+
     def _read(self):
         for line in self.proc.stdout:
             self.rows.append([x.strip() for x in line.split(",")])
 
     def stop(self):
-        if not self.proc:
+        if self.nvml:
+            self.stop_flag = True
+            self.t.join(timeout=2)
+        elif not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        self.t.join(timeout=2)
+        else:
+            self.proc.terminate()
+            self.t.join(timeout=2)
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for r in self.rows:
@@ -110,7 +149,7 @@ class ClockSampler:
         busy = [x for x in sm if x > 0.5 * max(mx)] if mx else sm
         return {"sm_mhz": float(np.median(busy or sm)) if sm else None,
                 "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
-                "samples": len(sm)}
+                "samples": len(sm), "source": "NVML in-process, 25 ms" if self.nvml else "nvidia-smi -lms 200"}
 
 
 def make_model(cnf, cid, device, kernel_path, vector=False):
@@ -262,9 +301,9 @@ def run_leg(ctx, cid, kind, B, steps, warmup, strong=False, want_cpu=True, want_
     icnf = make_model(cnf, cid, local, args.kernel_path, args.compute_mode == "vector")
     if world > 1:
         cnf.parallel.init_comm(icnf, rank, world)
-    # every N-th stage launch of the timed region is bracketed by CUDA events on the library's stream (N = 7 walks
+    # every N-th stage launch of the timed region is bracketed by CUDA events on the library's stream (N = 13 walks
     # through all stage indices of the 6-stage attempts): timing every launch costs two event records per launch,
-    # several per cent of a C2 step, and the record would then measure its own instrumentation
+    # several per cent of a C2 step (and a bracketed launch loses its programmatic overlap with its neighbours)
     cnf.set_option(icnf, "time_stages", max(1, args.stage_sample))
     if args.tc_dbg:
         cnf.set_option(icnf, "tc_dbg", args.tc_dbg)

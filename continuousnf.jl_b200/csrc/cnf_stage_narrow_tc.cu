@@ -128,7 +128,6 @@ template <int D>
 __global__ void __maxnreg__(96)
 k_stage_narrow_tc(const NtcW* __restrict__ wsmall, const __half* __restrict__ w2planes, CnfCtrl* __restrict__ c,
                   CnfBufs bf, int stage, int check_done, int ntiles, int dbg) {
-    if (check_done && c->done) return;
     constexpr int R = D + 1;
     constexpr int NV = 1 + D;                       // accumulator vectors: layer-2 pre-activation, D folded tangents
     constexpr int NB_BYTES = (1 + D) * 2 * NTC_PLANE_B;
@@ -174,9 +173,18 @@ k_stage_narrow_tc(const NtcW* __restrict__ wsmall, const __half* __restrict__ w2
     const uint32_t myA = sA + (uint32_t)g * (NTC_NVA * 2 * NTC_PLANE_A);
     const int barB = 1 + g;
 
+    // Programmatic dependent launch: everything above touches only this launch's own resources (weights, barriers,
+    // tensor memory), so it may run while the previous kernel of the stream is still finishing on other SMs; the
+    // controller block and the stage rows are read only after the wait.  (No-ops when launched without the attribute.)
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    const bool skip = check_done && c->done;
+
     double acc = 0.0;
     const int tile0 = blockIdx.x * NTC_GROUPS + g, tstride = gridDim.x * NTC_GROUPS;
-    if (warp == NTC_WORKERS / 32) {
+    if (skip) {
+        // the solve has finished: a speculative launch
+    } else if (warp == NTC_WORKERS / 32) {
         // ---- MMA issuer: layer 2 for all operand vectors of a tile as soon as its planes are written;
         // 3 MMAs per k-step (hi*hi + lo*hi + hi*lo), one commit per tile
         if ((tid & 31) == 0) {
@@ -402,7 +410,7 @@ k_stage_narrow_tc(const NtcW* __restrict__ wsmall, const __half* __restrict__ w2
     }
     }   // workers
     tc::tc_fence_before();
-    if (stage == 6) {
+    if (stage == 6 && !skip) {
         acc = cnf_block_sum(acc, sh_red);
         if (tid == 0) atomicAdd(&c->errsum, acc);
     }
@@ -504,12 +512,25 @@ int launch_stage_narrow_tc(cnf_handle* h, const CnfBufs& bf, int stage, int chec
     const int ntiles = (int)(bf.Bs / 128);
     int grid = (ntiles + NTC_GROUPS - 1) / NTC_GROUPS;
     if (grid > s->sms) grid = s->sms;
+    // launched with programmatic stream serialization: the prologue of this launch (weights into shared memory,
+    // barriers, tensor-memory allocation) overlaps the tail of the previous stage kernel (option tc_dbg & 64: off)
+    cudaLaunchConfig_t lc;
+    memset(&lc, 0, sizeof(lc));
+    lc.gridDim = dim3((unsigned)grid);
+    lc.blockDim = dim3(NTC_THREADS);
+    lc.dynamicSmemBytes = (size_t)(s->D == 1 ? ntc_smem_bytes<1>() : ntc_smem_bytes<2>());
+    lc.stream = h->stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    lc.attrs = at;
+    lc.numAttrs = (h->tc_dbg & 64) ? 0 : 1;
+    const NtcW* dw = s->d_w;
+    const __half* dw2 = s->d_w2;
     if (s->D == 1)
-        k_stage_narrow_tc<1><<<grid, NTC_THREADS, ntc_smem_bytes<1>(), h->stream>>>(s->d_w, s->d_w2, h->d_ctrl, bf, stage,
-                                                                                   check_done, ntiles, h->tc_dbg);
+        CNF_CUDA(cudaLaunchKernelEx(&lc, k_stage_narrow_tc<1>, dw, dw2, h->d_ctrl, bf, stage, check_done, ntiles, h->tc_dbg));
     else
-        k_stage_narrow_tc<2><<<grid, NTC_THREADS, ntc_smem_bytes<2>(), h->stream>>>(s->d_w, s->d_w2, h->d_ctrl, bf, stage,
-                                                                                   check_done, ntiles, h->tc_dbg);
+        CNF_CUDA(cudaLaunchKernelEx(&lc, k_stage_narrow_tc<2>, dw, dw2, h->d_ctrl, bf, stage, check_done, ntiles, h->tc_dbg));
     h->launches++;
     return CNF_OK;
 }
