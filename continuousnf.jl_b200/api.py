@@ -321,36 +321,47 @@ class _Mat:
 class _PinnedPool:
     """page-locked host buffers for output matrices (cnfb200_host_alloc): the device->host copy of a result
     runs at PCIe rate into them, ~6x faster than into pageable numpy memory.  A buffer goes back to the pool
-    when the array that wraps it is garbage-collected; small outputs stay ordinary numpy arrays."""
+    when the array that wraps it is garbage-collected; small outputs stay ordinary numpy arrays.  Sizes are
+    rounded up to powers of two (so varying batch sizes share buffers) and the pool never keeps more than
+    MAX_FREE_BYTES of idle page-locked memory: beyond that a returned buffer is freed."""
     MIN_BYTES = 1 << 16
-    MAX_KEEP = 8        # free buffers kept per size
+    MAX_KEEP = 8                 # free buffers kept per size class
+    MAX_FREE_BYTES = 1 << 30     # idle page-locked bytes kept in total
 
     def __init__(self):
         self.free = {}
+        self.free_bytes = 0
 
-    def take(self, nbytes):
-        lst = self.free.get(nbytes)
+    @staticmethod
+    def _cls(nbytes):
+        return 1 << max(int(nbytes) - 1, 0).bit_length()
+
+    def take(self, size):
+        lst = self.free.get(size)
         if lst:
+            self.free_bytes -= size
             return lst.pop()
         p = C.c_void_p()
-        if _cabi.load().cnfb200_host_alloc(nbytes, C.byref(p)) != 0 or not p.value:
+        if _cabi.load().cnfb200_host_alloc(size, C.byref(p)) != 0 or not p.value:
             return None
         return p.value
 
-    def give(self, nbytes, addr):
-        lst = self.free.setdefault(nbytes, [])
-        if len(lst) < self.MAX_KEEP:
+    def give(self, size, addr):
+        lst = self.free.setdefault(size, [])
+        if len(lst) < self.MAX_KEEP and self.free_bytes + size <= self.MAX_FREE_BYTES:
             lst.append(addr)
+            self.free_bytes += size
         else:
             _cabi.load().cnfb200_host_free(addr)
 
     def empty(self, shape):
         nbytes = int(np.prod(shape)) * 4
-        addr = self.take(nbytes) if nbytes >= self.MIN_BYTES else None
+        size = self._cls(nbytes)
+        addr = self.take(size) if nbytes >= self.MIN_BYTES else None
         if addr is None:
             return np.empty(shape, np.float32)
         buf = (C.c_float * (nbytes // 4)).from_address(addr)
-        weakref.finalize(buf, self.give, nbytes, addr)     # the numpy array keeps `buf` alive through .base
+        weakref.finalize(buf, self.give, size, addr)     # the numpy array keeps `buf` alive through .base
         return np.frombuffer(buf, dtype=np.float32).reshape(shape)
 
 

@@ -445,6 +445,31 @@ static int enqueue_attempt(cnf_handle* h, const CnfBufs& bf, int mode) {
     return CNF_OK;
 }
 
+// A rank that cannot enqueue the attempt its peers are about to run (out of memory for the next state slot) must not
+// simply return: with the peer-memory exchange its peers would spin in k_controller_p2p until the 60 s trap, with NCCL
+// they would block in the allreduce.  It contributes a NaN partial to that attempt's error-norm exchange instead, so
+// the replicated controllers of ALL ranks end the solve at the same attempt (retcode Unstable on the peers), and then
+// reports its own error.  In the NCCL variant the peers run one more (speculative, no-op) attempt before they learn
+// `done`; its allreduce is matched here.
+__global__ void k_poison_errsum(CnfCtrl* c) { c->errsum = __longlong_as_double(0x7ff8000000000000LL); }
+static void poison_attempt(cnf_handle* h) {
+    if (h->nranks <= 1) return;
+    k_poison_errsum<<<1, 1, 0, h->stream>>>(h->d_ctrl);
+    if (!h->p2p_ok) cnf_nccl_allreduce_f64(h, &h->d_ctrl->errsum, 1);
+    launch_controller(h);
+    if (!h->p2p_ok) cnf_nccl_allreduce_f64(h, &h->d_ctrl->errsum, 1);
+    cudaStreamSynchronize(h->stream);
+    cudaGetLastError();
+}
+// test hook: CNFB200_TEST_SLOT_FAIL="<rank>:<attempt>" makes that rank fail like an out-of-memory state slot would
+static bool test_slot_fail(const cnf_handle* h, long long attempt) {
+    const char* e = getenv("CNFB200_TEST_SLOT_FAIL");
+    if (!e) return false;
+    int r = -1;
+    long long a = -1;
+    return sscanf(e, "%d:%lld", &r, &a) == 2 && r == h->rank && a == attempt;
+}
+
 // state already packed into slot 0; runs the adaptive solve; fills stats (host copy of ctrl)
 static int solve_device(cnf_handle* h, const CnfBufs& bf, int mode, int R, long long Bglobal,
                         float t0, float t1, bool use_tape, CnfCtrl* out) {
@@ -508,7 +533,15 @@ static int solve_device(cnf_handle* h, const CnfBufs& bf, int mode, int R, long 
     long long launched = 0;
     int pend = -1;  // index of the pinned snapshot in flight
     for (;;) {
-        if (use_tape && (long long)h->slots.size() < launched + 2 && (rc = ensure_slots(h, (size_t)(launched + 10), (size_t)(launched + 2)))) return rc;
+        if (use_tape && (long long)h->slots.size() < launched + 2 && (rc = ensure_slots(h, (size_t)(launched + 10), (size_t)(launched + 2)))) {
+            poison_attempt(h);
+            return rc;
+        }
+        if (test_slot_fail(h, launched)) {
+            poison_attempt(h);
+            h->err = "state slots of the step tape do not fit the device memory (simulated: CNFB200_TEST_SLOT_FAIL)";
+            return CNF_ERR_OOM;
+        }
         if (use_tape && (long long)h->ktape.size() < launched + 2 &&
             (rc = ensure_ktape(h, (size_t)(launched + 10), (long long)c.D * bf.Bs))) return rc;
         if ((rc = enqueue_attempt(h, bf, mode))) return rc;

@@ -51,6 +51,29 @@ def main():
                 out[cid] = dict(dsteps=abs(s1["naccept"] - res["naccept"]),
                                 lp_rel=float(np.max(np.abs(lp1[lo:hi] - res["lp"]) / np.abs(lp1[lo:hi]))))
         dist.barrier()
+    # a rank that fails on the host mid-solve (simulated out-of-memory state slot at its 3rd attempt) must take its
+    # peers out of the solve with it: they return promptly with retcode Unstable instead of spinning on its mailbox
+    import time
+    inp = wl.make_inputs("C2", B=1 << 14)
+    lo, hi = cnf.parallel.shard_range(1 << 14, rank, world)
+    icnf = make_icnf("C2")
+    icnf.resource.device = local
+    cnf.parallel.init_comm(icnf, rank, world)
+    os.environ["CNFB200_TEST_SLOT_FAIL"] = f"{world - 1}:2"
+    t0 = time.perf_counter()
+    try:
+        cnf.inference(icnf, cnf.TestMode(), inp["xs"][lo:hi].T, inp["theta"], {})
+        outcome = ("ret", cnf.last_stats(icnf)["retcode"])
+    except cnf._cabi.CnfError as e:
+        outcome = ("err", "rc=-4" in str(e))
+    took = time.perf_counter() - t0
+    del os.environ["CNFB200_TEST_SLOT_FAIL"]
+    dist.barrier()
+    lp, _ = cnf.inference(icnf, cnf.TestMode(), inp["xs"][lo:hi].T, inp["theta"], {})   # the handles still work
+    st = cnf.last_stats(icnf)
+    gathered = [None] * world
+    dist.all_gather_object(gathered, dict(outcome=outcome, took=took, after=(st["retcode"], st["naccept"], bool(np.isfinite(lp).all()))))
+    out["collective_failure"] = gathered
     if rank == 0:
         print("RESULT " + json.dumps(out), flush=True)
     dist.destroy_process_group()

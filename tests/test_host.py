@@ -128,6 +128,21 @@ def test_pinned_output_pool_recycles_buffers_only_after_every_view_is_gone():
     assert pool.free == {1 << 18: [handed[0]]}
     c = pool.empty((1 << 14, 4))
     assert c.ctypes.data == handed[0]          # recycled
+    assert pool._cls(3 << 16) == 1 << 18 and pool._cls(1 << 18) == 1 << 18   # size classes: powers of two
+    pool.MAX_FREE_BYTES = 0                    # over the cap a returned buffer is freed, not kept
+    freed = []
+    orig_load = cnf._cabi.load
+
+    class _Lib:
+        def cnfb200_host_free(self, addr):
+            freed.append(addr)
+
+    cnf._cabi.load = lambda: _Lib()
+    try:
+        pool.give(1 << 18, 12345)
+    finally:
+        cnf._cabi.load = orig_load
+    assert freed == [12345] and 12345 not in pool.free.get(1 << 18, [])
     small = pool.empty((8, 4))                 # small results stay ordinary numpy arrays
     assert small.base is None and len(handed) == 2
     # without a CUDA device cnfb200_host_alloc refuses and the pool falls back to pageable memory

@@ -26,3 +26,9 @@ def test_shard_invariance_two_ranks():
         assert res["C2"]["lp_rel"] < 1e-4
     if res["C4"]["dsteps"] == 0:
         assert res["C4"]["loss_rel"] < 1e-4 and res["C4"]["grad_rel"] < 1e-3
+    cf = res["collective_failure"]
+    assert cf[-1]["outcome"] == ["err", True]                         # the failing rank reports its own error
+    assert all(r["outcome"] == ["ret", 3] for r in cf[:-1])             # its peers leave the solve: retcode Unstable
+    assert all(r["took"] < 20.0 for r in cf)                            # promptly, not after the 60 s mailbox trap
+    assert all(r["after"][0] == 0 and r["after"][2] for r in cf)        # and every handle still solves afterwards
+    assert len({r["after"][1] for r in cf}) == 1
