@@ -62,6 +62,8 @@ def parse():
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-parity", action="store_true")
     p.add_argument("--no-extra", action="store_true", help="default run without the train / strong-scaling blocks")
+    p.add_argument("--extras", default="train,cond_strong,train_strong",
+                   help="which extra blocks the default run carries (comma list; debugging aid)")
     p.add_argument("--cpu-sample", type=int, default=0)
     p.add_argument("--tc-dbg", type=int, default=0, help="debug / timing-experiment bits of the tensor-core kernels (option tc_dbg)")
     p.add_argument("--stage-sample", type=int, default=13, help="time every N-th stage-kernel launch with CUDA events (1 = all)")
@@ -652,10 +654,14 @@ def main():
             ("train_strong", "C5", "train", max(wl.CONFIGS["C5"]["B"] // world, 1), min(args.steps, 2 if world < 4 else 5), 3, True),
         ]
         for name, xc, xk, xB, xs, xw, xstrong in extras:
+            if name not in args.extras.split(","):
+                continue
             try:
                 blk = run_leg(ctx, xc, xk, xB, xs, xw, strong=xstrong, want_cpu=(name == "train"),
                               want_parity=True)
             except Exception as e:   # an extra block must not take the headline record down with it
+                import traceback
+                traceback.print_exc(file=sys.stderr)
                 blk = {"error": f"{type(e).__name__}: {e}"}
                 ok = False
             if ctx.rank == 0:

@@ -17,6 +17,36 @@ static bool is_device_ptr(const void* p) {
 }
 static inline long long round_up(long long x, long long m) { return (x + m - 1) / m * m; }
 
+// ---- trap record (cnf_tc_ptx.cuh: trap_with_record): one page-locked word per process, its address published to
+// the device global of every device a handle is created on
+static unsigned long long* g_trap_host = nullptr;
+static bool g_trap_dev[64] = {};
+static void trap_record_setup(int device) {
+    if (device < 0 || device >= 64 || g_trap_dev[device]) return;
+    if (!g_trap_host) {
+        if (cudaHostAlloc((void**)&g_trap_host, sizeof(unsigned long long), cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) {
+            cudaGetLastError();
+            g_trap_host = nullptr;
+            return;
+        }
+        *g_trap_host = 0ull;
+    }
+    unsigned long long* dptr = nullptr;
+    if (cudaHostGetDevicePointer((void**)&dptr, g_trap_host, 0) == cudaSuccess &&
+        cudaMemcpyToSymbol(tc::g_cnf_trap_record, &dptr, sizeof(dptr)) == cudaSuccess)
+        g_trap_dev[device] = true;
+    cudaGetLastError();
+}
+std::string cnf_trap_note() {
+    if (!g_trap_host) return "";
+    const unsigned long long v = *reinterpret_cast<volatile unsigned long long*>(g_trap_host);
+    if (!(v & 1ull)) return "";
+    char buf[160];
+    snprintf(buf, sizeof(buf), " [bounded wait gave up: site 0x%llx, block %llu, thread %llu, parity %llu]", v >> 48,
+             (v >> 32) & 0xffffull, (v >> 16) & 0xffffull, (v >> 8) & 0xffull);
+    return buf;
+}
+
 extern "C" const char* cnfb200_version(void) { return "cnfb200 0.1.0 (sm_100a)"; }
 
 extern "C" const char* cnfb200_last_error(const cnf_handle* h) { return h ? h->err.c_str() : "null handle"; }
@@ -57,6 +87,7 @@ extern "C" int32_t cnfb200_create(const cnf_config* cfg, cnf_handle** out) {
         return CNF_ERR_UNSUPPORTED;
     }
     CNF_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    trap_record_setup(h->device);
     CNF_CUDA(cudaEventCreate(&h->ev0));
     CNF_CUDA(cudaEventCreate(&h->ev1));
     CNF_CUDA(cudaEventCreate(&h->ev2));

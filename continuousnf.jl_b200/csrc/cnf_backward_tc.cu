@@ -91,7 +91,7 @@ k_tc_wgrad(const __grid_constant__ WgMaps mp, WgArgs ar) {
             int stage = 0; uint32_t phase = 0;
             for (int t = 0; t < ar.nterm; ++t)
                 for (int kb = kb0; kb < kb1; ++kb) {
-                    tc::mbar_wait(&ctl->empty[stage], phase ^ 1);
+                    tc::mbar_wait(&ctl->empty[stage], phase ^ 1, 0x201);
                     uint8_t* s = stages + (size_t)stage * stage_bytes;
                     tc::mbar_arrive_expect_tx(&ctl->full[stage], stage_bytes);
                     for (int q = 0; q < 2; ++q) {
@@ -114,7 +114,7 @@ k_tc_wgrad(const __grid_constant__ WgMaps mp, WgArgs ar) {
             uint32_t first = 1, first_b = 1;
             for (int t = 0; t < ar.nterm; ++t)
                 for (int kb = kb0; kb < kb1; ++kb) {
-                    tc::mbar_wait(&ctl->full[stage], phase);
+                    tc::mbar_wait(&ctl->full[stage], phase, 0x202);
                     tc::tc_fence_after();
                     const uint32_t s = tc::smem_u32(stages + (size_t)stage * stage_bytes);
 #pragma unroll
@@ -142,7 +142,7 @@ k_tc_wgrad(const __grid_constant__ WgMaps mp, WgArgs ar) {
         }
     } else {               // ===== epilogue: lane = output feature o, columns = input features i
         const int quad = warp & 3;
-        tc::mbar_wait(&ctl->tfull, 0);
+        tc::mbar_wait(&ctl->tfull, 0, 0x203);
         tc::tc_fence_after();
         const int o = mb * 128 + quad * 32 + lane;
         const uint32_t tbase = tmem + ((uint32_t)(quad * 32) << 16);

@@ -88,11 +88,15 @@ struct cnf_handle {
     void* ntc_state = nullptr;  // narrow tensor-core path state (cnf_stage_narrow_tc.cu)
 };
 
+// " [bounded wait gave up: site 0x..., block ..., thread ..., parity ...]" when a kernel trapped out of a wedged wait
+// (the record lives in page-locked host memory and outlives the context), else "" (cnf_api.cu)
+std::string cnf_trap_note();
+
 #define CNF_CUDA(call)                                                                   \
     do {                                                                                 \
         cudaError_t e__ = (call);                                                        \
         if (e__ != cudaSuccess) {                                                        \
-            h->err = std::string(#call) + ": " + cudaGetErrorString(e__);                \
+            h->err = std::string(#call) + ": " + cudaGetErrorString(e__) + cnf_trap_note();   \
             return (e__ == cudaErrorMemoryAllocation) ? CNF_ERR_OOM : CNF_ERR_CUDA;      \
         }                                                                                \
     } while (0)

@@ -100,7 +100,7 @@ struct FusedArgs {
 };
 
 struct FusedCtl {
-    uint64_t wbar, ready[FU_SLOTS], done[FU_SLOTS], turn[FU_SLOTS];
+    uint64_t wbar, ready[FU_SLOTS], done[FU_SLOTS], turn[FU_SLOTS][2];   // turn: two barriers per direction, used alternately
     uint32_t tmem_base;
 };
 
@@ -292,7 +292,7 @@ __global__ void __launch_bounds__(FU_THREADS, 1) k_tc_fused(const __grid_constan
         for (int l = 0; l < 3; ++l)
             for (int q = 0; q < 2; ++q) tc::tma_prefetch_desc(&mp.w[l][q]);
         tc::mbar_init(&ctl->wbar, 1);
-        for (int s = 0; s < FU_SLOTS; ++s) { tc::mbar_init(&ctl->ready[s], FU_WORKERS); tc::mbar_init(&ctl->done[s], 1); tc::mbar_init(&ctl->turn[s], 1); }
+        for (int s = 0; s < FU_SLOTS; ++s) { tc::mbar_init(&ctl->ready[s], FU_WORKERS); tc::mbar_init(&ctl->done[s], 1); tc::mbar_init(&ctl->turn[s][0], 1); tc::mbar_init(&ctl->turn[s][1], 1); }
         tc::fence_barrier_init();
     }
     if (warp == 0) tc::tmem_alloc(&ctl->tmem_base, 512);
@@ -340,7 +340,7 @@ __global__ void __launch_bounds__(FU_THREADS, 1) k_tc_fused(const __grid_constan
     const float* sb3 = sbias + 2 * H;
     uint32_t dpar = 0, rpar = 0;
     const int cbeg = hf * (H / 2);
-    if (wl == FU_ISSUER) tc::mbar_wait(&ctl->wbar, 0);
+    if (wl == FU_ISSUER) tc::mbar_wait(&ctl->wbar, 0, 0x740);
     // hand the slot's operands to the tensor core: arrive; the issuer warp waits for all eight warps, issues phase p
     // and commits; everybody then waits for the MMAs
 #define FU_STAMP(k_)                                                                              \
@@ -353,7 +353,7 @@ __global__ void __launch_bounds__(FU_THREADS, 1) k_tc_fused(const __grid_constan
         __syncwarp();                                                                             \
         if (lane == 0) tc::mbar_arrive(&ctl->ready[s]);                                           \
         if (wl == FU_ISSUER) {                                                                    \
-            tc::mbar_wait(&ctl->ready[s], rpar);                                                  \
+            tc::mbar_wait(&ctl->ready[s], rpar, 0x720 + (p_));                                    \
             rpar ^= 1;                                                                            \
             tc::tc_fence_after();                                                                 \
             if (lane == 0) {                                                                      \
@@ -362,7 +362,7 @@ __global__ void __launch_bounds__(FU_THREADS, 1) k_tc_fused(const __grid_constan
             }                                                                                     \
             __syncwarp();                                                                         \
         }                                                                                         \
-        tc::mbar_wait(&ctl->done[s], dpar);                                                       \
+        tc::mbar_wait(&ctl->done[s], dpar, 0x710 + (p_));                                                      \
         dpar ^= 1;                                                                                \
         tc::tc_fence_after();                                                                     \
         if (!((p_) == 5 && j + FU_SLOTS >= my_tiles)) FU_BATON_WAIT()                             \
@@ -395,17 +395,26 @@ __global__ void __launch_bounds__(FU_THREADS, 1) k_tc_fused(const __grid_constan
     // measured, both in their elementwise phase together, then both waiting for the tensor pipe).  Section k of slot 0
     // follows section k - 1 of slot 1; section k of slot 1 follows section k of slot 0.  A section = the work between
     // two hand-offs (E9 of a tile and P0 of the next one are one section); 6 per tile.
+    // Pass k of a slot goes to barrier k & 1 of the other slot's pair and is awaited with parity (k >> 1) & 1.  With ONE
+    // barrier per direction the scheme deadlocked about once in 10^4 launches: warp 0 passes the baton on its own, at
+    // the start of its hand-off, and in the sections where the hf = 0 warps have no work the two slots' warp 0 can
+    // complete two phases of that barrier within a few hundred cycles; a sibling warp still on its way to its wait
+    // (cold instruction cache: the first launches after another model's kernels) then tests a parity that has already
+    // come round again — a parity wait cannot tell "two phases ahead" from "not yet" — and waits for ever (found through
+    // the trap record, tc::trap_with_record, site 0x730).  With two barriers used alternately a barrier completes a
+    // second time only after passes k + 1 and k + 2 of BOTH slots, and pass k + 2 of this slot needs hand-off k + 1 of
+    // this slot, at which all eight of its warps have arrived, i.e. have left the wait for pass k.
     const bool baton = (ar.dbg & 8) == 0;
     const int n_other6 = 6 * ((my_tiles - (1 - s) + 1) / 2);   // sections of the other slot
     uint32_t ksec = 0;
 #define FU_BATON_WAIT()                                                                              \
     if (baton) {                                                                                     \
-        if (s == 0) { if (ksec >= 1 && (int)ksec - 1 < n_other6) tc::mbar_wait(&ctl->turn[0], (ksec - 1) & 1); } \
-        else tc::mbar_wait(&ctl->turn[1], ksec & 1);                                                 \
+        if (s == 0) { if (ksec >= 1 && (int)ksec - 1 < n_other6) tc::mbar_wait(&ctl->turn[0][(ksec - 1) & 1], ((ksec - 1) >> 1) & 1, 0x730); } \
+        else tc::mbar_wait(&ctl->turn[1][ksec & 1], (ksec >> 1) & 1, 0x731);                          \
     }
 #define FU_BATON_PASS()                                                                              \
     {                                                                                                \
-        if (baton && wl == 0 && lane == 0) tc::mbar_arrive(&ctl->turn[1 - s]);                       \
+        if (baton && wl == 0 && lane == 0) tc::mbar_arrive(&ctl->turn[1 - s][ksec & 1]);             \
         ++ksec;                                                                                      \
     }
     if (s < my_tiles) FU_BATON_WAIT()

@@ -72,7 +72,7 @@ __device__ __forceinline__ void ntc_bar_arrive(int id) { asm volatile("bar.arriv
 __device__ __forceinline__ void ntc_wait_sleep(uint64_t* bar, uint32_t parity, int nosleep = 0) {
     for (uint32_t it = 0; !tc::mbar_try_wait(bar, parity); ++it) {
         if (!nosleep) __nanosleep(64);
-        if (it > (1u << 24)) { asm volatile("trap;"); }
+        if (it > (1u << 24)) tc::trap_with_record(0x601, parity);
     }
 }
 // packed FP32 pairs (sm_100 f32x2 instructions); ptxas keeps the pairs in aligned registers, no moves
@@ -234,7 +234,7 @@ k_stage_narrow_tc(const NtcW* __restrict__ wsmall, const __half* __restrict__ w2
                     }
                 }
                 __nanosleep(32);   // a busy poll would take issue slots from the four worker warps of this scheduler
-                if (++spins > (1u << 24)) { asm volatile("trap;"); }
+                if (++spins > (1u << 24)) tc::trap_with_record(0x602, 0);
             }
         }
     } else {

@@ -259,7 +259,7 @@ __device__ __forceinline__ void tc_lds128(uint32_t addr, uint32_t* v) {
 template <bool F32>
 __device__ __forceinline__ void tc_ring_read(TcSmemCtl* ctl, TcRing& ring, int sub, int row, int lane, TcAux& a) {
     const int slot = sub * ring.d + (int)(ring.j % (uint32_t)ring.d);
-    tc::mbar_wait(&ctl->xfull[slot], (ring.j / (uint32_t)ring.d) & 1);
+    tc::mbar_wait(&ctl->xfull[slot], (ring.j / (uint32_t)ring.d) & 1, 0x101);
     ring.j++;
     const uint32_t sp = tc::smem_u32(ring.base) + (uint32_t)slot * (F32 ? 16384u : 8192u);
     uint32_t dep = 0;
@@ -604,7 +604,7 @@ k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, i
             for (int t = blockIdx.x; t < total; t += gridDim.x) {
                 const int mb = t / n_tiles, nb = t % n_tiles;
                 for (int kb = 0; kb < nk; ++kb) {
-                    tc::mbar_wait(&ctl->empty[stage], phase ^ 1);
+                    tc::mbar_wait(&ctl->empty[stage], phase ^ 1, 0x102);
                     uint8_t* s = smem + (size_t)stage * stage_bytes;
                     tc::mbar_arrive_expect_tx(&ctl->full[stage], stage_bytes);
                     for (int q = 0; q < 2; ++q) {
@@ -621,11 +621,11 @@ k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, i
             int stage = 0; uint32_t phase = 0; int it = 0;
             for (int t = blockIdx.x; t < total; t += gridDim.x, ++it) {
                 const int acc = it & 1;
-                tc::mbar_wait(&ctl->tempty[acc], ((it >> 1) & 1) ^ 1);
+                tc::mbar_wait(&ctl->tempty[acc], ((it >> 1) & 1) ^ 1, 0x103);
                 tc::tc_fence_after();
                 const uint32_t dcol = tmem + (uint32_t)acc * 256;
                 for (int kb = 0; kb < nk; ++kb) {
-                    tc::mbar_wait(&ctl->full[stage], phase);
+                    tc::mbar_wait(&ctl->full[stage], phase, 0x104);
                     tc::tc_fence_after();
                     const uint32_t s = tc::smem_u32(smem + (size_t)stage * stage_bytes);
 #pragma unroll
@@ -656,7 +656,7 @@ k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, i
                     const int k = c % TC_NSUB;
                     const uint32_t jj = (k == 0) ? j[0]++ : (k == 1 ? j[1]++ : j[2]++);
                     const int slot = k * naux + (int)(jj % (uint32_t)naux);
-                    tc::mbar_wait(&ctl->xempty[slot], ((jj / (uint32_t)naux) & 1) ^ 1);
+                    tc::mbar_wait(&ctl->xempty[slot], ((jj / (uint32_t)naux) & 1) ^ 1, 0x105);
                     uint8_t* sp = ring_base + (size_t)slot * slot_bytes;
                     tc::mbar_arrive_expect_tx(&ctl->xfull[slot], slot_bytes);
                     tc::tma_load_2d(&mp.x[0], &ctl->xfull[slot], sp, nb * BN + c * TC_CW, mb * TC_BM);
@@ -681,7 +681,7 @@ k_tc_gemm(const __grid_constant__ TcMaps mp, int m_tiles, int n_tiles, int BN, i
                 const int ng0 = nb * BN + sub * TC_CW;
                 if (!RING && sub * TC_CW < BN && ng0 < ep.N) tc_aux_load<PREC, BWD, KIND>(ep, rloc, ep.row0 + rloc, ng0, aux);
             }
-            tc::mbar_wait(&ctl->tfull[acc], (it >> 1) & 1);
+            tc::mbar_wait(&ctl->tfull[acc], (it >> 1) & 1, 0x106);
             tc::tc_fence_after();
             const uint32_t tbase = tmem + ((uint32_t)(quad * 32) << 16) + (uint32_t)acc * 256;
             if (BWD) tc_epilogue_bwd<KIND, RING>(ep, ctl, tbase, mb, nb, BN, quad, sub, lane, it & 1, aux, ring);

@@ -48,10 +48,23 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
         : "memory");
     return ok != 0;
 }
+// Where a bounded spin gave up: a record in page-locked host memory (mapped; survives the dead context), written
+// before the trap.  {tag << 48 | blockIdx.x << 32 | threadIdx.x << 16 | parity << 8 | 1}; tag = the wait site.
+__device__ unsigned long long* g_cnf_trap_record = nullptr;
+__device__ __noinline__ void trap_with_record(uint32_t tag, uint32_t parity) {
+    unsigned long long* r = g_cnf_trap_record;
+    if (r) {
+        *reinterpret_cast<volatile unsigned long long*>(r) =
+            ((unsigned long long)tag << 48) | ((unsigned long long)(blockIdx.x & 0xffffu) << 32) |
+            ((unsigned long long)(threadIdx.x & 0xffffu) << 16) | ((unsigned long long)(parity & 0xffu) << 8) | 1ull;
+        __threadfence_system();
+    }
+    asm volatile("trap;");
+}
 // bounded spin: a wedged pipeline traps instead of hanging the GPU box
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, uint32_t tag = 0) {
     for (uint32_t it = 0; !mbar_try_wait(bar, parity); ++it) {
-        if (it > (1u << 26)) { asm volatile("trap;"); }
+        if (it > (1u << 26)) trap_with_record(tag, parity);
     }
 }
 

@@ -82,7 +82,7 @@ typedef struct cnf_config {
 typedef struct cnf_stats {
     int64_t naccept, nreject, nf; /* nf = augmented_f evaluations */
     int32_t retcode;
-    int32_t kernel_path;          /* path actually used: 1 generic SIMT, 2 register-resident narrow, 3 tcgen05 layer GEMMs, 4 VectorMode, 5 whole-solve single-launch kernels, 6 narrow nets with layer 2 on tcgen05 */
+    int32_t kernel_path;          /* path actually used: 1 generic SIMT, 2 register-resident narrow, 3 tcgen05 layer GEMMs, 4 VectorMode (one-launch register kernel), 5 whole-solve single-launch kernels, 6 narrow nets with layer 2 on tcgen05, 7 fused multi-layer tcgen05 kernel (hidden 128), 8 VectorMode on the MatrixMode stage kernels */
     float t_final, dt_last;
     double ms_total;              /* device time of the whole call (CUDA events) */
     double ms_solve;              /* device time of the RK loop only */
