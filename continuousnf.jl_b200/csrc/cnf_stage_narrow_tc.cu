@@ -204,7 +204,9 @@ k_stage_narrow_tc(const NtcW* __restrict__ wsmall, const __half* __restrict__ w2
             while (left[0] > 0 || left[1] > 0) {
 #pragma unroll
                 for (int q = 0; q < NTC_GROUPS; ++q) {
-                    if (left[q] > 0 && tc::mbar_try_wait(&full[q], ph[q])) {
+                    // test_wait, not try_wait: the issuer watches both groups and must not be put to sleep on one
+                    // group's barrier while the other group's tile becomes ready (option tc_dbg & 256: the old try_wait)
+                    if (left[q] > 0 && ((dbg & 256) ? tc::mbar_try_wait(&full[q], ph[q]) : tc::mbar_test_wait(&full[q], ph[q]))) {
                         tc::tc_fence_after();
                         const uint32_t alo0 = (uint32_t)tc::umma_desc_sw128(sA + (uint32_t)q * (NTC_NVA * 2 * NTC_PLANE_A));
                         const uint32_t tq = *tmem_slot + (uint32_t)q * 256u;

@@ -48,6 +48,19 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
         : "memory");
     return ok != 0;
 }
+// non-blocking test (try_wait may suspend the thread for a hardware time slice before it reports "not yet": a poller
+// that watches several barriers must not sleep on one of them)
+__device__ __forceinline__ bool mbar_test_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred P;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 P, [%1], %2;\n\t"
+        "selp.b32 %0, 1, 0, P;\n\t}\n"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
 // Where a bounded spin gave up: a record in page-locked host memory (mapped; survives the dead context), written
 // before the trap.  {tag << 48 | blockIdx.x << 32 | threadIdx.x << 16 | parity << 8 | 1}; tag = the wait site.
 __device__ unsigned long long* g_cnf_trap_record = nullptr;

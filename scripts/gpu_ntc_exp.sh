@@ -5,10 +5,10 @@ rm -f gpurun_out/exp_c2*.json
 timeout 900 python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "narrow or C2 or c2 or logdensity" > gpurun_out/t_ntc.log 2>&1; echo "tests rc=$?" > gpurun_out/rcs3.txt
 B="timeout 600 python bench.py --config C2 --no-cpu-baseline --steps 10 --warmup 3"
 $B > gpurun_out/exp_c2_a.json 2> gpurun_out/exp_c2.err; echo "c2 rc=$?" >> gpurun_out/rcs3.txt
-$B --tc-dbg 64 > gpurun_out/exp_c2_nopdl.json 2>> gpurun_out/exp_c2.err
+$B --tc-dbg 256 > gpurun_out/exp_c2_trywait.json 2>> gpurun_out/exp_c2.err
+$B --tc-dbg 128 > gpurun_out/exp_c2_stagger.json 2>> gpurun_out/exp_c2.err
+$B --tc-dbg 384 > gpurun_out/exp_c2_trywait_stagger.json 2>> gpurun_out/exp_c2.err
 $B > gpurun_out/exp_c2_b.json 2>> gpurun_out/exp_c2.err
-$B --tc-dbg 64 > gpurun_out/exp_c2_nopdl2.json 2>> gpurun_out/exp_c2.err
-$B --stage-sample 1000 > gpurun_out/exp_c2_s1000.json 2>> gpurun_out/exp_c2.err
 cat gpurun_out/rcs3.txt; tail -3 gpurun_out/t_ntc.log; python -c "
 import json,glob
 for f in sorted(glob.glob('gpurun_out/exp_c2*.json')):
