@@ -74,9 +74,51 @@ static inline unsigned grid_for(long long n) {
     if (g > 148LL * 16) g = 148LL * 16;
     return (unsigned)(g < 1 ? 1 : g);
 }
+// The same combination four samples at a time (rows are 1 KB-aligned: Bs is a multiple of 256): the scalar body above
+// keeps 2-7 four-byte loads in flight per thread and reaches about half of the copy bandwidth; 16-byte accesses with
+// all rows of an element group requested together reach most of it.  Per-element arithmetic (and so every result bit)
+// is that of d_combine.  Used by the launch-per-stage drivers; the single-CTA whole-solve kernels keep the scalar body.
+#define CNF_V4(expr_x, expr_y, expr_z, expr_w) make_float4(expr_x, expr_y, expr_z, expr_w)
+__global__ void __launch_bounds__(CNF_NT) k_combine4(const CnfCtrl* __restrict__ c, CnfBufs bf, int stage, int also_S) {
+    if (c->done) return;
+    const int nrows = (stage == 6) ? c->R : c->D;
+    const long long n4 = (long long)nrows * bf.Bs / 4, nS4 = (long long)c->D * bf.Bs / 4;
+    const float4* u = reinterpret_cast<const float4*>(bf.slots[cnf_slot(c, c->naccept)]);
+    float4* out = reinterpret_cast<float4*>((stage == 6) ? bf.slots[cnf_slot(c, c->naccept + 1)] : bf.S);
+    float4* S4 = reinterpret_cast<float4*>(bf.S);
+    const float4* k1 = reinterpret_cast<const float4*>(bf.K[c->k1idx]);
+    const float4* kj[5];
+#pragma unroll
+    for (int j = 1; j < 6; ++j) kj[j - 1] = reinterpret_cast<const float4*>(bf.K[j]);
+    const float dt = c->dt, h0 = c->tdir * c->dt0init;
+    float a[6];
+#pragma unroll
+    for (int j = 0; j < 6; ++j) a[j] = (stage >= 1 && j < stage) ? c_A[stage][j] : 0.0f;
+    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n4; e += (long long)gridDim.x * blockDim.x) {
+        const float4 uv = u[e], k = k1[e];
+        float4 kv[5];
+#pragma unroll
+        for (int j = 1; j < 6; ++j)
+            if (j < stage) kv[j - 1] = kj[j - 1][e];
+        float4 v;
+        if (stage < 0) {
+            v = CNF_V4(fmaf(h0, k.x, uv.x), fmaf(h0, k.y, uv.y), fmaf(h0, k.z, uv.z), fmaf(h0, k.w, uv.w));
+        } else {
+            float4 acc = CNF_V4(a[0] * k.x, a[0] * k.y, a[0] * k.z, a[0] * k.w);
+#pragma unroll
+            for (int j = 1; j < 6; ++j)
+                if (j < stage)
+                    acc = CNF_V4(fmaf(a[j], kv[j - 1].x, acc.x), fmaf(a[j], kv[j - 1].y, acc.y), fmaf(a[j], kv[j - 1].z, acc.z),
+                                 fmaf(a[j], kv[j - 1].w, acc.w));
+            v = CNF_V4(fmaf(dt, acc.x, uv.x), fmaf(dt, acc.y, uv.y), fmaf(dt, acc.z, uv.z), fmaf(dt, acc.w, uv.w));
+        }
+        out[e] = v;
+        if (stage >= 0 && also_S && e < nS4) S4[e] = v;   // z rows of the new state
+    }
+}
 void launch_combine(cnf_handle* h, const CnfBufs& bf, int stage, int also_S) {
     int nrows = (stage == 6) ? h->cur_R : h->cfg.D;
-    k_combine<<<grid_for((long long)nrows * bf.Bs), CNF_NT, 0, h->stream>>>(h->d_ctrl, bf, stage, also_S);
+    k_combine4<<<grid_for((long long)nrows * bf.Bs / 4), CNF_NT, 0, h->stream>>>(h->d_ctrl, bf, stage, also_S);
     h->launches++;
 }
 
@@ -119,8 +161,63 @@ __device__ __forceinline__ void d_errnorm(CnfCtrl* c, const CnfBufs& bf) {
     if (threadIdx.x == 0) { atomicAdd(&c->errsum, acc); atomicAdd(&c->stiffu, su); atomicAdd(&c->stiffd, sd); }
 }
 __global__ void k_errnorm(CnfCtrl* c, CnfBufs bf) { d_errnorm(c, bf); }
+// four samples at a time, like k_combine4 (nine rows are read per element: the scalar body is latency-bound).  The
+// per-element quantities are those of d_errnorm; a thread adds its elements in a different order, which moves the
+// FP64 sums in their last bits (as the order of the block atomics already does).
+__global__ void __launch_bounds__(CNF_NT) k_errnorm4(CnfCtrl* c, CnfBufs bf) {
+    if (c->done) return;
+    __shared__ double sh[32];
+    const int R = c->R;
+    const float4* u = reinterpret_cast<const float4*>(bf.slots[cnf_slot(c, c->naccept)]);
+    const float4* un = reinterpret_cast<const float4*>(bf.slots[cnf_slot(c, c->naccept + 1)]);
+    const float4* k1 = reinterpret_cast<const float4*>(bf.K[c->k1idx]);
+    const float4* k7 = reinterpret_cast<const float4*>(bf.K[6 - c->k1idx]);
+    const float4* kj[5];
+#pragma unroll
+    for (int j = 1; j < 6; ++j) kj[j - 1] = reinterpret_cast<const float4*>(bf.K[j]);
+    const float dt = c->dt, reltol = c->reltol, abstol = c->abstol;
+    double acc = 0.0, su = 0.0, sd = 0.0;
+    const long long n4 = (long long)R * bf.Bs / 4, Bs4 = bf.Bs / 4;
+    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n4; e += (long long)gridDim.x * blockDim.x) {
+        const long long b0 = (e % Bs4) * 4;
+        if (b0 >= bf.B) continue;
+        const float4 uv = u[e], nv = un[e], q1 = k1[e], q7 = k7[e];
+        float4 kv[5];
+#pragma unroll
+        for (int j = 0; j < 5; ++j) kv[j] = kj[j][e];
+        const float U[4] = {uv.x, uv.y, uv.z, uv.w}, N[4] = {nv.x, nv.y, nv.z, nv.w}, K1[4] = {q1.x, q1.y, q1.z, q1.w},
+                    K7[4] = {q7.x, q7.y, q7.z, q7.w};
+        float KJ[5][4];
+#pragma unroll
+        for (int j = 0; j < 5; ++j) { KJ[j][0] = kv[j].x; KJ[j][1] = kv[j].y; KJ[j][2] = kv[j].z; KJ[j][3] = kv[j].w; }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            if (b0 + i >= bf.B) continue;
+            float a = c_BT[0] * K1[i];
+#pragma unroll
+            for (int j = 1; j < 6; ++j) a = fmaf(c_BT[j], KJ[j - 1][i], a);
+            a = fmaf(c_BT[6], K7[i], a);
+            float gd = (c_A[6][0] - c_A[5][0]) * K1[i];
+#pragma unroll
+            for (int j = 1; j < 5; ++j) gd = fmaf(c_A[6][j] - c_A[5][j], KJ[j - 1][i], gd);
+            gd = dt * fmaf(c_A[6][5], KJ[4][i], gd);
+            const float kd = K7[i] - KJ[4][i];
+            su += (double)kd * (double)kd;
+            sd += (double)gd * (double)gd;
+            const float ut = dt * a;
+            const float sc = fmaf(fmaxf(fabsf(U[i]), fabsf(N[i])), reltol, abstol);
+            float r = ut / sc;
+            if (N[i] != N[i]) r = N[i];
+            acc += (double)r * (double)r;
+        }
+    }
+    acc = cnf_block_sum(acc, sh);
+    su = cnf_block_sum(su, sh);
+    sd = cnf_block_sum(sd, sh);
+    if (threadIdx.x == 0) { atomicAdd(&c->errsum, acc); atomicAdd(&c->stiffu, su); atomicAdd(&c->stiffd, sd); }
+}
 void launch_errnorm(cnf_handle* h, const CnfBufs& bf) {
-    k_errnorm<<<grid_for((long long)h->cur_R * bf.Bs), CNF_NT, 0, h->stream>>>(h->d_ctrl, bf);
+    k_errnorm4<<<grid_for((long long)h->cur_R * bf.Bs / 4), CNF_NT, 0, h->stream>>>(h->d_ctrl, bf);
     h->launches++;
 }
 
