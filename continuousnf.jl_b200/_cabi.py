@@ -5,7 +5,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libcnfb200.so")
+# CNFB200_LIB: debugging aid (load a differently built library, e.g. to reproduce a fixed bug); the product is the in-tree file
+LIB_PATH = os.environ.get("CNFB200_LIB") or os.path.join(_HERE, "libcnfb200.so")
 
 MAX_LAYERS = 8
 MODE_TEST, MODE_TRAIN = 0, 1
