@@ -485,10 +485,16 @@ static int enqueue_attempt(cnf_handle* h, const CnfBufs& bf, int mode) {
 __global__ void k_poison_errsum(CnfCtrl* c) { c->errsum = __longlong_as_double(0x7ff8000000000000LL); }
 static void poison_attempt(cnf_handle* h) {
     if (h->nranks <= 1) return;
+    // was the solve already over after the last attempt this rank did enqueue?  (The controller is replicated: every
+    // rank holds the same `done`.)  Then the peers stop after the attempt they are enqueuing now and there is no
+    // further allreduce to match.
+    int was_done = 0;
+    cudaStreamSynchronize(h->stream);
+    cudaMemcpy(&was_done, &h->d_ctrl->done, sizeof(int), cudaMemcpyDeviceToHost);
     k_poison_errsum<<<1, 1, 0, h->stream>>>(h->d_ctrl);
     if (!h->p2p_ok) cnf_nccl_allreduce_f64(h, &h->d_ctrl->errsum, 1);
     launch_controller(h);
-    if (!h->p2p_ok) cnf_nccl_allreduce_f64(h, &h->d_ctrl->errsum, 1);
+    if (!h->p2p_ok && !was_done) cnf_nccl_allreduce_f64(h, &h->d_ctrl->errsum, 1);
     cudaStreamSynchronize(h->stream);
     cudaGetLastError();
 }

@@ -144,3 +144,10 @@ def test_julia_struct_mirrors_match_the_header_field_for_field():
                 assert "Array" in ct.__name__ or ct._length_ == 9
             else:
                 assert jl2c[jt] == ct.__name__, (jname, n, jt, ct.__name__)
+
+
+def test_static_scratch_limit_is_the_same_in_the_header_and_the_python_mirror():
+    import re
+    hdr = open(os.path.join(ROOT, "include", "cnfb200.h")).read()
+    m = re.search(r"#define\s+CNFB200_STATIC_SCRATCH_BYTES\s+\((\d+)u\s*<<\s*(\d+)\)", hdr)
+    assert m and (int(m.group(1)) << int(m.group(2))) == cnf._cabi.STATIC_SCRATCH_BYTES == 16 << 20
