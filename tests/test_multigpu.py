@@ -11,13 +11,22 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 @pytest.mark.gpu
-def test_shard_invariance_two_ranks():
+@pytest.mark.parametrize("exchange", ["peer-memory", "nccl"])
+def test_shard_invariance_two_ranks(exchange):
+    """both forms of the per-attempt error-norm exchange: inside the controller kernel over NVLink peer memory (default)
+    and as an ncclAllReduce launch (CNFB200_P2P=0)"""
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
-           "--master-addr", "127.0.0.1", "--master-port", "29631", os.path.join(ROOT, "tests", "multigpu_worker.py")]
-    p = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+           "--master-addr", "127.0.0.1", "--master-port", "29631" if exchange == "peer-memory" else "29632",
+           os.path.join(ROOT, "tests", "multigpu_worker.py")]
+    env = dict(os.environ)
+    if exchange == "nccl":
+        env["CNFB200_P2P"] = "0"
+    else:
+        env.pop("CNFB200_P2P", None)
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=env)
     assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
     line = [l for l in p.stdout.splitlines() if l.startswith("RESULT ")][-1]
     res = json.loads(line[7:])
