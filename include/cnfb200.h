@@ -17,6 +17,7 @@
 #ifndef CNFB200_H
 #define CNFB200_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus

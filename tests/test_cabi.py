@@ -151,3 +151,19 @@ def test_static_scratch_limit_is_the_same_in_the_header_and_the_python_mirror():
     hdr = open(os.path.join(ROOT, "include", "cnfb200.h")).read()
     m = re.search(r"#define\s+CNFB200_STATIC_SCRATCH_BYTES\s+\((\d+)u\s*<<\s*(\d+)\)", hdr)
     assert m and (int(m.group(1)) << int(m.group(2))) == cnf._cabi.STATIC_SCRATCH_BYTES == 16 << 20
+
+
+def test_headers_compile_as_plain_c(tmp_path):
+    """include/*.h are the boundary a C (or ccall / cgo / JNI) binding sees: they must stand alone in C99"""
+    import shutil
+    import subprocess
+    if not shutil.which("gcc"):
+        pytest.skip("no gcc")
+    src = tmp_path / "hdr.c"
+    src.write_text('#include "cnfb200.h"\n#include "cnf_tsit5.h"\n'
+                   "int main(void) { cnf_stats s; cnf_config c; (void)s; (void)c; return (int)sizeof(cnf_stats) - 88; }\n")
+    exe = tmp_path / "hdr"
+    p = subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I", os.path.join(ROOT, "include"),
+                        str(src), "-o", str(exe)], capture_output=True, text=True)
+    assert p.returncode == 0, p.stderr
+    assert subprocess.run([str(exe)]).returncode == 0   # sizeof(cnf_stats) is what the ctypes / Julia mirrors assume
